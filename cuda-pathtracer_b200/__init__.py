@@ -1,0 +1,7 @@
+"""B200-native path-tracing core behind the reference's ``raytrace()`` boundary.
+
+Python here is plumbing only (fixture reader, ctypes binding of the C ABI in
+``include/ptcore.h``, torch device buffers / torch.distributed for multi-GPU);
+the product is ``csrc/`` -> ``libptcore.so``.
+"""
+from . import ptscene  # noqa: F401

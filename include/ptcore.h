@@ -1,0 +1,246 @@
+/* ptcore.h -- C ABI of the B200-native path-tracing core.
+ *
+ * Drop-in boundary for the hot path of DavidPeicho/cuda-pathtracer: everything
+ * that sits behind
+ *
+ *     cudaError_t raytrace(cudaArray_const_t, const scene::Scenes&, unsigned scene_id,
+ *                          const std::vector<scene::Cubemap>&, int cubemap_id,
+ *                          const scene::Camera*, unsigned w, unsigned h, cudaStream_t,
+ *                          float3* temporal_framebuffer, bool moved, unsigned post_id)
+ *     (reference: cuda_opengl/include/shaders/raytrace.h:9-15, sole caller
+ *      cuda_opengl/src/gpu_processor.cpp:375-377)
+ *
+ * Plain C: pointers and sizes only, no C++/torch types.  All record types below
+ * are layout-identical to the reference's device data contract
+ * (cuda_opengl/include/scene/scene_data.h) so the reference's loader output can
+ * be passed without repacking.  Every entry point returns 0 on success or a
+ * negative ptc_status / positive cudaError_t; nothing exits or throws across the
+ * boundary (the reference's cudaCheckError() exits, cuda_helper.h:9-17 -- the C
+ * ABI reports instead and the C++ shim keeps the check-after convention).
+ */
+#ifndef PTCORE_H
+#define PTCORE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PTC_ABI_VERSION 1
+
+typedef enum ptc_status
+{
+  PTC_OK = 0,
+  PTC_ERR_INVALID = -1,   /* bad argument / unknown id                      */
+  PTC_ERR_NO_DEVICE = -2, /* no CUDA device: the core has NO CPU fallback    */
+  PTC_ERR_ALLOC = -3,
+  PTC_ERR_STATE = -4      /* e.g. render before upload                       */
+} ptc_status;
+
+/* == scene::Face, scene_data.h:46-53 (112 bytes, 16-aligned) */
+typedef struct ptc_face
+{
+  float vertices[3][3];  /* @0   */
+  float normals[3][3];   /* @36  */
+  float texcoords[3][2]; /* @72  */
+  float tangent[3];      /* @96  */
+  uint32_t material_id;  /* @108 */
+} ptc_face;
+
+/* == scene::Material, scene_data.h:95-100 (12 bytes of payload, 8-aligned -> 16) */
+typedef struct ptc_material
+{
+  int32_t diffuse_spec_map; /* RGBA float texture id: rgb = diffuse, a = specular mix */
+  int32_t normal_map;       /* RGB float texture id or -1                            */
+  float ior;                /* 1.0 = opaque                                          */
+  uint32_t _pad;
+} ptc_material;
+
+/* == scene::LightProp, scene_data.h:109-115 (32 bytes) */
+typedef struct ptc_light
+{
+  float color[3];
+  float vec[3]; /* sphere centre */
+  float emission;
+  float radius;
+} ptc_light;
+
+/* == scene::Texture, scene_data.h:31-37 (32 bytes, 16-aligned).  `data` is a HOST
+ * pointer here (linear floats as produced by stbi_loadf, nb_chan 3 or 4). */
+typedef struct ptc_texture
+{
+  int32_t w, h, nb_chan;
+  int32_t _pad0;
+  const float* data;
+  uint64_t _pad1;
+} ptc_texture;
+
+/* == scene::Camera, scene_data.h:123-133 (64 bytes).  u, v are outputs of ray
+ * generation in the reference (intersection.cuh:84-87); ignored on input. */
+typedef struct ptc_camera
+{
+  float position[3];
+  float dir[3];
+  float u[3];
+  float v[3];
+  float fov_x; /* radians */
+  float speed;
+  float aperture;
+  float focus_dist;
+} ptc_camera;
+
+/* One scene = what scene::SceneData + the global texture table describe
+ * (scene_data.h:71-87).  Faces are concatenated in mesh order; the global face
+ * index g = sum(mesh_face_counts[0..m-1]) + i is the hit id reported by the
+ * core, and the reference's first-index-wins tie rule
+ * (intersection.cuh:179-196) is defined on this order. */
+typedef struct ptc_scene_desc
+{
+  const ptc_face* faces;
+  const uint32_t* mesh_face_counts;
+  uint32_t n_meshes;
+  const ptc_material* materials;
+  uint32_t n_materials;
+  const ptc_light* lights;
+  uint32_t n_lights;
+  const ptc_texture* textures; /* global texture table (Scenes.textures) */
+  uint32_t n_textures;
+} ptc_scene_desc;
+
+/* Hit id encoding used by every entry point that reports hits. */
+#define PTC_HIT_MISS (-1)
+/* id in [0, n_faces)            : triangle, global face index
+ * id in [n_faces, n_faces+n_l)  : sphere light (id - n_faces)               */
+
+typedef struct ptc_render_args
+{
+  int32_t scene_id;
+  int32_t cubemap_id;
+  const ptc_camera* camera; /* host pointer, copied at call time             */
+  uint32_t width, height;   /* full image size (defines RNG ids, see below)  */
+  uint32_t row_begin, row_end; /* rows [row_begin,row_end) of the full image
+                                  rendered by this call (image-tile sharding);
+                                  0,0 means all rows                          */
+  uint32_t bounces;   /* path segments per sample; 0 -> 3, the reference's
+                         1 + (static_samples+1), raytrace.cu:66,243           */
+  uint32_t moved;     /* !=0: preview frame + accumulator reset, raytrace.cu:54-62,255,298 */
+  uint32_t post_id;   /* 0 none, 1 grayscale, 2 sepia, 3 invert, raytrace.cu:327-357 */
+  uint32_t frame_nb;  /* 0: use the context's own counter (the reference's
+                         function-static `seed`, raytrace.cu:296-300);
+                         k>0: render sample k explicitly (hash_seed = WangHash(k)) */
+  void* accum;        /* float3[(row_end-row_begin)*width] temporal framebuffer;
+                         rows stored bottom-up exactly like raytrace.cu:252 within
+                         the band.  DEVICE pointer for ptc_render, HOST (ideally
+                         pinned) for ptc_render_host                           */
+  void* out_rgba;     /* uchar4[(row_end-row_begin)*width], row 0 = top; may be NULL */
+  void* radiance_out; /* optional float3 per pixel (top-down rows): this frame's
+                         un-clamped radiance, for parity tests; may be NULL    */
+  void* stream;       /* cudaStream_t; NULL = default stream                  */
+} ptc_render_args;
+
+typedef struct ptc_counters
+{
+  uint64_t paths;          /* pixels rendered                                  */
+  uint64_t segments;       /* radiance-loop iterations == reference intersect() calls */
+  uint64_t traced;         /* closest-hit queries actually submitted to traversal */
+  uint64_t rays_per_bounce[16];
+  uint64_t nodes_visited;  /* only when built with PTC_STATS (debug entry)     */
+  uint64_t tris_tested;
+} ptc_counters;
+
+typedef struct ptc_scene_info
+{
+  uint32_t n_faces, n_lights, n_materials, n_textures;
+  uint32_t bvh_nodes;      /* wide nodes                                       */
+  uint32_t bvh_node_bytes; /* bytes per node                                   */
+  uint32_t tri_bytes;      /* bytes per intersection record                    */
+  uint32_t shade_bytes;    /* bytes per shading record                         */
+  uint64_t texture_bytes;  /* device bytes of texels                           */
+  uint32_t smem_resident;  /* 1 if nodes+triangles are staged in shared memory */
+} ptc_scene_info;
+
+typedef struct ptc_context ptc_context;
+
+int ptc_abi_version(void);
+
+/* One context per GPU.  Fails with PTC_ERR_NO_DEVICE when no CUDA device is
+ * usable -- there is no CPU fallback. */
+int ptc_create(int device, ptc_context** out);
+void ptc_destroy(ptc_context* ctx);
+const char* ptc_last_error(const ptc_context* ctx);
+
+/* Replaces Scene::upload_gpu + uploadScenes/uploadTextures
+ * (scene.cpp:370-391, gpu_processor.cpp:184-238): builds the wide BVH and the
+ * split triangle / shading records on the host, uploads them and the texel
+ * arena.  Returns the scene id to pass to ptc_render. */
+int ptc_upload_scene(ptc_context* ctx, const ptc_scene_desc* desc, int32_t* scene_id);
+int ptc_scene_info_get(const ptc_context* ctx, int32_t scene_id, ptc_scene_info* out);
+
+/* Replaces uploadCubemap (gpu_processor.cpp:68-161) after face extraction:
+ * `faces` = 6 faces (+x,-x,+y,-y,+z,-z) of size*size RGBA floats, host memory. */
+int ptc_set_cubemap(ptc_context* ctx, const float* faces, uint32_t size, int32_t* cubemap_id);
+
+/* The render call: one sample per pixel accumulated into `accum`, tonemapped
+ * RGBA8 written to `out_rgba`.  Asynchronous on args->stream, no hidden syncs. */
+int ptc_render(ptc_context* ctx, const ptc_render_args* args);
+
+/* Same, but accum / out_rgba / radiance_out are HOST buffers: accum is copied
+ * host->device only when `upload_accum` != 0 (first frame of a resumed
+ * accumulation), rendered, and out_rgba (and accum when `download_accum`)
+ * copied back; synchronises before returning. */
+int ptc_render_host(ptc_context* ctx, const ptc_render_args* args, int upload_accum,
+                    int download_accum);
+
+/* Resets the context's frame counter (what `moved` does, without a preview frame). */
+int ptc_reset_accumulation(ptc_context* ctx);
+
+int ptc_counters_get(ptc_context* ctx, ptc_counters* out);
+int ptc_counters_reset(ptc_context* ctx);
+
+/* -- parity / debugging entry points (used by tests, not by a renderer) -------- */
+
+/* Primary rays of sample `frame_nb` (RNG + camera + DOF as raytrace.cu:227-240),
+ * closest hit per pixel.  hit_ids[h*w] int32 (row 0 = top), t[h*w] float; HOST
+ * buffers; either may be NULL. */
+int ptc_trace_primary(ptc_context* ctx, int32_t scene_id, const ptc_camera* camera,
+                      uint32_t width, uint32_t height, uint32_t frame_nb,
+                      int32_t* hit_ids, float* t);
+
+/* Closest hit for n arbitrary rays (HOST arrays, origins/dirs as xyz triples). */
+int ptc_intersect_rays(ptc_context* ctx, int32_t scene_id, const float* origins,
+                       const float* dirs, uint64_t n, int32_t* hit_ids, float* t);
+
+/* First `n_draws` curand_uniform draws of curand_init(seed,0,0) for each of the
+ * n_seeds seeds, computed by the core's own XORWOW and (reference_impl != 0) by
+ * the toolkit's curand_kernel.h on the device. out[n_seeds*n_draws] HOST. */
+int ptc_debug_rng(ptc_context* ctx, const uint32_t* seeds, uint32_t n_seeds,
+                  uint32_t n_draws, int reference_impl, float* out);
+
+/* -- host-only helpers (no GPU needed) ----------------------------------------- */
+
+/* Builds the wide BVH for a scene on the host and returns its size; used by the
+ * oracle (O2 traverses the same nodes) and by CPU tests.  Buffers are owned by
+ * the library until ptc_host_bvh_free. */
+typedef struct ptc_host_bvh
+{
+  const void* nodes;       /* bvh_nodes * node_bytes                              */
+  uint32_t n_nodes;
+  uint32_t node_bytes;
+  const void* tris;        /* n_tris * tri_bytes, leaf order                      */
+  uint32_t n_tris;
+  uint32_t tri_bytes;
+  const uint32_t* tri_face_ids; /* leaf order -> global face index              */
+  float sah_cost;
+  uint32_t max_depth;
+  void* _owner;
+} ptc_host_bvh;
+
+int ptc_host_bvh_build(const ptc_scene_desc* desc, ptc_host_bvh* out);
+void ptc_host_bvh_free(ptc_host_bvh* bvh);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTCORE_H */

@@ -1,0 +1,233 @@
+// TEST INFRASTRUCTURE (oracle/_ref recipe) -- not product code.
+//
+// Runs the reference's OWN host loader (scene::Scene::upload,
+// cuda_opengl/src/scene/scene.cpp:304-358 and MaterialLoader,
+// cuda_opengl/src/scene/material_loader.cpp:153-401), compiled from the
+// sources where they lie under /root/reference and linked against
+// ref_shim/cuda_host_shim.cpp, then dumps what the path tracer kernel would
+// have received (Face[], Material[], LightProp[], Texture[], Camera, cubemap)
+// into a ".ptscene" container.  The container is the golden fixture the oracle,
+// the tests and the bench consume on machines where /root/reference is absent.
+//
+// usage: ref_loader ASSET_FOLDER SCENE_FILE OUT.ptscene
+#define STB_IMAGE_IMPLEMENTATION
+#include <stb/stb_image.h>
+
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <iostream>
+#include <string>
+#include <vector>
+
+#include <scene/material_loader.h>
+#include <scene/scene.h>
+#include <utils/texture_utils.h>
+#include <utils/utils.h>
+
+namespace {
+
+struct Writer
+{
+  FILE* f;
+  void raw(const void* p, size_t n) { fwrite(p, 1, n, f); }
+  void u32(uint32_t v) { raw(&v, 4); }
+  void i32(int32_t v) { raw(&v, 4); }
+  void f32(float v) { raw(&v, 4); }
+};
+
+// Same constant-colour cubemap as cuda_opengl/src/gpu_processor.cpp:38-58.
+std::vector<float>
+unit_cubemap(unsigned color)
+{
+  float r = ((color >> 16) & 0xFF) / 255.0f;
+  float g = ((color >> 8) & 0xFF) / 255.0f;
+  float b = (color & 0xFF) / 255.0f;
+  std::vector<float> img(4 * 6);
+  for (int n = 0; n < 6; ++n) {
+    img[n * 4 + 0] = r;
+    img[n * 4 + 1] = g;
+    img[n * 4 + 2] = b;
+    img[n * 4 + 3] = 0.0f;
+  }
+  return img;
+}
+
+// Follows uploadCubemap(), cuda_opengl/src/gpu_processor.cpp:68-161, up to the
+// point where the faces are handed to cudaMemcpy3D.
+std::vector<float>
+build_cubemap(const std::string& path_in_scene, const std::string& folder,
+              unsigned& size)
+{
+  const unsigned DEFAULT_COLOR = 0x131b23;
+  // uploadCubemaps() (gpu_processor.cpp:163-182) turns an empty path into the
+  // literal "empty" and always prefixes the asset folder.
+  std::string path = folder + "/" + (path_in_scene.empty() ? "empty" : path_in_scene);
+  size = 1;
+  if (path.empty() || utils::isHexa(path))
+    return unit_cubemap(path.empty() ? DEFAULT_COLOR
+                                     : strtol(path.c_str(), NULL, 16));
+  int w = 0, h = 0, nb_chan = 0;
+  float* loaded = stbi_loadf(path.c_str(), &w, &h, &nb_chan, STBI_default);
+  std::string error;
+  unsigned s = loaded ? w / 4 : 0;
+  if (!loaded)
+    error = "unknown error " + path;
+  else if (s != (unsigned)(h) / 3)
+    error = "width and height are not the same";
+  else if (s & (s - 1))
+    error = "size should be a power of 2";
+  if (!error.empty()) {
+    std::cerr << "ref_loader: cubemap fallback: " << error << std::endl;
+    if (loaded)
+      stbi_image_free(loaded);
+    return unit_cubemap(DEFAULT_COLOR);
+  }
+  size = s;
+  std::vector<float> img((size_t)size * size * 4 * 6);
+  float* tmp = texture::append_cube_faces(img.data(), loaded, w, 0, nb_chan, 4,
+                                          true, true);
+  tmp = texture::append_cube_faces(tmp, loaded, w, 1, nb_chan, 4, false, false);
+  texture::append_cube_faces(tmp, loaded, w, 1, nb_chan, 4, true, false);
+  stbi_image_free(loaded);
+  return img;
+}
+
+// stb_image.h:1565-1582 (stbi__ldr_to_hdr): float = (float)pow(u8/255.0f, 2.2f).
+inline float
+stb_gamma(unsigned char v)
+{
+  return (float)(pow(v / 255.0f, 2.2f) * 1.0f);
+}
+
+} // namespace
+
+int
+main(int argc, char** argv)
+{
+  if (argc < 4) {
+    std::cerr << "usage: ref_loader ASSET_FOLDER SCENE_FILE OUT.ptscene\n";
+    return 2;
+  }
+  std::string folder = argv[1], scene_file = argv[2], out = argv[3];
+
+  scene::Scene sc(folder + "/" + scene_file); // gpu_processor.cpp:262-263
+  sc.upload(nullptr);                          // gpu_processor.cpp:289
+  if (!sc.ready()) {
+    std::cerr << "ref_loader: scene failed to load: " << sc.error() << "\n";
+    return 1;
+  }
+  const scene::SceneData* sd = sc.getUploadedScenePointer(); // host memory (shim)
+  const scene::Camera cam = sc.getInitCamera();
+  const auto& textures = scene::MaterialLoader::instance()->getTextures();
+
+  FILE* f = fopen(out.c_str(), "wb");
+  if (!f) {
+    perror("ref_loader: fopen");
+    return 1;
+  }
+  Writer w{ f };
+  w.raw("PTSC", 4);
+  w.u32(1);
+  static_assert(sizeof(scene::Camera) == 64, "Camera layout");
+  static_assert(sizeof(scene::Face) == 112, "Face layout");
+  static_assert(sizeof(scene::LightProp) == 32, "LightProp layout");
+  w.raw(&cam, sizeof(cam));
+
+  w.u32(sd->lights.size);
+  for (unsigned i = 0; i < sd->lights.size; ++i)
+    w.raw(&sd->lights.data[i], sizeof(scene::LightProp));
+
+  w.u32(sd->materials.size);
+  for (unsigned i = 0; i < sd->materials.size; ++i) {
+    const scene::Material& m = sd->materials.data[i];
+    w.i32(m.diffuse_spec_map);
+    w.i32(m.normal_map);
+    w.f32(m.ior);
+  }
+
+  w.u32(sd->meshes.size);
+  size_t total_faces = 0;
+  for (unsigned i = 0; i < sd->meshes.size; ++i) {
+    w.u32(sd->meshes.data[i].faces.size);
+    total_faces += sd->meshes.data[i].faces.size;
+  }
+  for (unsigned i = 0; i < sd->meshes.size; ++i) {
+    const auto& faces = sd->meshes.data[i].faces;
+    if (faces.size)
+      w.raw(faces.data, (size_t)faces.size * sizeof(scene::Face));
+  }
+
+  w.u32((uint32_t)textures.size());
+  size_t tex_float_bytes = 0;
+  for (const scene::Texture& t : textures) {
+    w.i32(t.w);
+    w.i32(t.h);
+    w.i32(t.nb_chan);
+    size_t n = (size_t)t.w * t.h * t.nb_chan;
+    tex_float_bytes += n * 4;
+    // Try the compact form: every channel is an stb gamma-decoded byte, the
+    // alpha channel possibly a constant (pack(tex, default_a),
+    // material_loader.cpp:59-74).
+    bool compact = n > 64;
+    bool alpha_const = false;
+    float alpha_v = 0.f;
+    std::vector<unsigned char> bytes;
+    if (compact) {
+      int nc = t.nb_chan;
+      if (nc == 4) {
+        alpha_const = true;
+        alpha_v = t.data[3];
+        for (size_t i = 3; i < n; i += 4)
+          if (t.data[i] != alpha_v) {
+            alpha_const = false;
+            break;
+          }
+      }
+      int stored = (nc == 4 && alpha_const) ? 3 : nc;
+      bytes.resize((size_t)t.w * t.h * stored);
+      size_t k = 0;
+      for (size_t px = 0; px < (size_t)t.w * t.h && compact; ++px)
+        for (int c = 0; c < stored; ++c) {
+          float v = t.data[px * nc + c];
+          long q = lround(255.0 * pow((double)v, 1.0 / 2.2));
+          if (q < 0 || q > 255 || stb_gamma((unsigned char)q) != v) {
+            compact = false;
+            break;
+          }
+          bytes[k++] = (unsigned char)q;
+        }
+    }
+    if (compact) {
+      w.u32(1);
+      w.u32(alpha_const ? 1 : 0);
+      w.f32(alpha_v);
+      w.raw(bytes.data(), bytes.size());
+    } else {
+      w.u32(0);
+      w.raw(t.data, n * 4);
+    }
+  }
+
+  unsigned cube_size = 1;
+  std::vector<float> cube = build_cubemap(sc.getCubemapPath(), folder, cube_size);
+  const std::string& cp = sc.getCubemapPath();
+  w.u32((uint32_t)cp.size());
+  w.raw(cp.data(), cp.size());
+  w.u32(cube_size);
+  if (cube_size <= 64) {
+    w.u32(1);
+    w.raw(cube.data(), cube.size() * 4);
+  } else {
+    w.u32(0); // too large for a fixture; faces omitted
+  }
+  fclose(f);
+
+  std::cout << "ref_loader: " << scene_file << ": meshes=" << sd->meshes.size
+            << " faces=" << total_faces << " materials=" << sd->materials.size
+            << " lights=" << sd->lights.size << " textures=" << textures.size()
+            << " (" << tex_float_bytes << " B as float) cubemap=" << cube_size
+            << "^2x6 -> " << out << std::endl;
+  return 0;
+}

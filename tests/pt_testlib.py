@@ -1,0 +1,143 @@
+"""Shared helpers for tests / bench / fixtures: package import, fixture loading and
+ctypes wrappers around the two CHECKERS (oracle/_ref = the reference itself on host
+cores, oracle/libpt_oracle.so = the from-scratch restatement).  The product is only
+ever reached through ``pkg().Core`` (the C ABI)."""
+from __future__ import annotations
+
+import ctypes as C
+import importlib.util
+import os
+import sys
+
+import numpy as np
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(REPO, "tests", "golden")
+ORACLE_DIR = os.path.join(REPO, "oracle")
+PKG_DIR = os.path.join(REPO, "cuda-pathtracer_b200")
+PKG_NAME = "cuda_pathtracer_b200"
+
+
+def pkg():
+    """Imports the package (its directory name has a hyphen, so by path)."""
+    if PKG_NAME in sys.modules:
+        return sys.modules[PKG_NAME]
+    spec = importlib.util.spec_from_file_location(
+        PKG_NAME, os.path.join(PKG_DIR, "__init__.py"), submodule_search_locations=[PKG_DIR])
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[PKG_NAME] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+_scene_cache = {}
+
+
+def load_scene(name: str):
+    """Loads tests/golden/<name>.ptscene[.xz] (cached)."""
+    if name not in _scene_cache:
+        ptscene = pkg().ptscene
+        p = os.path.join(GOLDEN, name + ".ptscene")
+        if not os.path.exists(p):
+            p += ".xz"
+        _scene_cache[name] = ptscene.load_ptscene(p)
+    return _scene_cache[name]
+
+
+def _f32p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def cube_of(sc):
+    if sc.cubemap is None:
+        raise ValueError("fixture carries no cubemap faces")
+    return np.ascontiguousarray(sc.cubemap, dtype=np.float32), int(sc.cubemap_size)
+
+
+class _RenderLib:
+    """Common ctypes surface of libref_cpu.so (prefix ref_cpu_) and libpt_oracle.so
+    (prefix oracle_): same argument lists on purpose."""
+
+    def __init__(self, path, prefix):
+        if not os.path.exists(path):
+            raise FileNotFoundError(path)
+        self.lib = C.CDLL(path)
+        self.p = prefix
+        self.threads = os.cpu_count() or 1
+
+    def _fn(self, name):
+        return getattr(self.lib, self.p + name)
+
+    def radiance(self, sc, w, h, frame, bounces, moved=False):
+        cube, cs = cube_of(sc)
+        desc = sc.to_desc()
+        cam = sc.camera_struct()
+        out = np.zeros((h, w, 3), np.float32)
+        self._fn("radiance")(C.byref(desc), _f32p(cube), C.c_uint(cs), C.byref(cam),
+                             C.c_uint(w), C.c_uint(h), C.c_uint(frame), C.c_uint(bounces),
+                             C.c_int(int(moved)), _f32p(out), C.c_int(self.threads))
+        return out
+
+    def kernel(self, sc, w, h, frame, bounces, accum, moved=False, post_id=0):
+        """One accumulate-into-framebuffer launch; returns RGBA8 (h,w,4) uint8."""
+        cube, cs = cube_of(sc)
+        desc = sc.to_desc()
+        cam = sc.camera_struct()
+        rgba = np.zeros((h, w), np.uint32)
+        assert accum.dtype == np.float32 and accum.flags.c_contiguous
+        self._fn("kernel")(C.byref(desc), _f32p(cube), C.c_uint(cs), C.byref(cam),
+                           C.c_uint(w), C.c_uint(h), C.c_uint(frame), C.c_uint(bounces),
+                           C.c_int(int(moved)), C.c_uint(post_id), _f32p(accum),
+                           _f32p(rgba), C.c_int(self.threads))
+        return rgba.view(np.uint8).reshape(h, w, 4)
+
+    def intersect(self, sc, origins, dirs):
+        desc = sc.to_desc()
+        o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+        n = o.shape[0]
+        ids = np.zeros(n, np.int32)
+        t = np.zeros(n, np.float32)
+        self._fn("intersect")(C.byref(desc), _f32p(o), _f32p(d), C.c_uint64(n),
+                              _f32p(ids), _f32p(t), C.c_int(self.threads))
+        return ids, t
+
+    def primary_rays(self, sc, w, h, frame):
+        cam = sc.camera_struct()
+        o = np.zeros((h * w, 3), np.float32)
+        d = np.zeros((h * w, 3), np.float32)
+        self._fn("primary_rays")(C.byref(cam), C.c_uint(w), C.c_uint(h), C.c_uint(frame),
+                                 _f32p(o), _f32p(d))
+        return o, d
+
+
+class RefCpu(_RenderLib):
+    """The reference's own raytrace.cu on host cores (oracle/_ref/libref_cpu.so)."""
+
+    def __init__(self):
+        super().__init__(os.path.join(ORACLE_DIR, "_ref", "libref_cpu.so"), "ref_cpu_")
+        self.lib.ref_wang_hash.restype = C.c_uint
+
+    def wang_hash(self, a):
+        return self.lib.ref_wang_hash(C.c_uint(a & 0xFFFFFFFF))
+
+    def uniforms(self, seed, n):
+        out = np.zeros(n, np.float32)
+        self.lib.ref_curand_uniforms(C.c_uint32(seed), C.c_uint(n), _f32p(out))
+        return out
+
+
+class Oracle(_RenderLib):
+    """The from-scratch CPU restatement (oracle/libpt_oracle.so)."""
+
+    def __init__(self):
+        super().__init__(os.path.join(ORACLE_DIR, "libpt_oracle.so"), "oracle_")
+        self.lib.oracle_wang_hash.restype = C.c_uint
+
+    def wang_hash(self, a):
+        return self.lib.oracle_wang_hash(C.c_uint(a & 0xFFFFFFFF))
+
+    def uniforms(self, seed, n):
+        out = np.zeros(n, np.float32)
+        self.lib.oracle_uniforms(C.c_uint32(seed), C.c_uint(n), _f32p(out))
+        return out
