@@ -1,0 +1,343 @@
+// TEST / BASELINE INFRASTRUCTURE (oracle/_ref recipe) -- not product code.
+//
+// GPU baseline "G0": the REFERENCE's own kernel (cuda_opengl/src/shaders/raytrace.cu
+// and the .cuh headers it inlines) built for sm_100a.  gen/raytrace_gpu.cu is
+// produced by oracle/build_ref.py with the mechanical CUDA-12 patch (texture
+// object for the removed texture reference, linear RGBA8 store for the removed
+// surface reference, runtime static_samples, zero-initialised IntersectionData);
+// this file only adds the headless plumbing GPUProcessor used to provide
+// (cuda_opengl/src/gpu_processor.cpp:68-238): the device pointer tree, the cubemap
+// array, and entry points with the flat C-ABI scene description.
+#include "raytrace_gpu.cu" // generated into oracle/_ref/gen/
+
+#include <cstdio>
+#include <vector>
+
+#include "ptcore.h"
+
+namespace {
+
+struct RefGpu
+{
+  scene::Scenes scenes;
+  std::vector<void*> allocs;
+  cudaArray_t cube_array = nullptr;
+  cudaTextureObject_t cube_tex = 0;
+  uint32_t n_faces = 0, n_lights = 0;
+  scene::SceneData h_sd;
+};
+
+#define CK(x)                                                                                  \
+  do {                                                                                         \
+    cudaError_t e_ = (x);                                                                      \
+    if (e_ != cudaSuccess) {                                                                   \
+      fprintf(stderr, "ref_gpu: %s -> %s\n", #x, cudaGetErrorString(e_));                      \
+      return (int)e_;                                                                          \
+    }                                                                                          \
+  } while (0)
+
+template <typename T>
+int
+upload(RefGpu* g, const T* host, size_t n, T** dev)
+{
+  *dev = nullptr;
+  if (!n)
+    return 0;
+  CK(cudaMalloc(dev, n * sizeof(T)));
+  g->allocs.push_back(*dev);
+  CK(cudaMemcpy(*dev, host, n * sizeof(T), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+// Brute-force closest hit around the reference's own device intersectTriangle /
+// intersectSphere with the acceptance rules of intersect() (intersection.cuh:179-212);
+// intersect() does not report which face won, so the loop is repeated to get ids.
+__global__ void
+ref_hits_kernel(const scene::SceneData* sd, uint32_t n_faces, const float3* origins,
+                const float3* dirs, uint64_t n, int32_t* ids, float* ts)
+{
+  uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+  if (k >= n)
+    return;
+  scene::Ray r;
+  r.origin = origins[k];
+  r.dir = dirs[k];
+  float dist = 100000.0f, inter_dist = 100000.0f;
+  int32_t id = -1, gi = 0;
+  float3 nrm;
+  float2 uv;
+  for (size_t m = 0; m < sd->meshes.size; ++m) {
+    const auto& mesh = sd->meshes.data[m];
+    for (size_t i = 0; i < mesh.faces.size; ++i, ++gi)
+      if (intersectTriangle(mesh.faces.data[i], nrm, uv, r, inter_dist) && inter_dist < dist &&
+          inter_dist > 0.0) {
+        dist = inter_dist;
+        id = gi;
+      }
+  }
+  for (unsigned l = 0; l < sd->lights.size; ++l)
+    if (intersectSphere(r, sd->lights.data[l], inter_dist) && inter_dist < dist &&
+        inter_dist >= 0.0) {
+      dist = inter_dist;
+      id = (int32_t)(n_faces + l);
+    }
+  if (ids)
+    ids[k] = id;
+  if (ts)
+    ts[k] = dist;
+}
+
+// Primary rays exactly as `kernel` generates them (raytrace.cu:218-240).
+__global__ void
+ref_primary_kernel(unsigned width, unsigned height, scene::Camera cam, unsigned hash_seed,
+                   float3* origins, float3* dirs)
+{
+  const int x = blockDim.x * blockIdx.x + threadIdx.x;
+  const int y = blockDim.y * blockIdx.y + threadIdx.y;
+  if (x >= width || y >= height)
+    return;
+  const unsigned int tid = (blockIdx.x + blockIdx.y * gridDim.x) * (blockDim.x * blockDim.y) +
+                           (threadIdx.y * blockDim.x) + threadIdx.x;
+  curandState rand_state;
+  curand_init(hash_seed + tid, 0, 0, &rand_state);
+  scene::Ray r = generateRay(x, y, width / 2, height / 2, cam);
+  camera_dof(r, cam, &rand_state);
+  origins[(size_t)y * width + x] = r.origin;
+  dirs[(size_t)y * width + x] = r.dir;
+}
+
+__global__ void
+ref_rng_kernel(const uint32_t* seeds, uint32_t n_seeds, uint32_t n_draws, float* out)
+{
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_seeds)
+    return;
+  curandState st;
+  curand_init(seeds[i], 0, 0, &st);
+  for (uint32_t k = 0; k < n_draws; ++k)
+    out[(size_t)i * n_draws + k] = curand_uniform(&st);
+}
+
+} // namespace
+
+extern "C" {
+
+int
+ref_gpu_create(const ptc_scene_desc* d, const float* cube_faces, unsigned cube_size, void** out)
+{
+  RefGpu* g = new RefGpu();
+  *out = g;
+  // Scenes -> SceneData*[] -> Mesh[] -> Face[]   (scene.cpp:202-283, 370-391)
+  std::vector<scene::Mesh> meshes(d->n_meshes);
+  size_t off = 0;
+  for (uint32_t m = 0; m < d->n_meshes; ++m) {
+    meshes[m].faces.size = d->mesh_face_counts[m];
+    int rc = upload(g, (const scene::Face*)d->faces + off, d->mesh_face_counts[m],
+                    &meshes[m].faces.data);
+    if (rc)
+      return rc;
+    off += d->mesh_face_counts[m];
+  }
+  g->n_faces = (uint32_t)off;
+  g->n_lights = d->n_lights;
+  scene::SceneData& sd = g->h_sd;
+  sd.meshes.size = d->n_meshes;
+  sd.materials.size = d->n_materials;
+  sd.lights.size = d->n_lights;
+  int rc;
+  if ((rc = upload(g, meshes.data(), meshes.size(), &sd.meshes.data)))
+    return rc;
+  if ((rc = upload(g, (const scene::Material*)d->materials, d->n_materials, &sd.materials.data)))
+    return rc;
+  if ((rc = upload(g, (const scene::LightProp*)d->lights, d->n_lights, &sd.lights.data)))
+    return rc;
+  scene::SceneData* d_sd;
+  if ((rc = upload(g, &sd, 1, &d_sd)))
+    return rc;
+  if ((rc = upload(g, &d_sd, 1, &g->scenes.scenes))) // gpu_processor.cpp:184-203
+    return rc;
+  // textures (gpu_processor.cpp:205-238)
+  std::vector<scene::Texture> tex(d->n_textures);
+  for (uint32_t i = 0; i < d->n_textures; ++i) {
+    tex[i].w = d->textures[i].w;
+    tex[i].h = d->textures[i].h;
+    tex[i].nb_chan = d->textures[i].nb_chan;
+    size_t n = (size_t)tex[i].w * tex[i].h * tex[i].nb_chan;
+    if ((rc = upload(g, d->textures[i].data, n, &tex[i].data)))
+      return rc;
+  }
+  g->scenes.textures.size = d->n_textures;
+  if ((rc = upload(g, tex.data(), tex.size(), &g->scenes.textures.data)))
+    return rc;
+  // cubemap (gpu_processor.cpp:134-152) + the texture state raytrace() used to set
+  // on the texture reference (raytrace.cu:304-309)
+  cudaChannelFormatDesc desc = cudaCreateChannelDesc(32, 32, 32, 32, cudaChannelFormatKindFloat);
+  CK(cudaMalloc3DArray(&g->cube_array, &desc, make_cudaExtent(cube_size, cube_size, 6),
+                       cudaArrayCubemap));
+  cudaMemcpy3DParms p;
+  memset(&p, 0, sizeof(p));
+  p.srcPtr = make_cudaPitchedPtr((void*)cube_faces, cube_size * sizeof(float) * 4, cube_size,
+                                 cube_size);
+  p.dstArray = g->cube_array;
+  p.extent = make_cudaExtent(cube_size, cube_size, 6);
+  p.kind = cudaMemcpyHostToDevice;
+  CK(cudaMemcpy3D(&p));
+  cudaResourceDesc res;
+  memset(&res, 0, sizeof(res));
+  res.resType = cudaResourceTypeArray;
+  res.res.array.array = g->cube_array;
+  cudaTextureDesc td;
+  memset(&td, 0, sizeof(td));
+  td.addressMode[0] = cudaAddressModeWrap;
+  td.addressMode[1] = cudaAddressModeWrap;
+  td.filterMode = cudaFilterModeLinear;
+  td.normalizedCoords = 1;
+  td.readMode = cudaReadModeElementType;
+  CK(cudaCreateTextureObject(&g->cube_tex, &res, &td, nullptr));
+  CK(cudaMemcpyToSymbol(cubemap_ref, &g->cube_tex, sizeof(g->cube_tex)));
+  setupFunctionTables();
+  return 0;
+}
+
+void
+ref_gpu_destroy(void* h)
+{
+  RefGpu* g = (RefGpu*)h;
+  if (!g)
+    return;
+  if (g->cube_tex)
+    cudaDestroyTextureObject(g->cube_tex);
+  if (g->cube_array)
+    cudaFreeArray(g->cube_array);
+  for (void* p : g->allocs)
+    cudaFree(p);
+  delete g;
+}
+
+static int
+set_launch_state(unsigned* d_out, unsigned bounces)
+{
+  int static_samples = (int)bounces - 2; // max_bounces = 1 + (static_samples + 1)
+  CK(cudaMemcpyToSymbol(ref_out_rgba, &d_out, sizeof(d_out)));
+  CK(cudaMemcpyToSymbol(g_ref_static_samples, &static_samples, sizeof(int)));
+  return 0;
+}
+
+// The reference's public entry point raytrace() (raytrace.cu:287-325), including its
+// function-static frame counter.  d_accum / d_out are device pointers.
+int
+ref_gpu_raytrace(void* h, const ptc_camera* camera, unsigned width, unsigned height,
+                 unsigned bounces, int moved, unsigned post_id, float* d_accum, unsigned* d_out,
+                 void* stream)
+{
+  RefGpu* g = (RefGpu*)h;
+  int rc = set_launch_state(d_out, bounces);
+  if (rc)
+    return rc;
+  std::vector<scene::Cubemap> cubemaps(1);
+  cubemaps[0].cubemap = g->cube_array;
+  scene::Camera cam;
+  memcpy(&cam, camera, sizeof(cam));
+  raytrace(nullptr, g->scenes, 0, cubemaps, 0, &cam, width, height, (cudaStream_t)stream,
+           (float3*)d_accum, moved != 0, post_id);
+  return (int)cudaGetLastError();
+}
+
+// Same launch as raytrace.cu:315-322 but for an explicit sample number, so tests
+// can compare frame k without replaying frames 1..k-1.
+int
+ref_gpu_kernel(void* h, const ptc_camera* camera, unsigned width, unsigned height,
+               unsigned frame_nb, unsigned bounces, int moved, unsigned post_id, float* d_accum,
+               unsigned* d_out, void* stream)
+{
+  RefGpu* g = (RefGpu*)h;
+  int rc = set_launch_state(d_out, bounces);
+  if (rc)
+    return rc;
+  scene::Camera cam;
+  memcpy(&cam, camera, sizeof(cam));
+  dim3 threads_per_block(16, 16);
+  dim3 nb_blocks(width / threads_per_block.x + 1, height / threads_per_block.y + 1);
+  kernel<<<nb_blocks, threads_per_block, 0, (cudaStream_t)stream>>>(
+    width, height, g->scenes, 0, cam, WangHash(frame_nb), (int)frame_nb, (float3*)d_accum,
+    moved != 0, h_post_process_table[post_id]);
+  return (int)cudaGetLastError();
+}
+
+// Host-buffer conveniences for the parity tests.
+int
+ref_gpu_primary(void* h, const ptc_camera* camera, unsigned width, unsigned height,
+                unsigned frame_nb, float* origins, float* dirs, int32_t* ids, float* ts)
+{
+  RefGpu* g = (RefGpu*)h;
+  size_t n = (size_t)width * height;
+  float3 *d_o, *d_d;
+  int32_t* d_i;
+  float* d_t;
+  CK(cudaMalloc(&d_o, n * 12));
+  CK(cudaMalloc(&d_d, n * 12));
+  CK(cudaMalloc(&d_i, n * 4));
+  CK(cudaMalloc(&d_t, n * 4));
+  scene::Camera cam;
+  memcpy(&cam, camera, sizeof(cam));
+  dim3 tpb(16, 16), nb(width / 16 + 1, height / 16 + 1);
+  ref_primary_kernel<<<nb, tpb>>>(width, height, cam, WangHash(frame_nb), d_o, d_d);
+  scene::SceneData* d_sd;
+  CK(cudaMemcpy(&d_sd, g->scenes.scenes, sizeof(d_sd), cudaMemcpyDeviceToHost));
+  ref_hits_kernel<<<(unsigned)((n + 127) / 128), 128>>>(d_sd, g->n_faces, d_o, d_d, n, d_i, d_t);
+  CK(cudaDeviceSynchronize());
+  if (origins)
+    CK(cudaMemcpy(origins, d_o, n * 12, cudaMemcpyDeviceToHost));
+  if (dirs)
+    CK(cudaMemcpy(dirs, d_d, n * 12, cudaMemcpyDeviceToHost));
+  if (ids)
+    CK(cudaMemcpy(ids, d_i, n * 4, cudaMemcpyDeviceToHost));
+  if (ts)
+    CK(cudaMemcpy(ts, d_t, n * 4, cudaMemcpyDeviceToHost));
+  cudaFree(d_o), cudaFree(d_d), cudaFree(d_i), cudaFree(d_t);
+  return 0;
+}
+
+int
+ref_gpu_intersect(void* h, const float* origins, const float* dirs, uint64_t n, int32_t* ids,
+                  float* ts)
+{
+  RefGpu* g = (RefGpu*)h;
+  float3 *d_o, *d_d;
+  int32_t* d_i;
+  float* d_t;
+  CK(cudaMalloc(&d_o, n * 12));
+  CK(cudaMalloc(&d_d, n * 12));
+  CK(cudaMalloc(&d_i, n * 4));
+  CK(cudaMalloc(&d_t, n * 4));
+  CK(cudaMemcpy(d_o, origins, n * 12, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d_d, dirs, n * 12, cudaMemcpyHostToDevice));
+  scene::SceneData* d_sd;
+  CK(cudaMemcpy(&d_sd, g->scenes.scenes, sizeof(d_sd), cudaMemcpyDeviceToHost));
+  ref_hits_kernel<<<(unsigned)((n + 127) / 128), 128>>>(d_sd, g->n_faces, d_o, d_d, n, d_i, d_t);
+  CK(cudaDeviceSynchronize());
+  if (ids)
+    CK(cudaMemcpy(ids, d_i, n * 4, cudaMemcpyDeviceToHost));
+  if (ts)
+    CK(cudaMemcpy(ts, d_t, n * 4, cudaMemcpyDeviceToHost));
+  cudaFree(d_o), cudaFree(d_d), cudaFree(d_i), cudaFree(d_t);
+  return 0;
+}
+
+// cuRAND XORWOW known answers from the device (raytrace.cu:234-235 call pattern).
+int
+ref_gpu_rng(const uint32_t* seeds, uint32_t n_seeds, uint32_t n_draws, float* out)
+{
+  uint32_t* d_s;
+  float* d_o;
+  CK(cudaMalloc(&d_s, n_seeds * 4));
+  CK(cudaMalloc(&d_o, (size_t)n_seeds * n_draws * 4));
+  CK(cudaMemcpy(d_s, seeds, n_seeds * 4, cudaMemcpyHostToDevice));
+  ref_rng_kernel<<<(n_seeds + 63) / 64, 64>>>(d_s, n_seeds, n_draws, d_o);
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpy(out, d_o, (size_t)n_seeds * n_draws * 4, cudaMemcpyDeviceToHost));
+  cudaFree(d_s), cudaFree(d_o);
+  return 0;
+}
+
+} // extern "C"
