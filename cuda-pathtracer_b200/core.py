@@ -1,0 +1,241 @@
+"""ctypes binding of the C ABI (include/ptcore.h) -- plumbing, not the product.
+
+``Core`` mirrors the reference's call surface for the hot path: upload once
+(``Scene::upload`` + ``uploadTextures``/``uploadCubemaps``, scene.cpp:304-391,
+gpu_processor.cpp:163-238), then one ``render`` per frame
+(``raytrace(...)``, raytrace.h:9-15).  The library is loaded from the in-tree
+``libptcore.so``; a missing library or a machine without a CUDA device raises --
+there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import ptscene
+from .ptscene import PtcCamera, PtcSceneDesc
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libptcore.so")
+
+PTC_ERR_NO_DEVICE = -2
+
+
+class PtcRenderArgs(C.Structure):
+    _fields_ = [("scene_id", C.c_int32), ("cubemap_id", C.c_int32),
+                ("camera", C.POINTER(PtcCamera)),
+                ("width", C.c_uint32), ("height", C.c_uint32),
+                ("row_begin", C.c_uint32), ("row_end", C.c_uint32),
+                ("bounces", C.c_uint32), ("moved", C.c_uint32),
+                ("post_id", C.c_uint32), ("frame_nb", C.c_uint32),
+                ("accum", C.c_void_p), ("out_rgba", C.c_void_p),
+                ("radiance_out", C.c_void_p), ("stream", C.c_void_p)]
+
+
+class PtcCounters(C.Structure):
+    _fields_ = [("paths", C.c_uint64), ("segments", C.c_uint64), ("traced", C.c_uint64),
+                ("rays_per_bounce", C.c_uint64 * 16),
+                ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64)]
+
+
+class PtcSceneInfo(C.Structure):
+    _fields_ = [("n_faces", C.c_uint32), ("n_lights", C.c_uint32),
+                ("n_materials", C.c_uint32), ("n_textures", C.c_uint32),
+                ("bvh_nodes", C.c_uint32), ("bvh_node_bytes", C.c_uint32),
+                ("tri_bytes", C.c_uint32), ("shade_bytes", C.c_uint32),
+                ("texture_bytes", C.c_uint64), ("smem_resident", C.c_uint32)]
+
+
+class PtcHostBvh(C.Structure):
+    _fields_ = [("nodes", C.c_void_p), ("n_nodes", C.c_uint32), ("node_bytes", C.c_uint32),
+                ("tris", C.c_void_p), ("n_tris", C.c_uint32), ("tri_bytes", C.c_uint32),
+                ("tri_face_ids", C.c_void_p), ("sah_cost", C.c_float),
+                ("max_depth", C.c_uint32), ("_owner", C.c_void_p)]
+
+
+EXPORTS = ["ptc_abi_version", "ptc_create", "ptc_destroy", "ptc_last_error", "ptc_upload_scene",
+           "ptc_scene_info_get", "ptc_set_cubemap", "ptc_render", "ptc_render_host",
+           "ptc_reset_accumulation", "ptc_counters_get", "ptc_counters_reset",
+           "ptc_trace_primary", "ptc_intersect_rays", "ptc_debug_rng", "ptc_host_bvh_build",
+           "ptc_host_bvh_free"]
+
+_lib = None
+
+
+class PtcError(RuntimeError):
+    pass
+
+
+def load_library() -> C.CDLL:
+    """Loads libptcore.so; raises (loudly) when the CUDA extension was not built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise PtcError(f"{LIB_PATH} is missing: run `python __graft_entry__.py` (build()) first; "
+                           "this package has no CPU fallback")
+        lib = C.CDLL(LIB_PATH)
+        lib.ptc_last_error.restype = C.c_char_p
+        lib.ptc_last_error.argtypes = [C.c_void_p]
+        lib.ptc_destroy.restype = None
+        lib.ptc_destroy.argtypes = [C.c_void_p]
+        lib.ptc_host_bvh_free.restype = None
+        for name in ["ptc_upload_scene", "ptc_scene_info_get", "ptc_set_cubemap", "ptc_render",
+                     "ptc_render_host", "ptc_reset_accumulation", "ptc_counters_get",
+                     "ptc_counters_reset", "ptc_trace_primary", "ptc_intersect_rays", "ptc_debug_rng"]:
+            getattr(lib, name).restype = C.c_int
+        _lib = lib
+    return _lib
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return C.c_void_p(a.ctypes.data)
+    if hasattr(a, "data_ptr"):  # torch tensor
+        return C.c_void_p(a.data_ptr())
+    return C.c_void_p(int(a))
+
+
+def host_bvh(scene: ptscene.SceneBlob) -> dict:
+    """Host-only: builds the wide BVH and returns copies of its arrays (no GPU needed)."""
+    lib = load_library()
+    desc = scene.to_desc()
+    hb = PtcHostBvh()
+    rc = lib.ptc_host_bvh_build(C.byref(desc), C.byref(hb))
+    if rc:
+        raise PtcError(f"ptc_host_bvh_build failed: {rc}")
+    try:
+        nodes = np.ctypeslib.as_array((C.c_uint8 * (hb.n_nodes * hb.node_bytes)).from_address(hb.nodes)).copy()
+        n_t = hb.n_tris * hb.tri_bytes
+        tris = (np.ctypeslib.as_array((C.c_uint8 * n_t).from_address(hb.tris)).copy()
+                if n_t else np.zeros(0, np.uint8))
+        ids = (np.ctypeslib.as_array((C.c_uint32 * hb.n_tris).from_address(hb.tri_face_ids)).copy()
+               if hb.n_tris else np.zeros(0, np.uint32))
+        return {"nodes": nodes.reshape(hb.n_nodes, hb.node_bytes),
+                "tris": tris.reshape(hb.n_tris, hb.tri_bytes) if hb.n_tris else tris.reshape(0, 48),
+                "face_ids": ids, "sah_cost": float(hb.sah_cost), "max_depth": int(hb.max_depth)}
+    finally:
+        lib.ptc_host_bvh_free(C.byref(hb))
+
+
+class Core:
+    """One context per GPU (gpu_processor.h:20-98 holds the same state in GPUProcessor)."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        self.ctx = C.c_void_p()
+        rc = self.lib.ptc_create(C.c_int(device), C.byref(self.ctx))
+        if rc == PTC_ERR_NO_DEVICE:
+            raise PtcError("no usable CUDA device: the path-tracing core has no CPU fallback")
+        if rc:
+            raise PtcError(f"ptc_create failed: {rc}")
+        self.device = device
+        self._keep = []
+
+    def close(self):
+        if self.ctx:
+            self.lib.ptc_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc:
+            msg = self.lib.ptc_last_error(self.ctx)
+            raise PtcError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+
+    # -- upload ----------------------------------------------------------------
+    def upload_scene(self, scene: ptscene.SceneBlob) -> int:
+        desc = scene.to_desc()
+        sid = C.c_int32(-1)
+        self._check(self.lib.ptc_upload_scene(self.ctx, C.byref(desc), C.byref(sid)), "ptc_upload_scene")
+        return sid.value
+
+    def set_cubemap(self, faces: np.ndarray) -> int:
+        faces = np.ascontiguousarray(faces, dtype=np.float32)
+        assert faces.ndim == 4 and faces.shape[0] == 6 and faces.shape[3] == 4
+        cid = C.c_int32(-1)
+        self._check(self.lib.ptc_set_cubemap(self.ctx, _ptr(faces), C.c_uint32(faces.shape[1]),
+                                             C.byref(cid)), "ptc_set_cubemap")
+        return cid.value
+
+    def scene_info(self, scene_id: int) -> PtcSceneInfo:
+        info = PtcSceneInfo()
+        self._check(self.lib.ptc_scene_info_get(self.ctx, C.c_int32(scene_id), C.byref(info)),
+                    "ptc_scene_info_get")
+        return info
+
+    # -- render ----------------------------------------------------------------
+    def _args(self, scene_id, cubemap_id, camera, width, height, accum, out_rgba=None,
+              radiance_out=None, bounces=3, moved=False, post_id=0, frame_nb=0, rows=None,
+              stream=0):
+        cam = camera if isinstance(camera, PtcCamera) else camera.camera_struct()
+        self._keep = [cam]
+        a = PtcRenderArgs()
+        a.scene_id, a.cubemap_id = scene_id, cubemap_id
+        a.camera = C.pointer(cam)
+        a.width, a.height = width, height
+        a.row_begin, a.row_end = rows if rows else (0, 0)
+        a.bounces, a.moved, a.post_id, a.frame_nb = bounces, int(bool(moved)), post_id, frame_nb
+        a.accum = _ptr(accum)
+        a.out_rgba = _ptr(out_rgba)
+        a.radiance_out = _ptr(radiance_out)
+        a.stream = C.c_void_p(int(stream)) if stream else None
+        return a
+
+    def render(self, *args, **kw):
+        """Device-pointer render call (accum / out_rgba / radiance_out are device buffers)."""
+        a = self._args(*args, **kw)
+        self._check(self.lib.ptc_render(self.ctx, C.byref(a)), "ptc_render")
+
+    def render_host(self, *args, upload_accum=False, download_accum=False, **kw):
+        """Host-buffer render call: copies in/out and synchronises."""
+        a = self._args(*args, **kw)
+        self._check(self.lib.ptc_render_host(self.ctx, C.byref(a), C.c_int(int(upload_accum)),
+                                             C.c_int(int(download_accum))), "ptc_render_host")
+
+    def reset_accumulation(self):
+        self._check(self.lib.ptc_reset_accumulation(self.ctx), "ptc_reset_accumulation")
+
+    def counters(self) -> PtcCounters:
+        c = PtcCounters()
+        self._check(self.lib.ptc_counters_get(self.ctx, C.byref(c)), "ptc_counters_get")
+        return c
+
+    def reset_counters(self):
+        self._check(self.lib.ptc_counters_reset(self.ctx), "ptc_counters_reset")
+
+    # -- parity entry points -----------------------------------------------------
+    def trace_primary(self, scene_id, camera, width, height, frame_nb=1):
+        cam = camera if isinstance(camera, PtcCamera) else camera.camera_struct()
+        ids = np.zeros((height, width), np.int32)
+        t = np.zeros((height, width), np.float32)
+        self._check(self.lib.ptc_trace_primary(self.ctx, C.c_int32(scene_id), C.byref(cam),
+                                               C.c_uint32(width), C.c_uint32(height),
+                                               C.c_uint32(frame_nb), _ptr(ids), _ptr(t)),
+                    "ptc_trace_primary")
+        return ids, t
+
+    def intersect_rays(self, scene_id, origins, dirs):
+        o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+        ids = np.zeros(o.shape[0], np.int32)
+        t = np.zeros(o.shape[0], np.float32)
+        self._check(self.lib.ptc_intersect_rays(self.ctx, C.c_int32(scene_id), _ptr(o), _ptr(d),
+                                                C.c_uint64(o.shape[0]), _ptr(ids), _ptr(t)),
+                    "ptc_intersect_rays")
+        return ids, t
+
+    def debug_rng(self, seeds, n_draws, reference_impl=False):
+        s = np.ascontiguousarray(seeds, np.uint32)
+        out = np.zeros((s.size, n_draws), np.float32)
+        self._check(self.lib.ptc_debug_rng(self.ctx, _ptr(s), C.c_uint32(s.size), C.c_uint32(n_draws),
+                                           C.c_int(int(reference_impl)), _ptr(out)), "ptc_debug_rng")
+        return out

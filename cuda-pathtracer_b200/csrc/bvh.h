@@ -1,0 +1,85 @@
+// bvh.h -- host/device-shared layouts of the acceleration structure and the
+// per-triangle records, plus the host builder's interface.
+//
+// The reference has no acceleration structure: intersect() loops over every face
+// (cuda_opengl/include/shaders/intersection.cuh:179-196).  What this structure must
+// reproduce is the reference's ANSWER: the closest front-facing hit, first face
+// index winning ties (intersection.cuh:110,183-184).
+#pragma once
+
+#include <stdint.h>
+
+#include <vector>
+
+#include "ptcore.h"
+
+namespace ptc {
+
+// 8-wide compressed node, 80 bytes, 16-byte aligned (5 x 128-bit loads).
+// Child boxes are quantised to 8 bits per plane relative to the node origin:
+//   lo_a = origin_a + qlo_a[i] * 2^(e_a - 127 ... as float bits e_a << 23)
+// Quantisation rounds outwards, so decoded boxes contain the true ones.
+//
+// meta[i]:  0                      empty slot
+//           0b001'11sss (>= 0x38)  internal child; sss = slot i; bit position 24+i
+//                                  in the hit mask (before octant reordering)
+//           0bccc'ooooo            leaf: ooooo = first triangle offset (0..23) from
+//                                  tri_base, ccc = unary count (001, 011, 111)
+struct alignas(16) Node8
+{
+  float origin[3];
+  uint8_t e[3];
+  uint8_t imask;       // bit i: slot i holds an internal child
+  uint32_t child_base; // node index of the first internal child (children contiguous)
+  uint32_t tri_base;   // index of this node's first triangle record
+  uint8_t meta[8];
+  uint8_t qlo[3][8];
+  uint8_t qhi[3][8];
+};
+static_assert(sizeof(Node8) == 80, "Node8 must be 80 bytes");
+
+// Intersection record, 48 bytes (3 x 128-bit loads).  Edges are precomputed with the
+// same single fp32 subtraction the reference performs per ray
+// (intersection.cuh:106-107), so Moeller-Trumbore sees identical operands.
+struct alignas(16) TriRecord
+{
+  float v0[3];
+  float e1[3]; // v1 - v0
+  float e2[3]; // v2 - v0
+  uint32_t face_id; // global face index (mesh order) -- the tie-break key
+  uint32_t _pad[2];
+};
+static_assert(sizeof(TriRecord) == 48, "TriRecord must be 48 bytes");
+
+// Shading record, 80 bytes, indexed by global face id (5 x 128-bit loads).
+struct alignas(16) ShadeRecord
+{
+  float n[3][3];  // vertex normals
+  float uv[3][2]; // vertex texcoords
+  float tangent[3];
+  uint32_t material_id;
+};
+static_assert(sizeof(ShadeRecord) == 80, "ShadeRecord must be 80 bytes");
+
+struct BuildStats
+{
+  float sah_cost = 0.f;
+  uint32_t max_depth = 0;
+  uint32_t n_leaves = 0;
+};
+
+struct HostBvh
+{
+  std::vector<Node8> nodes;       // nodes[0] is the root
+  std::vector<TriRecord> tris;    // leaf order
+  std::vector<uint32_t> face_ids; // leaf order -> global face id
+  BuildStats stats;
+};
+
+// Builds the wide BVH for all faces of `desc` (host, single call, deterministic).
+void build_bvh(const ptc_scene_desc* desc, HostBvh& out);
+
+// Shading records in global face order.
+void build_shade_records(const ptc_scene_desc* desc, std::vector<ShadeRecord>& out);
+
+} // namespace ptc

@@ -745,6 +745,184 @@ oracle_primary_rays(const ptc_camera* camera, unsigned width, unsigned height, u
   return 0;
 }
 
+// ---------------------------------------------------------------------------
+// O2: closest hit through the PRODUCT's wide BVH (nodes/triangle records built by
+// ptc_host_bvh_build and passed in by the test harness), traversed here by
+// independent scalar code in the same near-to-far slot order as the device kernel,
+// so the node / triangle visit counts are the algorithmic traffic the roofline uses.
+// The triangle arithmetic is the oracle's own (unfused) Moeller-Trumbore.
+// ---------------------------------------------------------------------------
+namespace {
+
+struct O2Node // mirrors the 80-byte layout documented in cuda-pathtracer_b200/csrc/bvh.h
+{
+  float origin[3];
+  uint8_t e[3];
+  uint8_t imask;
+  uint32_t child_base;
+  uint32_t tri_base;
+  uint8_t meta[8];
+  uint8_t qlo[3][8];
+  uint8_t qhi[3][8];
+};
+static_assert(sizeof(O2Node) == 80, "node layout");
+
+struct O2Tri
+{
+  float v0[3], e1[3], e2[3];
+  uint32_t face_id;
+  uint32_t pad[2];
+};
+static_assert(sizeof(O2Tri) == 48, "tri layout");
+
+inline bool
+o2_tri(const O2Tri& T, const Ray& ray, float& t)
+{
+  V3 v0 = v3(T.v0), v0v1 = v3(T.e1), v0v2 = v3(T.e2);
+  V3 p_vec = cross(ray.dir, v0v2);
+  float det = dot(v0v1, p_vec);
+  if ((double)det < 0.0000001)
+    return false;
+  float inv_det = 1.f / det;
+  V3 t_vec = ray.origin - v0;
+  float u = dot(t_vec, p_vec) * inv_det;
+  if (u < 0 || u > 1)
+    return false;
+  V3 qvec = cross(t_vec, v0v1);
+  float v = dot(ray.dir, qvec) * inv_det;
+  if (v < 0 || u + v > 1)
+    return false;
+  t = dot(v0v2, qvec) * inv_det;
+  return true;
+}
+
+inline void
+o2_closest(const O2Node* nodes, const O2Tri* tris, const ptc_scene_desc* desc, uint32_t n_faces,
+           const Ray& r, int32_t& best_id, float& best_t, uint64_t& n_nodes, uint64_t& n_tris)
+{
+  best_t = 100000.0f;
+  best_id = -1;
+  const float eps = 1e-20f;
+  float idir[3], o[3] = { r.origin.x, r.origin.y, r.origin.z }, d[3] = { r.dir.x, r.dir.y, r.dir.z };
+  uint32_t oct = 0;
+  for (int a = 0; a < 3; ++a) {
+    idir[a] = 1.0f / (fabsf(d[a]) > eps ? d[a] : copysignf(eps, d[a]));
+    if (d[a] < 0.f)
+      oct |= 1u << a;
+  }
+  const uint32_t oct_inv = 7u - oct;
+  struct Entry
+  {
+    uint32_t base, mask;
+  };
+  Entry stack[64];
+  int sp = 0;
+  Entry ng = { 0u, 0x80000000u }, tg = { 0u, 0u };
+  for (;;) {
+    if (ng.mask & 0xFF000000u) {
+      uint32_t bit = 31u - (uint32_t)__builtin_clz(ng.mask);
+      ng.mask &= ~(1u << bit);
+      uint32_t imask = ng.mask & 0xFFu;
+      if (ng.mask & 0xFF000000u)
+        stack[sp++] = ng;
+      uint32_t slot = (bit - 24u) ^ oct_inv;
+      uint32_t rel = (uint32_t)__builtin_popcount(imask & ~(0xFFFFFFFFu << slot));
+      const O2Node& n = nodes[ng.base + rel];
+      n_nodes++;
+      uint32_t hitmask = 0;
+      for (int i = 0; i < 8; ++i) {
+        float tmin = 0.0f, tmax = best_t;
+        for (int a = 0; a < 3; ++a) {
+          uint32_t bits = (uint32_t)n.e[a] << 23;
+          float sc;
+          std::memcpy(&sc, &bits, 4);
+          float lo = n.origin[a] + (float)n.qlo[a][i] * sc, hi = n.origin[a] + (float)n.qhi[a][i] * sc;
+          float t0 = (lo - o[a]) * idir[a], t1 = (hi - o[a]) * idir[a];
+          if (t0 > t1)
+            std::swap(t0, t1);
+          // widen by a few ulp: this checker only has to be conservative
+          t0 -= fabsf(t0) * 1e-6f;
+          t1 += fabsf(t1) * 1e-6f;
+          tmin = fmaxf(tmin, t0);
+          tmax = fminf(tmax, t1);
+        }
+        if (tmin <= tmax) {
+          uint32_t m = n.meta[i];
+          uint32_t inner = ((m & 0x18u) == 0x18u) ? oct_inv : 0u;
+          hitmask |= (m >> 5) << ((m & 31u) ^ inner);
+        }
+      }
+      ng.base = n.child_base;
+      ng.mask = (hitmask & 0xFF000000u) | n.imask;
+      tg.base = n.tri_base;
+      tg.mask = hitmask & 0x00FFFFFFu;
+    } else {
+      tg = ng;
+      ng = Entry{ 0u, 0u };
+    }
+    while (tg.mask) {
+      uint32_t bit = (uint32_t)__builtin_ctz(tg.mask);
+      tg.mask &= tg.mask - 1u;
+      const O2Tri& T = tris[tg.base + bit];
+      n_tris++;
+      float t;
+      if (o2_tri(T, r, t) && t > 0.0 &&
+          (t < best_t || (t == best_t && (int32_t)T.face_id < best_id))) {
+        best_t = t;
+        best_id = (int32_t)T.face_id;
+      }
+    }
+    if (!(ng.mask & 0xFF000000u)) {
+      if (sp == 0)
+        break;
+      ng = stack[--sp];
+    }
+  }
+  for (uint32_t l = 0; l < desc->n_lights; ++l) {
+    float t;
+    if (intersect_sphere_ref(r, desc->lights[l], t) && t < best_t && t >= 0.0) {
+      best_t = t;
+      best_id = (int32_t)(n_faces + l);
+    }
+  }
+}
+
+} // namespace
+
+int
+oracle_intersect_bvh(const ptc_scene_desc* desc, const void* nodes, const void* tris,
+                     const float* origins, const float* dirs, uint64_t n, int32_t* hit_ids,
+                     float* t_out, uint64_t* nodes_visited, uint64_t* tris_tested, int n_threads)
+{
+  SceneView sc(desc, nullptr, 0);
+  const unsigned chunk = 4096;
+  const unsigned n_chunks = (unsigned)((n + chunk - 1) / chunk);
+  std::vector<uint64_t> nn(n_chunks, 0), nt(n_chunks, 0);
+  parallel_for(n_chunks, n_threads, [&](unsigned c) {
+    uint64_t lo = (uint64_t)c * chunk, hi = lo + chunk < n ? lo + chunk : n;
+    for (uint64_t k = lo; k < hi; ++k) {
+      Ray r;
+      r.origin = v3(origins + 3 * k);
+      r.dir = v3(dirs + 3 * k);
+      int32_t id;
+      float t;
+      o2_closest((const O2Node*)nodes, (const O2Tri*)tris, desc, sc.n_faces, r, id, t, nn[c], nt[c]);
+      if (hit_ids)
+        hit_ids[k] = id;
+      if (t_out)
+        t_out[k] = t;
+    }
+  });
+  uint64_t a = 0, b = 0;
+  for (unsigned c = 0; c < n_chunks; ++c)
+    a += nn[c], b += nt[c];
+  if (nodes_visited)
+    *nodes_visited = a;
+  if (tris_tested)
+    *tris_tested = b;
+  return 0;
+}
+
 void
 oracle_uniforms(uint32_t seed, unsigned n, float* out)
 {

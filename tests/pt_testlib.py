@@ -141,3 +141,75 @@ class Oracle(_RenderLib):
         out = np.zeros(n, np.float32)
         self.lib.oracle_uniforms(C.c_uint32(seed), C.c_uint(n), _f32p(out))
         return out
+
+
+class RefGpu:
+    """GPU baseline G0: the reference's own kernel patched for CUDA 12 and built for
+    sm_100a (oracle/_ref/libref_gpu.so, see oracle/build_ref.py).  Needs a GPU."""
+
+    def __init__(self, sc):
+        path = os.path.join(ORACLE_DIR, "_ref", "libref_gpu.so")
+        if not os.path.exists(path):
+            raise FileNotFoundError(path)
+        self.lib = C.CDLL(path)
+        self.sc = sc
+        self.h = C.c_void_p()
+        cube, cs = cube_of(sc)
+        desc = sc.to_desc()
+        rc = self.lib.ref_gpu_create(C.byref(desc), _f32p(cube), C.c_uint(cs), C.byref(self.h))
+        if rc:
+            raise RuntimeError(f"ref_gpu_create failed: {rc}")
+
+    def close(self):
+        if self.h:
+            self.lib.ref_gpu_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def kernel(self, w, h, frame, bounces, d_accum, d_out, moved=False, post_id=0, stream=0):
+        """Explicit-frame launch; d_accum / d_out are device pointers (ints)."""
+        cam = self.sc.camera_struct()
+        rc = self.lib.ref_gpu_kernel(self.h, C.byref(cam), C.c_uint(w), C.c_uint(h), C.c_uint(frame),
+                                     C.c_uint(bounces), C.c_int(int(moved)), C.c_uint(post_id),
+                                     C.c_void_p(d_accum), C.c_void_p(d_out), C.c_void_p(stream))
+        if rc:
+            raise RuntimeError(f"ref_gpu_kernel failed: {rc}")
+
+    def raytrace(self, w, h, bounces, d_accum, d_out, moved=False, post_id=0, stream=0):
+        """The reference's public raytrace() with its own frame counter."""
+        cam = self.sc.camera_struct()
+        rc = self.lib.ref_gpu_raytrace(self.h, C.byref(cam), C.c_uint(w), C.c_uint(h),
+                                       C.c_uint(bounces), C.c_int(int(moved)), C.c_uint(post_id),
+                                       C.c_void_p(d_accum), C.c_void_p(d_out), C.c_void_p(stream))
+        if rc:
+            raise RuntimeError(f"ref_gpu_raytrace failed: {rc}")
+
+    def primary(self, w, h, frame):
+        cam = self.sc.camera_struct()
+        o = np.zeros((h * w, 3), np.float32)
+        d = np.zeros((h * w, 3), np.float32)
+        ids = np.zeros(h * w, np.int32)
+        t = np.zeros(h * w, np.float32)
+        rc = self.lib.ref_gpu_primary(self.h, C.byref(cam), C.c_uint(w), C.c_uint(h), C.c_uint(frame),
+                                      _f32p(o), _f32p(d), _f32p(ids), _f32p(t))
+        if rc:
+            raise RuntimeError(f"ref_gpu_primary failed: {rc}")
+        return o, d, ids.reshape(h, w), t.reshape(h, w)
+
+    def intersect(self, origins, dirs):
+        o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+        ids = np.zeros(o.shape[0], np.int32)
+        t = np.zeros(o.shape[0], np.float32)
+        rc = self.lib.ref_gpu_intersect(self.h, _f32p(o), _f32p(d), C.c_uint64(o.shape[0]),
+                                        _f32p(ids), _f32p(t))
+        if rc:
+            raise RuntimeError(f"ref_gpu_intersect failed: {rc}")
+        return ids, t
+
+    def rng(self, seeds, n_draws):
+        s = np.ascontiguousarray(seeds, np.uint32)
+        out = np.zeros((s.size, n_draws), np.float32)
+        rc = self.lib.ref_gpu_rng(_f32p(s), C.c_uint32(s.size), C.c_uint32(n_draws), _f32p(out))
+        if rc:
+            raise RuntimeError(f"ref_gpu_rng failed: {rc}")
+        return out
