@@ -5,5 +5,7 @@ Python here is plumbing only (fixture reader, ctypes binding of the C ABI in
 the product is ``csrc/`` -> ``libptcore.so``.
 """
 from . import ptscene  # noqa: F401
+from . import synth  # noqa: F401
+from . import tiles  # noqa: F401
 from . import core  # noqa: F401,E402
 from .core import Core, PtcError, host_bvh, load_library  # noqa: F401,E402

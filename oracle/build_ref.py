@@ -131,8 +131,10 @@ def build_cpu():
     gen_cpu_source()
     # -ffp-contract=off: the reference arithmetic is evaluated operation by
     # operation in IEEE fp32; the from-scratch oracle is compiled the same way.
+    # -Bsymbolic: the CUDA-runtime stand-ins of cuda_host_shim.cpp must win inside this
+    # library even when a real libcudart is already loaded globally (torch does that).
     run(["g++", "-std=c++14", "-O2", "-w", "-fPIC", "-shared", "-pthread", "-ffp-contract=off",
-         "-I", GEN, *INC, "-I", os.path.join(HERE, "ref_shim"), "-include", shim,
+         "-Wl,-Bsymbolic", "-I", GEN, *INC, "-I", os.path.join(HERE, "ref_shim"), "-include", shim,
          drv, os.path.join(HERE, "ref_shim", "cuda_host_shim.cpp"), "-o", out])
     return out
 

