@@ -1,0 +1,449 @@
+#!/usr/bin/env python3
+"""bench.py -- BASELINE.json's metric on BASELINE.json's config.
+
+    python bench.py --gpus N --steps K --warmup W            # this repository's CUDA path
+    python bench.py --impl reference --gpus N --steps K ...   # the reference on host cores
+
+metric    Mrays/s @1080p, 1 spp/frame, README indoor scene (frames/s reported alongside).
+          A ray = one radiance-loop iteration = one reference intersect() call (SURVEY 8d
+          "segments"); identical for both implementations under identical seeds.
+workload  BASELINE.json configs[1]: indoor scene (textures as the MTL names them, cubemap =
+          the reference's constant fallback since garden.jpg is not shipped), 1920x1080,
+          1 spp per frame, temporal accumulation, bounces = 3 (the reference's constant).
+step      one frame = one raytrace() call = 1 spp over the whole image.
+N > 1     weak scaling by image tiles: the image grows to N x 1080p pixels (1920x2160,
+          3840x2160, 3840x4320), the scene is replicated, every rank accumulates its own
+          band of whole 16-row strips, and ONE NCCL all-gather of the RGBA8 bands follows the
+          last timed frame (inside the timed region).  No per-frame collective.
+value     device-resident: accumulator and RGBA8 stay in HBM, CUDA events per frame on the
+          launching stream, L2 flushed (512 MB memset) between timed frames.
+e2e       the same frames through ptc_render_host: camera/arguments host->device and the
+          RGBA8 frame device->pinned host every step, inside the timed region.
+roofline  for the dominant kernel (traversal): bytes of BVH nodes + triangle records the
+          traced rays fetch (counted by the kernel's own visit counters) over
+          the kernel's CUDA-event time, against MEASURED_PEAKS.json's HBM figure -- with the
+          FP32 issue bound printed beside it, since a 27 KB scene is not bandwidth-bound.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import importlib.util
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+PKG_DIR = os.path.join(REPO, "cuda-pathtracer_b200")
+GOLDEN = os.path.join(REPO, "tests", "golden")
+WEAK_DIMS = {1: (1920, 1080), 2: (1920, 2160), 4: (3840, 2160), 8: (3840, 4320)}
+
+
+def pkg():
+    name = "cuda_pathtracer_b200"
+    if name in sys.modules:
+        return sys.modules[name]
+    spec = importlib.util.spec_from_file_location(name, os.path.join(PKG_DIR, "__init__.py"),
+                                                  submodule_search_locations=[PKG_DIR])
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def load_scene(P, name):
+    if name.startswith("synth"):
+        return P.synth.terrain_room(grid=int(name[5:] or 256), tex_size=256)
+    p = os.path.join(GOLDEN, name + ".ptscene")
+    if not os.path.exists(p):
+        p += ".xz"
+    sc = P.ptscene.load_ptscene(p)
+    if sc.cubemap is None:
+        sc.cubemap = P.synth.constant_cubemap((19 / 255.0, 27 / 255.0, 35 / 255.0))
+        sc.cubemap_size = 1
+    return sc
+
+
+def measured_peaks():
+    p = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = [r for (t, r) in self.rows if t0 - 0.05 <= t <= t1 + 0.15] or [r for (_, r) in self.rows]
+        for r in rows:
+            f = [x.strip() for x in r.split(",")]
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except Exception:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+# the reference arm / cpu_baseline: the reference's own code (oracle/_ref) or the oracle port
+# ---------------------------------------------------------------------------------------------
+class CpuRenderer:
+    def __init__(self, prefer_reference=True):
+        ref = os.path.join(REPO, "oracle", "_ref", "libref_cpu.so")
+        port = os.path.join(REPO, "oracle", "libpt_oracle.so")
+        self.orc = C.CDLL(port) if os.path.exists(port) else None
+        if prefer_reference and os.path.exists(ref):
+            self.lib, self.kind, self.fn = C.CDLL(ref), "reference", "ref_cpu_kernel_sample"
+        elif self.orc is not None:
+            self.lib, self.kind, self.fn = self.orc, "port", "oracle_kernel_sample"
+        else:
+            raise RuntimeError("neither oracle/_ref/libref_cpu.so nor oracle/libpt_oracle.so is built")
+        self.cores = os.cpu_count() or 1
+
+    def count(self, sc, w, h, frame, bounces, stride, offset):
+        """Pixels and segments of the sample (untimed; the oracle port counts them)."""
+        desc, cam = sc.to_desc(), sc.camera_struct()
+        acc = np.zeros((h, w, 3), np.float32)
+        px, seg = C.c_uint64(0), C.c_uint64(0)
+        self.orc.oracle_kernel_sample(C.byref(desc), sc.cubemap.ctypes.data_as(C.c_void_p), C.c_uint(sc.cubemap_size),
+                                      C.byref(cam), C.c_uint(w), C.c_uint(h), C.c_uint(frame), C.c_uint(bounces),
+                                      C.c_uint(stride), C.c_uint(offset), acc.ctypes.data_as(C.c_void_p), None,
+                                      C.byref(px), C.byref(seg), C.c_int(self.cores))
+        return px.value, seg.value
+
+    def run(self, sc, w, h, frame, bounces, stride, offset, acc, out):
+        desc, cam = sc.to_desc(), sc.camera_struct()
+        args = [C.byref(desc), sc.cubemap.ctypes.data_as(C.c_void_p), C.c_uint(sc.cubemap_size), C.byref(cam),
+                C.c_uint(w), C.c_uint(h), C.c_uint(frame), C.c_uint(bounces), C.c_uint(stride), C.c_uint(offset),
+                acc.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p)]
+        if self.kind == "port":
+            args += [None, None]
+        args.append(C.c_int(self.cores))
+        t0 = time.perf_counter()
+        getattr(self.lib, self.fn)(*args)
+        return time.perf_counter() - t0
+
+
+def cpu_sample(P, sc, w, h, bounces, steps, warmup, target_step_s, prefer_reference=True):
+    """Times `steps` sampled launches; the stride is sized from one probe so a step takes about
+    target_step_s on this box's cores."""
+    cpu = CpuRenderer(prefer_reference)
+    acc = np.zeros((h, w, 3), np.float32)
+    out = np.zeros((h, w), np.uint32)
+    n_blocks = (w // 16 + 1) * (h // 16 + 1)
+    probe_stride = max(1, n_blocks // 256)
+    t = cpu.run(sc, w, h, 1, bounces, probe_stride, 0, acc, out)
+    full = t * probe_stride
+    stride = int(max(1, min(n_blocks, round(full / target_step_s))))
+    for k in range(warmup):
+        cpu.run(sc, w, h, k + 1, bounces, stride, k % stride, acc, out)
+    secs = segs = px = 0
+    for k in range(steps):
+        frame, off = warmup + k + 1, (warmup + k) % stride
+        p, s = cpu.count(sc, w, h, frame, bounces, stride, off)
+        secs += cpu.run(sc, w, h, frame, bounces, stride, off, acc, out)
+        segs, px = segs + s, px + p
+    return {"kind": cpu.kind, "cores": cpu.cores, "seconds": secs, "segments": segs, "pixels": px,
+            "stride": stride, "mrays": segs / secs / 1e6, "steps": steps,
+            "sample": f"{steps} launches x every {stride}-th 16x16 block of the {w}x{h} frame "
+                      f"({px} px, {segs} segments, {secs:.1f} s on {cpu.cores} threads)"}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    P = pkg()
+    sc = load_scene(P, args.scene)
+    w, h = (args.width, args.height) if args.width else WEAK_DIMS.get(args.gpus, WEAK_DIMS[1])
+    total = max(1, args.steps + args.warmup)
+    r = cpu_sample(P, sc, w, h, args.bounces, args.steps, args.warmup, min(2.0, 150.0 / total))
+    ms = r["seconds"] / args.steps * 1e3
+    frames_full = r["pixels"] / float(w * h)
+    line = {"impl": "reference", "metric": "Mrays/s @1080p 1spp indoor", "value": r["mrays"], "unit": "Mrays/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "frames_per_s": frames_full / r["seconds"],
+            "config": config_dict(args, w, h, sc, "host cores; each step = a strided sample of 16x16 blocks"),
+            "cpu_baseline": {"value": r["mrays"], "unit": "Mrays/s", "cores": r["cores"], "kind": r["kind"],
+                             "sample": r["sample"]},
+            "e2e": {"value": r["mrays"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+def config_dict(args, w, h, sc, l2):
+    return {"workload": f"{args.scene} {w}x{h} 1spp/frame bounces={args.bounces} temporal accumulation "
+                        f"(BASELINE.json configs[1]; cubemap = reference's constant fallback)",
+            "scene": args.scene, "width": w, "height": h, "bounces": args.bounces, "faces": sc.n_faces,
+            "partition": f"{args.gpus} band(s) of 16-row strips, scene replicated", "l2": l2}
+
+
+# ---------------------------------------------------------------------------------------------
+# this repository's arm
+# ---------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the path-tracing core has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    P = pkg()
+    sc = load_scene(P, args.scene)
+    n = max(world, 1)
+    w, h = (args.width, args.height) if args.width else WEAK_DIMS.get(n, (1920, 1080 * n))
+    core = P.Core(local)
+    sid = core.upload_scene(sc)
+    cid = core.set_cubemap(sc.cubemap)
+    gather = P.tiles.BandGather(h, w, world, rank)
+    r0, r1 = gather.band
+    bh = r1 - r0
+    dev = torch.device("cuda", local)
+    accum = torch.zeros(max(bh, 1), w, 3, device=dev)
+    out = torch.zeros(max(bh, 1), w, dtype=torch.int32, device=dev)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream()
+    K, W = args.steps, args.warmup
+
+    def frame(k):
+        if bh:
+            core.render(sid, cid, sc, w, h, accum, out, None, bounces=args.bounces, frame_nb=k,
+                        rows=(r0, r1), stream=stream.cuda_stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident value -----------------------------------------------------------
+    for k in range(1, W + 1):
+        frame(k)
+    if world > 1:
+        gather.gather(out.view(torch.uint8).view(bh, w, 4))  # warm NCCL
+    barrier()
+    core.reset_counters()
+    launches_before = core.launch_count()
+    sampler = ClockSampler(local) if rank == 0 else None
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_wall0 = time.time()
+    for k in range(K):
+        flush.zero_()                       # L2 flush between timed frames (outside the event pair)
+        ev[k][0].record(stream)
+        frame(W + 1 + k)
+        ev[k][1].record(stream)
+    g0.record(stream)
+    full = gather.gather(out.view(torch.uint8).view(bh, w, 4)) if bh else None
+    g1.record(stream)
+    barrier()
+    t_wall1 = time.time()
+    clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
+    ms_frames = sum(a.elapsed_time(b) for a, b in ev)
+    ms_gather = g0.elapsed_time(g1)
+    ms_total = ms_frames + ms_gather
+    c = core.counters()
+    launches = core.launch_count() - launches_before
+    stats = torch.tensor([ms_total, float(c.segments), float(c.traced), float(launches), ms_gather],
+                         dtype=torch.float64, device=dev)
+    if world > 1:
+        mx = stats.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+        ms_total, ms_gather = float(mx[0]), float(mx[4])
+    segments, traced, launches = float(stats[1]), float(stats[2]), int(stats[3])
+    value = segments / (ms_total * 1e-3) / 1e6
+
+    # ---- steady state without the flush (informational) -----------------------------------
+    barrier()
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record(stream)
+    for k in range(K):
+        frame(W + 1 + k)
+    s1.record(stream)
+    barrier()
+    ms_steady = s0.elapsed_time(s1) / K
+
+    # ---- end to end through the host-buffer call ------------------------------------------
+    h_accum = torch.zeros(max(bh, 1), w, 3).pin_memory()
+    h_out = torch.zeros(max(bh, 1), w, dtype=torch.int32).pin_memory()
+    e2e_ms = 0.0
+    if bh:
+        core.render_host(sid, cid, sc, w, h, h_accum.numpy(), h_out.numpy(), None, bounces=args.bounces,
+                         frame_nb=1, rows=(r0, r1), upload_accum=True)
+        for k in range(2, W + 1):
+            core.render_host(sid, cid, sc, w, h, h_accum.numpy(), h_out.numpy(), None, bounces=args.bounces,
+                             frame_nb=k, rows=(r0, r1))
+    barrier()
+    t0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for k in range(K):
+        if bh:
+            core.render_host(sid, cid, sc, w, h, h_accum.numpy(), h_out.numpy(), None, bounces=args.bounces,
+                             frame_nb=W + 1 + k, rows=(r0, r1), stream=stream.cuda_stream)
+    e1.record(stream)
+    barrier()
+    e2e_ms = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3)  # host-synchronous call: wall >= device
+    t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms = float(t[0])
+    e2e_value = segments / (e2e_ms * 1e-3) / 1e6
+
+    # ---- roofline of the dominant kernel (rank 0, N = 1 only needs it) ---------------------
+    roof = cpu_base = gpu_base = None
+    if rank == 0:
+        roof = roofline(P, core, sid, cid, sc, w, h, r0, r1, args, accum, out, stream)
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                r = cpu_sample(P, sc, w, h, args.bounces, 3, 1, 4.0, prefer_reference=False)
+                cpu_base = {"value": r["mrays"], "unit": "Mrays/s", "cores": r["cores"], "kind": r["kind"],
+                            "sample": r["sample"]}
+            except Exception as e:  # the checker is optional for the product, mandatory for the report
+                cpu_base = {"value": None, "unit": "Mrays/s", "cores": 0, "kind": "port", "sample": f"failed: {e}"}
+            gpu_base = reference_kernel_on_gpu(sc, w, h, args.bounces, K, W)
+
+    if rank == 0:
+        line = {"metric": "Mrays/s @1080p 1spp indoor", "value": value, "unit": "Mrays/s", "n_gpus": world,
+                "steps": K, "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "frames_per_s": K / (ms_total * 1e-3), "segments_per_step": segments / K,
+                "traced_per_step": traced / K, "ms_per_step_steady_no_flush": ms_steady,
+                "ms_gather_once": ms_gather,
+                "config": config_dict(args, w, h, sc, "512 MB memset between timed frames (outside the per-frame "
+                                                     "event pairs); steady-state figure without flush alongside"),
+                "clocks": clocks,
+                "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_ms / K,
+                        "h2d_bytes_per_step": C.sizeof(P.core.PtcRenderArgs) + 64,
+                        "d2h_bytes_per_step": int(bh) * w * 4},
+                "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu_base,
+                "reference_kernel_same_gpu": gpu_base}
+        print(json.dumps(line))
+    core.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def roofline(P, core, sid, cid, sc, w, h, r0, r1, args, accum, out, stream):
+    """Times the traversal kernel alone (CUDA events on its stream, L2 flushed before each
+    launch) on this frame's real ray queues and divides its algorithmic bytes by that time."""
+    import torch
+    hbm, how = measured_peaks()
+    try:
+        prof = core.profile_frame(sid, cid, sc, w, h, accum, out, bounces=args.bounces, frame_nb=5,
+                                  rows=(r0, r1), stream=stream.cuda_stream, repeats=5)
+    except Exception as e:
+        return {"bound": "hbm", "achieved": None, "peak": hbm, "unit": "GB/s", "frac": None, "traffic": None,
+                "note": f"profile_frame failed: {e}"}
+    info = core.scene_info(sid)
+    nbytes = prof["nodes_visited"] * info.bvh_node_bytes + prof["tris_tested"] * info.tri_bytes \
+        + prof["traced"] * prof["ray_io_bytes"]
+    ach = nbytes / (prof["extend_ms"] * 1e-3) / 1e9
+    flops = prof["nodes_visited"] * 160.0 + prof["tris_tested"] * 37.0
+    sm_mhz = prof.get("sm_mhz") or 1965.0
+    fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12
+    return {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": None,
+            "peak_source": how, "kernel": prof["kernel"], "kernel_ms_per_frame": prof["extend_ms"],
+            "frame_ms": prof["frame_ms"], "kernel_share_of_frame": prof["extend_ms"] / prof["frame_ms"],
+            "algorithmic_bytes_per_launch": nbytes, "nodes_per_ray": prof["nodes_visited"] / max(1, prof["traced"]),
+            "tris_per_ray": prof["tris_tested"] / max(1, prof["traced"]),
+            "fp32_bound": {"achieved_tflops": flops / (prof["extend_ms"] * 1e-3) / 1e12,
+                           "peak_tflops_at_max_clock": fp32_peak,
+                           "frac": flops / (prof["extend_ms"] * 1e-3) / 1e12 / fp32_peak},
+            "stages_ms": prof["stages_ms"]}
+
+
+def reference_kernel_on_gpu(sc, w, h, bounces, K, W):
+    """GPU baseline the north star names: the reference's own kernel (CUDA-12 patch, sm_100a,
+    oracle/_ref/libref_gpu.so) timed on the same B200 with the same frames."""
+    import torch
+    path = os.path.join(REPO, "oracle", "_ref", "libref_gpu.so")
+    if not os.path.exists(path):
+        return {"unavailable": "oracle/_ref/libref_gpu.so not built (needs /root/reference at build time)"}
+    sys.path.insert(0, os.path.join(REPO, "tests"))
+    from pt_testlib import RefGpu
+    g0 = RefGpu(sc)
+    acc = torch.zeros(h, w, 3, device="cuda")
+    out = torch.zeros(h, w, dtype=torch.int32, device="cuda")
+    for k in range(1, W + 1):
+        g0.kernel(w, h, k, bounces, acc.data_ptr(), out.data_ptr())
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    K = min(K, 32)
+    e0.record()
+    for k in range(K):
+        g0.kernel(w, h, W + 1 + k, bounces, acc.data_ptr(), out.data_ptr())
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / K
+    g0.close()
+    return {"ms_per_step": ms, "value": w * h * bounces / (ms * 1e-3) / 1e6, "unit": "Mrays/s",
+            "note": "reference raytrace.cu kernel, brute force over all faces, 16x16 blocks, same seeds"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--scene", default="indoor_tex")
+    ap.add_argument("--width", type=int, default=0)
+    ap.add_argument("--height", type=int, default=0)
+    ap.add_argument("--bounces", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -640,6 +640,48 @@ oracle_kernel(const ptc_scene_desc* desc, const float* cube_faces, unsigned cube
   return 0;
 }
 
+// Bounded SAMPLE of one launch, for timing on host cores (bench.py's cpu_baseline leg):
+// only the reference's 16x16 blocks b = by * (width/16 + 1) + bx with
+// b % block_stride == block_offset are rendered (rt.cu:315-317 defines the blocks).
+// Reports the pixels rendered and the radiance-loop iterations (segments) they took.
+int
+oracle_kernel_sample(const ptc_scene_desc* desc, const float* cube_faces, unsigned cube_size,
+                     const ptc_camera* camera, unsigned width, unsigned height, unsigned frame_nb,
+                     unsigned bounces, unsigned block_stride, unsigned block_offset, float* accum,
+                     uint32_t* out_rgba, uint64_t* pixels, uint64_t* segments, int n_threads)
+{
+  SceneView sc(desc, cube_faces, cube_size);
+  const uint32_t hash_seed = wang_hash(frame_nb);
+  const unsigned gx = width / 16 + 1, gy = height / 16 + 1;
+  if (!block_stride)
+    block_stride = 1;
+  std::vector<unsigned> blocks;
+  for (unsigned b = block_offset % block_stride; b < gx * gy; b += block_stride)
+    blocks.push_back(b);
+  std::vector<PathStats> st(blocks.size());
+  std::vector<uint64_t> px(blocks.size(), 0);
+  parallel_for((unsigned)blocks.size(), n_threads, [&](unsigned k) {
+    const unsigned bx = blocks[k] % gx, by = blocks[k] / gx;
+    for (unsigned ty = 0; ty < 16; ++ty)
+      for (unsigned tx = 0; tx < 16; ++tx) {
+        const unsigned x = bx * 16 + tx, y = by * 16 + ty;
+        if (x >= width || y >= height)
+          continue;
+        pixel(sc, camera, width, height, x, y, hash_seed, (int)frame_nb, (int)bounces, false, 0,
+              accum, out_rgba, nullptr, nullptr, &st[k]);
+        px[k]++;
+      }
+  });
+  uint64_t s = 0, n = 0;
+  for (size_t k = 0; k < blocks.size(); ++k)
+    s += st[k].segments, n += px[k];
+  if (pixels)
+    *pixels = n;
+  if (segments)
+    *segments = s;
+  return 0;
+}
+
 // Per-pixel un-clamped radiance (row 0 = top).
 int
 oracle_radiance(const ptc_scene_desc* desc, const float* cube_faces, unsigned cube_size,

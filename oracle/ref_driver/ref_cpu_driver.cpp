@@ -28,10 +28,27 @@ RefCubemapHost g_ref_cubemap = { nullptr, 0 };
 uint32_t* g_ref_out_rgba = nullptr;
 unsigned g_ref_out_width = 0;
 int g_ref_static_samples = 1;
+// bounded sample of a launch (bench.py's reference arm): only blocks with
+// b % stride == offset are executed
+static unsigned g_ref_block_stride = 1, g_ref_block_offset = 0;
 
 void
-ref_parallel_blocks(unsigned n_blocks, void (*fn)(unsigned, void*), void* ctx)
+ref_parallel_blocks(unsigned n_blocks_all, void (*fn_all)(unsigned, void*), void* ctx_all)
 {
+  struct Strided
+  {
+    void (*fn)(unsigned, void*);
+    void* ctx;
+    unsigned stride, offset;
+  } sd = { fn_all, ctx_all, g_ref_block_stride, g_ref_block_offset % g_ref_block_stride };
+  const unsigned n_blocks =
+    sd.stride > 1 ? (n_blocks_all > sd.offset ? (n_blocks_all - sd.offset + sd.stride - 1) / sd.stride : 0)
+                  : n_blocks_all;
+  void (*fn)(unsigned, void*) = [](unsigned b, void* c) {
+    Strided* s = static_cast<Strided*>(c);
+    s->fn(s->stride > 1 ? b * s->stride + s->offset : b, s->ctx);
+  };
+  void* ctx = &sd;
   int nt = g_ref_threads > 0 ? g_ref_threads : 1;
   if (nt == 1) {
     for (unsigned b = 0; b < n_blocks; ++b)
@@ -184,6 +201,23 @@ ref_cpu_kernel(const ptc_scene_desc* desc, const float* cube_faces, unsigned cub
              to_cam(camera), WangHash(frame_nb), (int)frame_nb, (float3*)accum,
              moved != 0, h_post_process_table[post_id]);
   return 0;
+}
+
+// The same launch restricted to the 16x16 blocks b with b % block_stride == block_offset
+// (a bounded sample for timing the reference on host cores).
+int
+ref_cpu_kernel_sample(const ptc_scene_desc* desc, const float* cube_faces, unsigned cube_size,
+                      const ptc_camera* camera, unsigned width, unsigned height,
+                      unsigned frame_nb, unsigned bounces, unsigned block_stride,
+                      unsigned block_offset, float* accum, uint32_t* out_rgba, int n_threads)
+{
+  g_ref_block_stride = block_stride ? block_stride : 1;
+  g_ref_block_offset = block_offset;
+  int rc = ref_cpu_kernel(desc, cube_faces, cube_size, camera, width, height, frame_nb, bounces, 0,
+                          0, accum, out_rgba, n_threads);
+  g_ref_block_stride = 1;
+  g_ref_block_offset = 0;
+  return rc;
 }
 
 // Per-pixel un-clamped radiance of sample `frame_nb` (row 0 = top): the kernel's
