@@ -12,7 +12,8 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libptcore.so")
 CUDA = os.environ.get("CUDA_HOME", "/usr/local/cuda")
 SOURCES = ["ptcore.cu", "kernels.cu", "bvh_builder.cpp"]
-HEADERS = ["bvh.h", "device_types.cuh", "kernels.cuh", "vecmath.cuh", "../../include/ptcore.h"]
+HEADERS = ["bvh.h", "device_types.cuh", "kernels.cuh", "vecmath.cuh", "traverse.cuh", "shade.cuh",
+           "../../include/ptcore.h"]
 
 
 def up_to_date():

@@ -31,7 +31,9 @@ class PtcRenderArgs(C.Structure):
                 ("bounces", C.c_uint32), ("moved", C.c_uint32),
                 ("post_id", C.c_uint32), ("frame_nb", C.c_uint32),
                 ("accum", C.c_void_p), ("out_rgba", C.c_void_p),
-                ("radiance_out", C.c_void_p), ("stream", C.c_void_p)]
+                ("radiance_out", C.c_void_p), ("stream", C.c_void_p),
+                ("strip_rows", C.c_uint32), ("strip_stride", C.c_uint32),
+                ("strip_phase", C.c_uint32), ("_pad", C.c_uint32)]
 
 
 class PtcCounters(C.Structure):
@@ -48,6 +50,15 @@ class PtcSceneInfo(C.Structure):
                 ("texture_bytes", C.c_uint64), ("smem_resident", C.c_uint32)]
 
 
+class PtcProfile(C.Structure):
+    _fields_ = [("n_launches", C.c_uint32), ("launch_ms", C.c_float * 66),
+                ("launch_bounce0", C.c_uint32 * 66), ("launch_iters", C.c_uint32 * 66),
+                ("frame_ms", C.c_float), ("traced", C.c_uint64), ("segments", C.c_uint64),
+                ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
+                ("rays_per_bounce", C.c_uint64 * 16), ("queue_rays", C.c_uint64),
+                ("queue_bytes_per_ray", C.c_uint32)]
+
+
 class PtcHostBvh(C.Structure):
     _fields_ = [("nodes", C.c_void_p), ("n_nodes", C.c_uint32), ("node_bytes", C.c_uint32),
                 ("tris", C.c_void_p), ("n_tris", C.c_uint32), ("tri_bytes", C.c_uint32),
@@ -59,7 +70,8 @@ EXPORTS = ["ptc_abi_version", "ptc_create", "ptc_destroy", "ptc_last_error", "pt
            "ptc_scene_info_get", "ptc_set_cubemap", "ptc_render", "ptc_render_host",
            "ptc_reset_accumulation", "ptc_counters_get", "ptc_counters_reset",
            "ptc_trace_primary", "ptc_intersect_rays", "ptc_debug_rng", "ptc_host_bvh_build",
-           "ptc_host_bvh_free"]
+           "ptc_host_bvh_free", "ptc_band_rows", "ptc_launch_count", "ptc_set_wavefront",
+           "ptc_profile_frame"]
 
 _lib = None
 
@@ -83,8 +95,10 @@ def load_library() -> C.CDLL:
         lib.ptc_host_bvh_free.restype = None
         for name in ["ptc_upload_scene", "ptc_scene_info_get", "ptc_set_cubemap", "ptc_render",
                      "ptc_render_host", "ptc_reset_accumulation", "ptc_counters_get",
-                     "ptc_counters_reset", "ptc_trace_primary", "ptc_intersect_rays", "ptc_debug_rng"]:
+                     "ptc_counters_reset", "ptc_trace_primary", "ptc_intersect_rays", "ptc_debug_rng",
+                     "ptc_launch_count", "ptc_set_wavefront", "ptc_profile_frame"]:
             getattr(lib, name).restype = C.c_int
+        lib.ptc_band_rows.restype = C.c_uint32
         _lib = lib
     return _lib
 
@@ -175,7 +189,7 @@ class Core:
     # -- render ----------------------------------------------------------------
     def _args(self, scene_id, cubemap_id, camera, width, height, accum, out_rgba=None,
               radiance_out=None, bounces=3, moved=False, post_id=0, frame_nb=0, rows=None,
-              stream=0):
+              stream=0, strips=None):
         cam = camera if isinstance(camera, PtcCamera) else camera.camera_struct()
         self._keep = [cam]
         a = PtcRenderArgs()
@@ -188,7 +202,41 @@ class Core:
         a.out_rgba = _ptr(out_rgba)
         a.radiance_out = _ptr(radiance_out)
         a.stream = C.c_void_p(int(stream)) if stream else None
+        if strips:  # (strip_rows, strip_stride, strip_phase): interleaved image tiles
+            a.strip_rows, a.strip_stride, a.strip_phase = strips
         return a
+
+    def band_rows(self, width, height, rows=None, strips=None) -> int:
+        a = PtcRenderArgs()
+        a.width, a.height = width, height
+        a.row_begin, a.row_end = rows if rows else (0, 0)
+        if strips:
+            a.strip_rows, a.strip_stride, a.strip_phase = strips
+        return int(self.lib.ptc_band_rows(C.byref(a)))
+
+    def launch_count(self) -> int:
+        n = C.c_uint64(0)
+        self._check(self.lib.ptc_launch_count(self.ctx, C.byref(n)), "ptc_launch_count")
+        return n.value
+
+    def set_wavefront(self, first_iters=0, next_iters=0):
+        self._check(self.lib.ptc_set_wavefront(self.ctx, C.c_uint32(first_iters), C.c_uint32(next_iters)),
+                    "ptc_set_wavefront")
+
+    def profile_frame(self, *args, repeats=5, **kw) -> dict:
+        """Per-launch CUDA-event times of one frame + traversal statistics (ptc_profile_frame)."""
+        a = self._args(*args, **kw)
+        pr = PtcProfile()
+        self._check(self.lib.ptc_profile_frame(self.ctx, C.byref(a), C.c_uint32(repeats), C.byref(pr)),
+                    "ptc_profile_frame")
+        n = pr.n_launches
+        return {"launch_ms": [pr.launch_ms[i] for i in range(n)],
+                "launch_bounce0": [pr.launch_bounce0[i] for i in range(n)],
+                "launch_iters": [pr.launch_iters[i] for i in range(n)],
+                "frame_ms": pr.frame_ms, "traced": pr.traced, "segments": pr.segments,
+                "nodes_visited": pr.nodes_visited, "tris_tested": pr.tris_tested,
+                "rays_per_bounce": [pr.rays_per_bounce[i] for i in range(16)],
+                "queue_rays": pr.queue_rays, "queue_bytes_per_ray": pr.queue_bytes_per_ray}
 
     def render(self, *args, **kw):
         """Device-pointer render call (accum / out_rgba / radiance_out are device buffers)."""

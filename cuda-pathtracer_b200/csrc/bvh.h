@@ -64,7 +64,8 @@ static_assert(sizeof(ShadeRecord) == 80, "ShadeRecord must be 80 bytes");
 struct BuildStats
 {
   float sah_cost = 0.f;
-  uint32_t max_depth = 0;
+  uint32_t max_depth = 0;  // binary tree
+  uint32_t wide_depth = 0; // levels of 8-wide nodes (root = 1)
   uint32_t n_leaves = 0;
 };
 

@@ -13,6 +13,7 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 
@@ -55,6 +56,14 @@ struct BinNode
 
 constexpr int kBins = 16;
 constexpr uint32_t kMaxLeaf = 3;
+
+static float
+trav_cost()
+{
+  static float c = getenv("PTC_TRAV_COST") ? (float)atof(getenv("PTC_TRAV_COST")) : 1.0f;
+  return c;
+}
+
 
 struct Builder
 {
@@ -143,7 +152,7 @@ struct Builder
       mid = first + count / 2;
     } else {
       float leaf_cost = box.half_area() * count;
-      if (count <= kMaxLeaf && leaf_cost <= best_cost + box.half_area() * 1.0f)
+      if (count <= kMaxLeaf && leaf_cost <= best_cost + box.half_area() * trav_cost())
         return idx; // cheaper (or as cheap) to keep as a leaf
       float ext = cbox.hi[best_axis] - cbox.lo[best_axis];
       float scale = kBins / ext;
@@ -161,6 +170,88 @@ struct Builder
     nodes[idx].left = l;
     nodes[idx].right = r;
     return idx;
+  }
+};
+
+// Optimal collapse of the binary tree into 8-wide nodes (dynamic program over
+// "represent the subtree of n as a forest of at most i wide-node children", after
+// Ylitie, Karras, Laine 2017, section 3.1).  Cost = surface-area-weighted node visits
+// (c_node) and triangle tests (c_prim); the ratio follows the measured instruction cost
+// of one 8-wide node test (~260) against one triangle test (~55) in the traversal kernel.
+struct CollapseDp
+{
+  static constexpr float kNodeCost = 1.0f;
+  const float kPrimCost = getenv("PTC_PRIM_COST") ? (float)atof(getenv("PTC_PRIM_COST")) : 0.22f;
+  const std::vector<BinNode>& nodes;
+  struct Entry
+  {
+    float c[8];        // c[i], i = 1..7
+    uint8_t split[9];  // distribute(j): roots given to the left child, j = 2..8
+    uint8_t use_dist[8]; // c[i] came from distribute(i) (else from c[i-1]), i = 2..7
+    bool leaf1;        // c[1] is the leaf alternative
+  };
+  std::vector<Entry> e;
+
+  explicit CollapseDp(const std::vector<BinNode>& n) : nodes(n), e(n.size())
+  {
+    for (int idx = (int)nodes.size() - 1; idx >= 0; --idx) { // children have larger indices
+      const BinNode& n = nodes[idx];
+      Entry& en = e[idx];
+      std::memset(&en, 0, sizeof(en));
+      const float area = n.box.half_area();
+      const float c_leaf = n.count <= kMaxLeaf ? area * (float)n.count * kPrimCost : FLT_MAX;
+      if (n.leaf()) {
+        for (int i = 1; i < 8; ++i)
+          en.c[i] = c_leaf;
+        en.leaf1 = true;
+        continue;
+      }
+      const Entry &l = e[n.left], &r = e[n.right];
+      float dist[9];
+      for (int j = 2; j <= 8; ++j) {
+        dist[j] = FLT_MAX;
+        for (int k = 1; k < j; ++k) {
+          if (k > 7 || j - k > 7)
+            continue;
+          float c = l.c[k] + r.c[j - k];
+          if (c < dist[j]) {
+            dist[j] = c;
+            en.split[j] = (uint8_t)k;
+          }
+        }
+      }
+      const float c_internal = dist[8] + area * kNodeCost;
+      en.leaf1 = c_leaf <= c_internal;
+      en.c[1] = en.leaf1 ? c_leaf : c_internal;
+      for (int i = 2; i < 8; ++i) {
+        en.use_dist[i] = dist[i] < en.c[i - 1];
+        en.c[i] = en.use_dist[i] ? dist[i] : en.c[i - 1];
+      }
+    }
+  }
+
+  bool is_leaf(int n) const { return e[n].leaf1; }
+
+  // roots of the optimal forest of at most i trees for the subtree of n
+  void gather(int n, int i, std::vector<int>& out) const
+  {
+    while (i > 1 && !(nodes[n].left >= 0 && e[n].use_dist[i]))
+      --i;
+    if (i == 1) {
+      out.push_back(n);
+      return;
+    }
+    const int k = e[n].split[i];
+    gather(nodes[n].left, k, out);
+    gather(nodes[n].right, i - k, out);
+  }
+
+  // children of the wide node that represents the (internal) subtree of n
+  void gather_children(int n, std::vector<int>& out) const
+  {
+    const int k = e[n].split[8];
+    gather(nodes[n].left, k, out);
+    gather(nodes[n].right, 8 - k, out);
   }
 };
 
@@ -215,7 +306,7 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
       extent = std::max(extent, scene.hi[a] - scene.lo[a]);
       maxabs = std::max(maxabs, std::max(std::fabs(scene.lo[a]), std::fabs(scene.hi[a])));
     }
-  const float pad = std::ldexp(std::max(extent, maxabs), -16) + FLT_MIN;
+  const float pad = std::ldexp(std::max(extent, maxabs), -15) + FLT_MIN;
   for (Box& b : boxes)
     for (int a = 0; a < 3; ++a) {
       b.lo[a] -= pad;
@@ -241,6 +332,7 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
     std::memset(&n, 0, sizeof(n));
     n.e[0] = n.e[1] = n.e[2] = 1;
     out.nodes.push_back(n);
+    out.stats.wide_depth = 1;
     return;
   }
 
@@ -257,43 +349,29 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
     out.stats.sah_cost = root_area > 0 ? (float)(cost / root_area) : 0.f;
   }
 
+  const CollapseDp dp(b.nodes);
+
   struct Pending
   {
     int bin;      // binary node whose subtree this wide node covers
     uint32_t out; // index in out.nodes
+    uint32_t depth;
   };
   std::vector<Pending> queue;
   out.nodes.emplace_back();
-  queue.push_back({ root, 0 });
+  queue.push_back({ root, 0, 1 });
 
   for (size_t qi = 0; qi < queue.size(); ++qi) {
     const Pending cur = queue[qi];
     const BinNode& top = b.nodes[cur.bin];
+    out.stats.wide_depth = std::max(out.stats.wide_depth, cur.depth);
 
-    // 1. gather up to 8 children
+    // 1. gather up to 8 children: the forest of binary subtrees the collapse DP chose
     std::vector<int> kids;
-    if (top.leaf())
+    if (dp.is_leaf(cur.bin))
       kids.push_back(cur.bin);
-    else {
-      kids.push_back(top.left);
-      kids.push_back(top.right);
-      while (kids.size() < 8) {
-        int best = -1;
-        float best_area = -1.f;
-        for (size_t k = 0; k < kids.size(); ++k) {
-          const BinNode& c = b.nodes[kids[k]];
-          if (!c.leaf() && c.box.half_area() > best_area) {
-            best_area = c.box.half_area();
-            best = (int)k;
-          }
-        }
-        if (best < 0)
-          break;
-        int open = kids[best];
-        kids[best] = b.nodes[open].left;
-        kids.push_back(b.nodes[open].right);
-      }
-    }
+    else
+      dp.gather_children(cur.bin, kids);
 
     // 2. slot assignment: slot s is visited first by rays whose direction is
     //    negative exactly on the axes set in s, so it should hold the child that
@@ -362,7 +440,7 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
         n.qlo[a][s] = (uint8_t)std::min(255.f, std::max(0.f, ql));
         n.qhi[a][s] = (uint8_t)std::min(255.f, std::max(0.f, qh));
       }
-      if (c.leaf()) {
+      if (dp.is_leaf(kids[k])) {
         uint32_t unary = (1u << c.count) - 1u; // 001, 011, 111
         n.meta[s] = (uint8_t)((unary << 5) | tri_off);
         std::vector<uint32_t> ids(b.order.begin() + c.first, b.order.begin() + c.first + c.count);
@@ -374,7 +452,7 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
       } else {
         n.imask |= (uint8_t)(1u << s);
         n.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
-        queue.push_back({ kids[k], (uint32_t)out.nodes.size() });
+        queue.push_back({ kids[k], (uint32_t)out.nodes.size(), cur.depth + 1 });
         out.nodes.emplace_back();
       }
     }

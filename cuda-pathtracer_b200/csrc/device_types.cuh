@@ -12,6 +12,11 @@ constexpr float kMaxDist = 100000.0f; // MAX_DIST, intersection.cuh:165
 constexpr int kNodeVec = 5;           // uint4 per Node8
 constexpr int kTriVec = 3;            // float4 per TriRecord
 constexpr int kShadeVec = 5;          // float4 per ShadeRecord
+// traversal stack entries per ray: one node group + one deferred triangle group per level of
+// the wide tree (ptc_upload_scene rejects trees deeper than kStackSize / 2 - 1)
+constexpr int kStackSize = 48;
+constexpr int kBlock = 256;           // threads per CTA of the path kernels (8 warps)
+constexpr int kTileW = 8, kTileH = 4; // pixels one warp covers in the first wavefront stage
 
 struct DTexture // arena-resident copy of scene::Texture (scene_data.h:31-37)
 {
@@ -33,17 +38,21 @@ struct DScene
   uint32_t n_tris;
 };
 
-// Wavefront path state, structure of arrays over path slots (slot = pixel index
-// inside the rendered band).  104 bytes per path.
-struct PathState
+// One compacted ray queue: structure of arrays over queue slots, 64 bytes per live path,
+// written once by the stage that produced the ray and read once by the next stage.
+//   o   : origin.xyz, w = carried specular_col (reference quirk Q3)
+//   d   : dir.xyz (not renormalised after a specular mix, Q8), w = bits: RNG draws so far
+//   thr : throughput.xyz, w = bits: band-local pixel index
+//   acc : radiance of this sample so far .xyz
+// The XORWOW state is NOT stored: it is a pure function of (pixel, frame, draws so far) and
+// is replayed from the seed (24 B read + 24 B written per ray per bounce saved for ~8 integer
+// instructions per replayed draw).
+struct RayQueue
 {
-  float4* ray_o;  // origin.xyz, w = carried specular_col (reference quirk Q3)
-  float4* ray_d;  // dir.xyz (not normalised after a specular mix, Q8)
-  uint4* hit;     // t bits, hit id (PTC_HIT_MISS = 0xffffffff), barycentric u, v bits
-  float4* thr;    // throughput.xyz
-  float4* acc;    // accumulated radiance.xyz of this sample
-  uint4* rng_a;   // XORWOW v[0..3]
-  uint2* rng_b;   // XORWOW v[4], d
+  float4* o;
+  float4* d;
+  float4* thr;
+  float4* acc;
 };
 
 struct Counters // device mirror of the ray-count part of ptc_counters
@@ -60,12 +69,34 @@ struct FrameParams
 {
   ptc_camera cam;
   uint32_t width, height;      // full image
-  uint32_t row_begin, row_end; // band rendered by this context
+  uint32_t row_begin;          // contiguous band: first global row (strip_stride == 1)
+  uint32_t band_rows;          // rows rendered by this call
+  uint32_t strip_rows;         // interleaved bands: rows per strip ...
+  uint32_t strip_stride;       // ... every strip_stride-th strip ...
+  uint32_t strip_phase;        // ... starting at strip strip_phase (1, x, 0 = contiguous)
+  uint32_t tiles_x;            // ceil(width / kTileW)
   uint32_t hash_seed;          // WangHash(frame_nb), raytrace.cu:321
   int32_t frame_nb;
   int32_t max_bounces;         // 1 + (static_samples + 1), raytrace.cu:66
   int32_t is_static;           // !moved
   uint32_t post_id;
+};
+
+// band-local row -> row of the full image
+__host__ __device__ inline uint32_t
+global_row(const FrameParams& fp, uint32_t lrow)
+{
+  if (fp.strip_stride <= 1)
+    return fp.row_begin + lrow;
+  const uint32_t k = lrow / fp.strip_rows;
+  return (fp.strip_phase + k * fp.strip_stride) * fp.strip_rows + lrow % fp.strip_rows;
+}
+
+struct FrameOut
+{
+  float* accum;         // float3 per band pixel, rows bottom-up inside the band (raytrace.cu:252)
+  uint32_t* out_rgba;   // RGBA8 per band pixel, row 0 = top; may be null
+  float* radiance_out;  // optional un-clamped radiance of this sample, top-down; may be null
 };
 
 } // namespace ptc

@@ -5,24 +5,24 @@
 
 namespace ptc {
 
-void launch_generate(const FrameParams& fp, const PathState& st, cudaStream_t s);
-void launch_extend(const DScene& sc, const PathState& st, const uint32_t* queue,
-                   const uint32_t* queue_count, uint32_t n_max, Counters* ctr, int bounce,
-                   cudaStream_t s);
-void launch_shade(const FrameParams& fp, const DScene& sc, const PathState& st,
-                  cudaTextureObject_t cube, const uint32_t* queue, const uint32_t* queue_count,
-                  uint32_t n_max, uint32_t* queue_out, uint32_t* count_out, Counters* ctr, int bounce,
-                  cudaStream_t s);
-void launch_shade_preview(const FrameParams& fp, const DScene& sc, const PathState& st,
-                          cudaTextureObject_t cube, uint32_t n_max, Counters* ctr, cudaStream_t s);
-void launch_accumulate(const FrameParams& fp, const PathState& st, float* accum, uint32_t* out_rgba,
-                       float* radiance_out, Counters* ctr, cudaStream_t s);
+// resident CTAs per SM of k_path<first, stats> (sizes the persistent grid)
+int path_kernel_blocks_per_sm(bool first, bool stats);
+
+// One wavefront step: `n_iters` x [extend -> shade] starting at radiance-loop iteration
+// `bounce0`.  first: rays are generated (8x4 pixel tile per warp) instead of read from
+// `qin`; survivors are appended to `qout` / `qout_count`.  `work` is a zeroed counter the
+// persistent warps pull their work items from.
+void launch_path(bool first, bool stats, uint32_t grid, const FrameParams& fp, const DScene& sc,
+                 cudaTextureObject_t cube, const RayQueue& qin, const uint32_t* qin_count,
+                 const RayQueue& qout, uint32_t* qout_count, const FrameOut& fo, Counters* ctr,
+                 uint32_t* work, int bounce0, int n_iters, cudaStream_t s);
+
+void launch_primary_hits(const FrameParams& fp, const DScene& sc, int32_t* ids, float* ts,
+                         cudaStream_t s);
 void launch_intersect_rays(const DScene& sc, const float* origins, const float* dirs, uint64_t n,
                            int32_t* ids, float* ts, Counters* ctr, cudaStream_t s);
 void launch_debug_rng(const uint32_t* seeds, uint32_t n_seeds, uint32_t n_draws, float* out,
                       cudaStream_t s);
-void launch_export_primary(const PathState& st, uint32_t n, int32_t* ids, float* ts, float* origins,
-                           float* dirs, cudaStream_t s);
 // toolkit cuRAND on the device, for the RNG known-answer test
 void launch_debug_curand(const uint32_t* seeds, uint32_t n_seeds, uint32_t n_draws, float* out,
                          cudaStream_t s);

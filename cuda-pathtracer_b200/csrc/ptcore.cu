@@ -40,11 +40,14 @@ struct ptc_context
   int device = 0;
   std::vector<SceneDev> scenes;
   std::vector<CubeDev> cubemaps;
-  PathState st{};
-  uint32_t capacity = 0;       // path slots allocated
-  uint32_t* queue[2] = { nullptr, nullptr };
-  uint32_t* counts = nullptr;  // one counter per bounce
+  RayQueue queue[2]{};         // double-buffered compacted ray queues
+  uint32_t capacity = 0;       // queue slots allocated
+  uint32_t* counts = nullptr;  // one queue counter per wavefront step
   Counters* ctr = nullptr;
+  int n_sms = 148;
+  int grid_first = 0, grid_next = 0, grid_first_stats = 0, grid_next_stats = 0;
+  uint32_t first_iters = 1, next_iters = 1; // wavefront granularity (ptc_set_wavefront)
+  uint64_t launches = 0;
   uint32_t seed = 0;           // the reference's function-static frame counter (raytrace.cu:296)
   // staging for ptc_render_host
   float* h_accum_dev = nullptr;
@@ -57,6 +60,7 @@ struct ptc_context
 namespace {
 
 constexpr int kMaxBounces = 64;
+constexpr int kCountSlots = 2 * (kMaxBounces + 2); // queue counters, then work counters
 
 int
 fail(ptc_context* ctx, int code, const std::string& msg)
@@ -108,17 +112,13 @@ dev_upload(ptc_context* ctx, SceneDev& s, const T* host, size_t n, const T** out
 void
 free_state(ptc_context* ctx)
 {
-  cudaFree(ctx->st.ray_o);
-  cudaFree(ctx->st.ray_d);
-  cudaFree(ctx->st.hit);
-  cudaFree(ctx->st.thr);
-  cudaFree(ctx->st.acc);
-  cudaFree(ctx->st.rng_a);
-  cudaFree(ctx->st.rng_b);
-  cudaFree(ctx->queue[0]);
-  cudaFree(ctx->queue[1]);
-  ctx->st = PathState{};
-  ctx->queue[0] = ctx->queue[1] = nullptr;
+  for (RayQueue& q : ctx->queue) {
+    cudaFree(q.o);
+    cudaFree(q.d);
+    cudaFree(q.thr);
+    cudaFree(q.acc);
+    q = RayQueue{};
+  }
   ctx->capacity = 0;
 }
 
@@ -128,15 +128,12 @@ ensure_capacity(ptc_context* ctx, uint32_t n)
   if (n <= ctx->capacity)
     return 0;
   free_state(ctx);
-  CUDA_TRY(ctx, cudaMalloc(&ctx->st.ray_o, (size_t)n * sizeof(float4)));
-  CUDA_TRY(ctx, cudaMalloc(&ctx->st.ray_d, (size_t)n * sizeof(float4)));
-  CUDA_TRY(ctx, cudaMalloc(&ctx->st.hit, (size_t)n * sizeof(uint4)));
-  CUDA_TRY(ctx, cudaMalloc(&ctx->st.thr, (size_t)n * sizeof(float4)));
-  CUDA_TRY(ctx, cudaMalloc(&ctx->st.acc, (size_t)n * sizeof(float4)));
-  CUDA_TRY(ctx, cudaMalloc(&ctx->st.rng_a, (size_t)n * sizeof(uint4)));
-  CUDA_TRY(ctx, cudaMalloc(&ctx->st.rng_b, (size_t)n * sizeof(uint2)));
-  CUDA_TRY(ctx, cudaMalloc(&ctx->queue[0], (size_t)n * sizeof(uint32_t)));
-  CUDA_TRY(ctx, cudaMalloc(&ctx->queue[1], (size_t)n * sizeof(uint32_t)));
+  for (RayQueue& q : ctx->queue) {
+    CUDA_TRY(ctx, cudaMalloc(&q.o, (size_t)n * sizeof(float4)));
+    CUDA_TRY(ctx, cudaMalloc(&q.d, (size_t)n * sizeof(float4)));
+    CUDA_TRY(ctx, cudaMalloc(&q.thr, (size_t)n * sizeof(float4)));
+    CUDA_TRY(ctx, cudaMalloc(&q.acc, (size_t)n * sizeof(float4)));
+  }
   ctx->capacity = n;
   return 0;
 }
@@ -153,6 +150,40 @@ wang_hash(uint32_t a)
   return a;
 }
 
+// Rows this call renders: contiguous band or interleaved strips (ptcore.h).
+bool
+band_geometry(const ptc_render_args* a, FrameParams& fp)
+{
+  fp.width = a->width;
+  fp.height = a->height;
+  fp.tiles_x = (a->width + kTileW - 1) / kTileW;
+  fp.strip_rows = a->strip_rows ? a->strip_rows : 16u;
+  fp.strip_stride = a->strip_stride > 1 ? a->strip_stride : 1u;
+  fp.strip_phase = a->strip_phase;
+  if (fp.strip_stride == 1) {
+    fp.strip_phase = 0;
+    uint32_t r0 = a->row_begin, r1 = a->row_end;
+    if (r0 == 0 && r1 == 0)
+      r1 = a->height;
+    if (r0 >= r1 || r1 > a->height)
+      return false;
+    fp.row_begin = r0;
+    fp.band_rows = r1 - r0;
+    return true;
+  }
+  if (a->row_begin || a->row_end || fp.strip_phase >= fp.strip_stride)
+    return false;
+  fp.row_begin = 0;
+  const uint32_t n_strips = (a->height + fp.strip_rows - 1) / fp.strip_rows;
+  uint32_t rows = 0;
+  for (uint32_t s = fp.strip_phase; s < n_strips; s += fp.strip_stride) {
+    const uint32_t b = s * fp.strip_rows, e = b + fp.strip_rows < a->height ? b + fp.strip_rows : a->height;
+    rows += e - b;
+  }
+  fp.band_rows = rows;
+  return rows > 0;
+}
+
 int
 fill_frame(ptc_context* ctx, const ptc_render_args* a, FrameParams& fp, bool advance_counter)
 {
@@ -165,14 +196,8 @@ fill_frame(ptc_context* ctx, const ptc_render_args* a, FrameParams& fp, bool adv
   if (a->width == 0 || a->height == 0)
     return fail(ctx, PTC_ERR_INVALID, "empty image");
   fp.cam = *a->camera;
-  fp.width = a->width;
-  fp.height = a->height;
-  fp.row_begin = a->row_begin;
-  fp.row_end = a->row_end;
-  if (fp.row_begin == 0 && fp.row_end == 0)
-    fp.row_end = a->height;
-  if (fp.row_begin >= fp.row_end || fp.row_end > a->height)
-    return fail(ctx, PTC_ERR_INVALID, "bad row range");
+  if (!band_geometry(a, fp))
+    return fail(ctx, PTC_ERR_INVALID, "bad row range / strip arguments");
   uint32_t bounces = a->bounces ? a->bounces : 3u; // 1 + (static_samples + 1), static_samples = 1
   if (bounces > (uint32_t)kMaxBounces)
     return fail(ctx, PTC_ERR_INVALID, "too many bounces");
@@ -196,32 +221,69 @@ fill_frame(ptc_context* ctx, const ptc_render_args* a, FrameParams& fp, bool adv
   return 0;
 }
 
-// Enqueues one frame; accum/out/rad are device pointers.
+// One launch of the frame's schedule.
+struct Step
+{
+  bool first;
+  int bounce0, n_iters;
+};
+
+// The wavefront schedule of a frame: the first stage generates the rays and runs
+// `first_iters` radiance-loop iterations in registers; every later stage runs `next_iters`.
+int
+frame_schedule(const ptc_context* ctx, const FrameParams& fp, Step* steps)
+{
+  int n = 0;
+  if (!fp.is_static) {
+    steps[n++] = Step{ true, 0, 1 };
+    return n;
+  }
+  int b = (int)ctx->first_iters < fp.max_bounces ? (int)ctx->first_iters : fp.max_bounces;
+  steps[n++] = Step{ true, 0, b };
+  while (b < fp.max_bounces) {
+    int k = (int)ctx->next_iters < fp.max_bounces - b ? (int)ctx->next_iters : fp.max_bounces - b;
+    steps[n++] = Step{ false, b, k };
+    b += k;
+  }
+  return n;
+}
+
+// Enqueues one frame; accum/out/rad are device pointers.  `ev` (optional) receives one
+// event before the first launch and one after every launch.
 int
 enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp, float* accum,
-              uint32_t* out, float* rad, cudaStream_t s)
+              uint32_t* out, float* rad, cudaStream_t s, bool stats = false, cudaEvent_t* ev = nullptr)
 {
   const SceneDev& sc = ctx->scenes[a->scene_id];
   const CubeDev& cm = ctx->cubemaps[a->cubemap_id];
-  const uint32_t n = (fp.row_end - fp.row_begin) * fp.width;
+  const uint32_t n = fp.band_rows * fp.width;
   int rc = ensure_capacity(ctx, n);
   if (rc)
     return rc;
-  CUDA_TRY(ctx, cudaMemsetAsync(ctx->counts, 0, sizeof(uint32_t) * (kMaxBounces + 1), s));
-  launch_generate(fp, ctx->st, s);
-  if (!fp.is_static) {
-    launch_extend(sc.d, ctx->st, nullptr, nullptr, n, ctx->ctr, 0, s);
-    launch_shade_preview(fp, sc.d, ctx->st, cm.tex, n, ctx->ctr, s);
-  } else {
-    for (int b = 0; b < fp.max_bounces; ++b) {
-      const uint32_t* q = b ? ctx->queue[b & 1] : nullptr;
-      const uint32_t* qc = b ? ctx->counts + b : nullptr;
-      launch_extend(sc.d, ctx->st, q, qc, n, ctx->ctr, b, s);
-      launch_shade(fp, sc.d, ctx->st, cm.tex, q, qc, n, ctx->queue[(b + 1) & 1], ctx->counts + b + 1,
-                   ctx->ctr, b, s);
+  FrameOut fo{ accum, out, rad };
+  Step steps[kMaxBounces + 1];
+  const int n_steps = frame_schedule(ctx, fp, steps);
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->counts, 0, sizeof(uint32_t) * kCountSlots, s));
+  if (ev)
+    CUDA_TRY(ctx, cudaEventRecord(ev[0], s));
+  const uint32_t tiles = fp.tiles_x * ((fp.band_rows + kTileH - 1) / kTileH);
+  for (int k = 0; k < n_steps; ++k) {
+    const Step& st = steps[k];
+    uint32_t grid;
+    if (st.first) {
+      const uint32_t want = (tiles + kBlock / 32 - 1) / (kBlock / 32);
+      const uint32_t cap = (uint32_t)(stats ? ctx->grid_first_stats : ctx->grid_first);
+      grid = want < cap ? want : cap;
+    } else {
+      grid = (uint32_t)(stats ? ctx->grid_next_stats : ctx->grid_next);
     }
+    launch_path(st.first, stats, grid, fp, sc.d, cm.tex, ctx->queue[k & 1], ctx->counts + k,
+                ctx->queue[(k + 1) & 1], ctx->counts + k + 1, fo, ctx->ctr,
+                ctx->counts + kMaxBounces + 2 + k, st.bounce0, st.n_iters, s);
+    ctx->launches++;
+    if (ev)
+      CUDA_TRY(ctx, cudaEventRecord(ev[k + 1], s));
   }
-  launch_accumulate(fp, ctx->st, accum, out, rad, ctx->ctr, s);
   CUDA_TRY(ctx, cudaGetLastError());
   return 0;
 }
@@ -251,12 +313,18 @@ ptc_create(int device, ptc_context** out)
   ctx->device = device;
   DeviceGuard g(device);
   if (cudaMalloc(&ctx->ctr, sizeof(Counters)) != cudaSuccess ||
-      cudaMalloc(&ctx->counts, sizeof(uint32_t) * (kMaxBounces + 1)) != cudaSuccess) {
+      cudaMalloc(&ctx->counts, sizeof(uint32_t) * kCountSlots) != cudaSuccess) {
     delete ctx;
     return PTC_ERR_ALLOC;
   }
   cudaMemset(ctx->ctr, 0, sizeof(Counters));
-  cudaMemset(ctx->counts, 0, sizeof(uint32_t) * (kMaxBounces + 1));
+  cudaMemset(ctx->counts, 0, sizeof(uint32_t) * kCountSlots);
+  cudaDeviceGetAttribute(&ctx->n_sms, cudaDevAttrMultiProcessorCount, device);
+  // persistent grids: resident CTAs per SM x SMs (148 on B200)
+  ctx->grid_first = ctx->n_sms * path_kernel_blocks_per_sm(true, false);
+  ctx->grid_next = ctx->n_sms * path_kernel_blocks_per_sm(false, false);
+  ctx->grid_first_stats = ctx->n_sms * path_kernel_blocks_per_sm(true, true);
+  ctx->grid_next_stats = ctx->n_sms * path_kernel_blocks_per_sm(false, true);
   *out = ctx;
   return PTC_OK;
 }
@@ -317,6 +385,8 @@ ptc_upload_scene(ptc_context* ctx, const ptc_scene_desc* desc, int32_t* scene_id
 
   HostBvh bvh;
   build_bvh(desc, bvh);
+  if (2 * (int)bvh.stats.wide_depth + 2 > kStackSize)
+    return fail(ctx, PTC_ERR_INVALID, "BVH too deep for the traversal stack");
   std::vector<ShadeRecord> shade;
   build_shade_records(desc, shade);
 
@@ -453,7 +523,7 @@ ptc_render_host(ptc_context* ctx, const ptc_render_args* args, int upload_accum,
     return rc;
   if (!args->accum)
     return fail(ctx, PTC_ERR_INVALID, "accum is required");
-  const size_t n = (size_t)(fp.row_end - fp.row_begin) * fp.width;
+  const size_t n = (size_t)fp.band_rows * fp.width;
   cudaStream_t s = (cudaStream_t)args->stream;
   if (n != ctx->h_px) {
     cudaFree(ctx->h_accum_dev);
@@ -524,6 +594,108 @@ ptc_counters_reset(ptc_context* ctx)
   return PTC_OK;
 }
 
+uint32_t
+ptc_band_rows(const ptc_render_args* args)
+{
+  FrameParams fp;
+  memset(&fp, 0, sizeof(fp));
+  if (!args || !args->width || !args->height || !band_geometry(args, fp))
+    return 0;
+  return fp.band_rows;
+}
+
+int
+ptc_launch_count(const ptc_context* ctx, uint64_t* out)
+{
+  if (!ctx || !out)
+    return PTC_ERR_INVALID;
+  *out = ctx->launches;
+  return PTC_OK;
+}
+
+int
+ptc_set_wavefront(ptc_context* ctx, uint32_t first_iters, uint32_t next_iters)
+{
+  if (!ctx)
+    return PTC_ERR_INVALID;
+  if (first_iters)
+    ctx->first_iters = first_iters;
+  if (next_iters)
+    ctx->next_iters = next_iters;
+  return PTC_OK;
+}
+
+int
+ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeats, ptc_profile* out)
+{
+  if (!ctx || !out || !repeats)
+    return PTC_ERR_INVALID;
+  DeviceGuard g(ctx->device);
+  memset(out, 0, sizeof(*out));
+  FrameParams fp;
+  int rc = fill_frame(ctx, args, fp, false);
+  if (rc)
+    return rc;
+  if (!args->accum)
+    return fail(ctx, PTC_ERR_INVALID, "accum is required");
+  cudaStream_t s = (cudaStream_t)args->stream;
+  Step steps[kMaxBounces + 1];
+  const int n_steps = frame_schedule(ctx, fp, steps);
+  std::vector<cudaEvent_t> ev((size_t)(n_steps + 1) * repeats);
+  for (cudaEvent_t& e : ev)
+    CUDA_TRY(ctx, cudaEventCreate(&e));
+  // statistics pass (untimed): ray counts and BVH node / triangle visits of this frame
+  Counters before, after;
+  CUDA_TRY(ctx, cudaStreamSynchronize(s));
+  CUDA_TRY(ctx, cudaMemcpy(&before, ctx->ctr, sizeof(before), cudaMemcpyDeviceToHost));
+  rc = enqueue_frame(ctx, args, fp, (float*)args->accum, (uint32_t*)args->out_rgba, nullptr, s, true);
+  if (rc)
+    return rc;
+  CUDA_TRY(ctx, cudaStreamSynchronize(s));
+  CUDA_TRY(ctx, cudaMemcpy(&after, ctx->ctr, sizeof(after), cudaMemcpyDeviceToHost));
+  std::vector<uint32_t> counts(kMaxBounces + 2);
+  CUDA_TRY(ctx, cudaMemcpy(counts.data(), ctx->counts, counts.size() * 4, cudaMemcpyDeviceToHost));
+  out->traced = after.traced - before.traced;
+  out->segments = after.segments - before.segments;
+  out->nodes_visited = after.nodes_visited - before.nodes_visited;
+  out->tris_tested = after.tris_tested - before.tris_tested;
+  for (int i = 0; i < 16; ++i)
+    out->rays_per_bounce[i] = after.rays_per_bounce[i] - before.rays_per_bounce[i];
+  for (int k = 1; k < n_steps; ++k)
+    out->queue_rays += counts[k];
+  out->queue_bytes_per_ray = 4 * sizeof(float4);
+  // timed passes
+  for (uint32_t r = 0; r < repeats; ++r) {
+    rc = enqueue_frame(ctx, args, fp, (float*)args->accum, (uint32_t*)args->out_rgba, nullptr, s, false,
+                       ev.data() + (size_t)r * (n_steps + 1));
+    if (rc)
+      return rc;
+  }
+  CUDA_TRY(ctx, cudaStreamSynchronize(s));
+  out->n_launches = (uint32_t)n_steps;
+  for (int k = 0; k < n_steps && k < 66; ++k) {
+    float sum = 0.f;
+    for (uint32_t r = 0; r < repeats; ++r) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, ev[(size_t)r * (n_steps + 1) + k], ev[(size_t)r * (n_steps + 1) + k + 1]);
+      sum += ms;
+    }
+    out->launch_ms[k] = sum / repeats;
+    out->launch_bounce0[k] = (uint32_t)steps[k].bounce0;
+    out->launch_iters[k] = (uint32_t)steps[k].n_iters;
+  }
+  float total = 0.f;
+  for (uint32_t r = 0; r < repeats; ++r) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ev[(size_t)r * (n_steps + 1)], ev[(size_t)r * (n_steps + 1) + n_steps]);
+    total += ms;
+  }
+  out->frame_ms = total / repeats;
+  for (cudaEvent_t& e : ev)
+    cudaEventDestroy(e);
+  return PTC_OK;
+}
+
 int
 ptc_trace_primary(ptc_context* ctx, int32_t scene_id, const ptc_camera* camera, uint32_t width,
                   uint32_t height, uint32_t frame_nb, int32_t* hit_ids, float* t)
@@ -537,22 +709,21 @@ ptc_trace_primary(ptc_context* ctx, int32_t scene_id, const ptc_camera* camera, 
   fp.width = width;
   fp.height = height;
   fp.row_begin = 0;
-  fp.row_end = height;
+  fp.band_rows = height;
+  fp.strip_rows = 16;
+  fp.strip_stride = 1;
+  fp.tiles_x = (width + kTileW - 1) / kTileW;
   fp.frame_nb = (int)(frame_nb ? frame_nb : 1);
   fp.hash_seed = wang_hash((uint32_t)fp.frame_nb);
   fp.max_bounces = 1;
   fp.is_static = 1;
   const uint32_t n = width * height;
-  int rc = ensure_capacity(ctx, n);
-  if (rc)
-    return rc;
   int32_t* d_ids = nullptr;
   float* d_t = nullptr;
   CUDA_TRY(ctx, cudaMalloc(&d_ids, (size_t)n * 4));
   CUDA_TRY(ctx, cudaMalloc(&d_t, (size_t)n * 4));
-  launch_generate(fp, ctx->st, 0);
-  launch_extend(ctx->scenes[scene_id].d, ctx->st, nullptr, nullptr, n, ctx->ctr, 0, 0);
-  launch_export_primary(ctx->st, n, d_ids, d_t, nullptr, nullptr, 0);
+  launch_primary_hits(fp, ctx->scenes[scene_id].d, d_ids, d_t, 0);
+  ctx->launches++;
   cudaError_t e = cudaDeviceSynchronize();
   if (e == cudaSuccess && hit_ids)
     e = cudaMemcpy(hit_ids, d_ids, (size_t)n * 4, cudaMemcpyDeviceToHost);
@@ -585,6 +756,7 @@ ptc_intersect_rays(ptc_context* ctx, int32_t scene_id, const float* origins, con
     e = cudaMemcpy(d_d, dirs, n * 12, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) {
     launch_intersect_rays(ctx->scenes[scene_id].d, d_o, d_d, n, d_i, d_t, ctx->ctr, 0);
+    ctx->launches++;
     e = cudaDeviceSynchronize();
   }
   if (e == cudaSuccess && hit_ids)

@@ -1,0 +1,287 @@
+// traverse.cuh -- RNG, camera ray generation and closest hit (device functions).
+//
+//   rng_*        cuRAND XORWOW restated (curand_kernel.h:772-799,863-874)
+//   primary_ray  RNG seed + camera ray + depth of field       (raytrace.cu:218-240)
+//   closest_hit  what intersect() computes by brute force (intersection.cuh:161-212),
+//                answered through the 8-wide compressed BVH
+#pragma once
+
+#include "device_types.cuh"
+#include "vecmath.cuh"
+
+namespace ptc {
+
+// ---------------------------------------------------------------------------
+// cuRAND XORWOW, restated (curand_kernel.h:772-799 init with subsequence = offset = 0,
+// :863-874 step, curand_uniform.h:69-72).  State is 6 words, carried per path.
+// ---------------------------------------------------------------------------
+struct Rng
+{
+  uint32_t v0, v1, v2, v3, v4, d;
+};
+
+__device__ __forceinline__ void
+rng_init(Rng& s, uint32_t seed32)
+{
+  uint32_t s0 = seed32 ^ 0xaad26b49u;
+  uint32_t s1 = 0xf7dcefddu; // high seed word is zero: hash_seed + tid wraps in 32 bits
+  uint32_t t0 = 1099087573u * s0;
+  uint32_t t1 = 2591861531u * s1;
+  s.d = 6615241u + t1 + t0;
+  s.v0 = 123456789u + t0;
+  s.v1 = 362436069u ^ t0;
+  s.v2 = 521288629u + t1;
+  s.v3 = 88675123u ^ t1;
+  s.v4 = 5783321u + t0;
+}
+
+__device__ __forceinline__ uint32_t
+rng_next(Rng& s)
+{
+  uint32_t t = s.v0 ^ (s.v0 >> 2);
+  s.v0 = s.v1;
+  s.v1 = s.v2;
+  s.v2 = s.v3;
+  s.v3 = s.v4;
+  s.v4 = (s.v4 ^ (s.v4 << 4)) ^ (t ^ (t << 1));
+  s.d += 362437u;
+  return s.v4 + s.d;
+}
+
+__device__ __forceinline__ float
+rng_uniform(Rng& s)
+{
+  // x * 2^-32 is exact, so the fused and unfused forms agree bit for bit
+  return __fmaf_rn((float)rng_next(s), 2.3283064e-10f, 2.3283064e-10f / 2.0f);
+}
+
+// Advances the generator by n draws (replay instead of storing 24 B of state per ray).
+__device__ __forceinline__ void
+rng_skip(Rng& s, uint32_t n)
+{
+  for (uint32_t k = 0; k < n; ++k)
+    rng_next(s);
+}
+
+// raytrace.cu:227-229 under the reference's launch shape (16x16 blocks,
+// gridDim.x = width/16 + 1, raytrace.cu:315-317) -- independent of OUR launch shape.
+__device__ __forceinline__ uint32_t
+reference_tid(uint32_t x, uint32_t y, uint32_t width)
+{
+  uint32_t gx = width / 16u + 1u;
+  return ((x >> 4) + (y >> 4) * gx) * 256u + (y & 15u) * 16u + (x & 15u);
+}
+
+__device__ __forceinline__ void
+primary_ray(const FrameParams& fp, uint32_t x, uint32_t y, Rng& rng, float3& origin, float3& dir)
+{
+  rng_init(rng, fp.hash_seed + reference_tid(x, y, fp.width));
+
+  // generateRay, intersection.cuh:75-97
+  const int half_w = (int)(fp.width / 2), half_h = (int)(fp.height / 2);
+  const float3 cpos = mk3(fp.cam.position[0], fp.cam.position[1], fp.cam.position[2]);
+  const float3 cdir = mk3(fp.cam.dir[0], fp.cam.dir[1], fp.cam.dir[2]);
+  float screen_dist = half_w / tanf(fp.cam.fov_x * 0.5f);
+  float3 cu = normalize(cross(cdir, mk3(0.0f, -1.0f, 0.0f)));
+  float3 cv = normalize(cross(cu, cdir));
+  cu = cu * -1.0f;
+  float3 screen_pos =
+    cpos + (cdir * screen_dist) + (cu * (float)((int)x - half_w)) + (cv * (float)((int)y - half_h));
+  dir = normalize(screen_pos - cpos);
+  origin = cpos;
+
+  // camera_dof, post_process.cuh:49-67 (the * M_PI is a double multiply on Linux)
+  float3 focal_point = fp.cam.focus_dist * dir;
+  float random_angle = (float)((double)(rng_uniform(rng) * 2.0f) * 3.14159265358979323846);
+  float random_radius = rng_uniform(rng) * fp.cam.aperture;
+  float3 ap = (cosf(random_angle) * cu + sinf(random_angle) * cv) * random_radius;
+  dir = normalize(focal_point - ap);
+  origin = origin + ap;
+}
+
+// Moeller-Trumbore exactly as intersection.cuh:102-135 evaluates it on the device
+// (fma placement per the reference build's SASS); e1/e2 are the reference's v0v1/v0v2.
+// Returns t, or NaN-free "no hit" via the bool.
+__device__ __forceinline__ bool
+tri_test(const float4 t0, const float4 t1, const float4 t2, const float3 o, const float3 d, float& t,
+         float& u_out, float& v_out)
+{
+  const float3 v0 = mk3(t0.x, t0.y, t0.z);
+  const float3 e1 = mk3(t0.w, t1.x, t1.y);
+  const float3 e2 = mk3(t1.z, t1.w, t2.x);
+  const float3 p = cross_ref(d, e2);
+  const float det = dot3_ref(e1, p);
+  if (det < 1e-7f) // == ((double)det < 0.0000001): no float lies between the two constants
+    return false;
+  const float inv_det = __fdividef(1.f, det);
+  const float3 tv = mk3(__fsub_rn(o.x, v0.x), __fsub_rn(o.y, v0.y), __fsub_rn(o.z, v0.z));
+  const float u = __fmul_rn(dot3_ref(tv, p), inv_det);
+  if (u < 0.f || u > 1.f)
+    return false;
+  const float3 q = cross_ref(tv, e1);
+  const float v = __fmul_rn(dot3_ref(d, q), inv_det);
+  if (v < 0.f || __fadd_rn(u, v) > 1.f)
+    return false;
+  t = __fmul_rn(dot3_ref(e2, q), inv_det);
+  u_out = u;
+  v_out = v;
+  return true;
+}
+
+// intersectSphere, intersection.cuh:140-155, including the discarded-ternary
+// behaviour at :152 (t keeps b + disc when both roots fail the epsilon test).
+__device__ __forceinline__ bool
+sphere_test(const ptc_light& L, const float3 o, const float3 d, float& t)
+{
+  const float3 op = mk3(__fsub_rn(L.vec[0], o.x), __fsub_rn(L.vec[1], o.y), __fsub_rn(L.vec[2], o.z));
+  const float b = dot3_ref(op, d);
+  float disc = __fmaf_rn(L.radius, L.radius, __fmaf_rn(b, b, -dot3_ref(op, op)));
+  if (disc < 0.f)
+    return false;
+  disc = __fsqrt_rn(disc);
+  t = __fsub_rn(b, disc);
+  if (!(t > 0.01f))
+    t = __fadd_rn(b, disc);
+  return t != 0.f;
+}
+
+// Quantised plane coordinate q (byte k of w) as the float 1 + q * 2^-15: ONE byte-permute
+// drops the byte into mantissa bits 8..15 of 1.0f -- no int->float conversion (I2F runs on
+// the quarter-rate XU pipe and was 48 instructions per node test).
+__device__ __forceinline__ float
+byte_unit(uint32_t w, int k)
+{
+  return __uint_as_float(__byte_perm(w, 0x3F800000u, 0x7604u | ((uint32_t)k << 4)));
+}
+
+
+// Closest hit with the reference's acceptance rules: triangles front-facing only,
+// 0 < t < best, lowest face index wins equal t (intersection.cuh:110,183-184);
+// then sphere lights with 0 <= t < best in light order (intersection.cuh:199-212).
+//
+// Traversal order never changes the answer (the winner is the lexicographic minimum of
+// (t, face id) and boxes are only culled when strictly farther than the best hit), so the
+// loop is shaped for SIMT convergence instead: every iteration runs AT MOST one triangle
+// test and one 8-wide node test per lane, and a leaf's remaining triangles are deferred on
+// the stack instead of being looped over while the other lanes of the warp idle.
+template <bool STATS>
+__device__ __forceinline__ void
+closest_hit(const DScene& sc, const float3 o, const float3 d, float& best_t, uint32_t& best_id,
+            float& best_u, float& best_v, uint32_t& n_nodes, uint32_t& n_tris)
+{
+  best_t = kMaxDist;
+  best_id = 0xFFFFFFFFu;
+  best_u = best_v = 0.f;
+
+  // guarded reciprocal direction for the (conservative) slab tests only
+  const float eps = 1e-20f;
+  const float3 idir = mk3(1.0f / (fabsf(d.x) > eps ? d.x : copysignf(eps, d.x)),
+                          1.0f / (fabsf(d.y) > eps ? d.y : copysignf(eps, d.y)),
+                          1.0f / (fabsf(d.z) > eps ? d.z : copysignf(eps, d.z)));
+  const uint32_t oct = (d.x < 0.f ? 1u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 4u : 0u);
+  const uint32_t oct_inv = 7u - oct;
+
+  uint2 stack[kStackSize];
+  int sp = 0;
+  uint2 ng = make_uint2(0u, 0x80000000u); // root as a one-entry node group
+  uint2 tg = make_uint2(0u, 0u);          // triangle group: base index, 24-bit mask
+
+  for (;;) {
+    // -- at most one triangle test ------------------------------------------------------
+    if (tg.y) {
+      const uint32_t bit = __ffs(tg.y) - 1u;
+      tg.y &= tg.y - 1u;
+      const float4* tp = sc.tris + (size_t)(tg.x + bit) * kTriVec;
+      const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+      if (STATS)
+        n_tris++;
+      float t, u, v;
+      if (tri_test(t0, t1, t2, o, d, t, u, v)) {
+        const uint32_t fid = __float_as_uint(t2.y);
+        if (t > 0.f && (t < best_t || (t == best_t && fid < best_id))) {
+          best_t = t;
+          best_id = fid;
+          best_u = u;
+          best_v = v;
+        }
+      }
+    }
+
+    // -- at most one node test ------------------------------------------------------------
+    if (ng.y & 0xFF000000u) {
+      const uint32_t bit = 31u - __clz(ng.y);
+      ng.y &= ~(1u << bit);
+      const uint32_t imask = ng.y & 0xFFu;
+      if (ng.y & 0xFF000000u)
+        stack[sp++] = ng;
+      const uint32_t slot = (bit - 24u) ^ oct_inv;
+      const uint32_t rel = __popc(imask & ~(0xFFFFFFFFu << slot));
+      const uint32_t idx = ng.x + rel;
+
+      const uint4* np = sc.nodes + (size_t)idx * kNodeVec;
+      const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3),
+                  n4 = __ldg(np + 4);
+      if (STATS)
+        n_nodes++;
+
+      // plane = origin + q * 2^(e-127);  with v = 1 + q * 2^-15 (byte_unit):
+      //   t = (plane - o) * idir = v * a + b,  a = 2^(e-127+15) * idir,  b = (origin - o) * idir - a
+      // The rounding of b is far inside the pad the builder puts around every triangle box.
+      const float sx = __uint_as_float(((n0.w & 0xFFu) + 15u) << 23);
+      const float sy = __uint_as_float((((n0.w >> 8) & 0xFFu) + 15u) << 23);
+      const float sz = __uint_as_float((((n0.w >> 16) & 0xFFu) + 15u) << 23);
+      const float ax = sx * idir.x, ay = sy * idir.y, az = sz * idir.z;
+      const float bx = (__uint_as_float(n0.x) - o.x) * idir.x - ax;
+      const float by = (__uint_as_float(n0.y) - o.y) * idir.y - ay;
+      const float bz = (__uint_as_float(n0.z) - o.z) * idir.z - az;
+
+      uint32_t hitmask = 0;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const uint32_t meta4 = half ? n1.w : n1.z;
+        const uint32_t lox = half ? n2.y : n2.x, loy = half ? n2.w : n2.z, loz = half ? n3.y : n3.x;
+        const uint32_t hix = half ? n3.w : n3.z, hiy = half ? n4.y : n4.x, hiz = half ? n4.w : n4.z;
+        const uint32_t nx = (oct & 1u) ? hix : lox, fx = (oct & 1u) ? lox : hix;
+        const uint32_t ny = (oct & 2u) ? hiy : loy, fy = (oct & 2u) ? loy : hiy;
+        const uint32_t nz = (oct & 4u) ? hiz : loz, fz = (oct & 4u) ? loz : hiz;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float tnx = fmaf(byte_unit(nx, k), ax, bx), tfx = fmaf(byte_unit(fx, k), ax, bx);
+          const float tny = fmaf(byte_unit(ny, k), ay, by), tfy = fmaf(byte_unit(fy, k), ay, by);
+          const float tnz = fmaf(byte_unit(nz, k), az, bz), tfz = fmaf(byte_unit(fz, k), az, bz);
+          const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
+          const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, best_t));
+          if (tmin <= tmax) {
+            const uint32_t m = (meta4 >> (8 * k)) & 0xFFu;
+            const uint32_t inner = ((m & 0x18u) == 0x18u) ? oct_inv : 0u;
+            hitmask |= (m >> 5) << ((m & 31u) ^ inner);
+          }
+        }
+      }
+      if (tg.y)
+        stack[sp++] = tg; // triangles of the previous leaf group not tested yet: defer
+      ng = make_uint2(n1.x, (hitmask & 0xFF000000u) | (n0.w >> 24));
+      tg = make_uint2(n1.y, hitmask & 0x00FFFFFFu);
+    }
+
+    if (!((ng.y & 0xFF000000u) | tg.y)) {
+      if (sp == 0)
+        break;
+      const uint2 e = stack[--sp];
+      if (e.y & 0xFF000000u)
+        ng = e; // node group (always carries at least one unvisited child)
+      else
+        tg = e; // deferred triangle group
+    }
+  }
+
+  for (uint32_t l = 0; l < sc.n_lights; ++l) {
+    float t;
+    if (sphere_test(sc.lights[l], o, d, t) && t < best_t && t >= 0.f) {
+      best_t = t;
+      best_id = sc.n_faces + l;
+    }
+  }
+}
+
+} // namespace ptc

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define PTC_ABI_VERSION 1
+#define PTC_ABI_VERSION 2
 
 typedef enum ptc_status
 {
@@ -138,6 +138,15 @@ typedef struct ptc_render_args
   void* radiance_out; /* optional float3 per pixel (top-down rows): this frame's
                          un-clamped radiance, for parity tests; may be NULL    */
   void* stream;       /* cudaStream_t; NULL = default stream                  */
+  /* Interleaved image tiles (multi-GPU load balance).  strip_stride <= 1: the contiguous
+   * band [row_begin,row_end) above.  strip_stride > 1: row_begin/row_end must be 0 and this
+   * call renders the strips s = strip_phase, strip_phase + strip_stride, ... where strip s
+   * is rows [s*strip_rows, min((s+1)*strip_rows, height)); the band seen through accum /
+   * out_rgba / radiance_out is those strips stacked top-down (accum bottom-up inside it). */
+  uint32_t strip_rows;   /* 0 -> 16, the reference's block height (raytrace.cu:315) */
+  uint32_t strip_stride;
+  uint32_t strip_phase;
+  uint32_t _pad;
 } ptc_render_args;
 
 typedef struct ptc_counters
@@ -198,6 +207,37 @@ int ptc_reset_accumulation(ptc_context* ctx);
 
 int ptc_counters_get(ptc_context* ctx, ptc_counters* out);
 int ptc_counters_reset(ptc_context* ctx);
+
+/* Number of rows a call with these args renders (band height), or 0 on bad args. */
+uint32_t ptc_band_rows(const ptc_render_args* args);
+
+/* Kernels this context has launched so far (host-side count). */
+int ptc_launch_count(const ptc_context* ctx, uint64_t* out);
+
+/* Wavefront granularity: how many radiance-loop iterations the first stage (generate +
+ * extend + shade) and each later stage run in registers before handing the surviving rays
+ * to the next stage through the compacted queue.  0 keeps the current value.  Results do
+ * not depend on it (tests/test_gpu_parity.py::test_wavefront_granularity_invariance). */
+int ptc_set_wavefront(ptc_context* ctx, uint32_t first_iters, uint32_t next_iters);
+
+/* Measurement: renders the frame described by `args` `repeats` times with CUDA events
+ * around every kernel launch on args->stream (device pointers as for ptc_render), plus one
+ * untimed pass with traversal statistics.  The accumulator receives repeats + 1 samples. */
+typedef struct ptc_profile
+{
+  uint32_t n_launches;        /* kernel launches per frame                            */
+  float launch_ms[66];        /* mean duration of each launch over the repeats        */
+  uint32_t launch_bounce0[66];/* first radiance-loop iteration each launch handles     */
+  uint32_t launch_iters[66];
+  float frame_ms;             /* mean duration of the whole frame (all launches)      */
+  uint64_t traced, segments;  /* per frame                                            */
+  uint64_t nodes_visited, tris_tested; /* per frame, from the statistics pass          */
+  uint64_t rays_per_bounce[16];
+  uint64_t queue_rays;        /* rays written to (and read back from) a queue          */
+  uint32_t queue_bytes_per_ray; /* bytes per queue slot (written once + read once)     */
+} ptc_profile;
+int ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeats,
+                      ptc_profile* out);
 
 /* -- parity / debugging entry points (used by tests, not by a renderer) -------- */
 

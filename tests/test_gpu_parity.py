@@ -480,3 +480,72 @@ def test_scene_info(core):
     assert info.n_faces == 446 and info.n_lights == 3 and info.n_materials == 6 and info.n_textures == 9
     assert info.bvh_node_bytes == 80 and info.tri_bytes == 48 and info.shade_bytes == 80
     assert info.texture_bytes >= 66_000_000
+
+
+# -- wavefront schedule / interleaved tiles ----------------------------------------------------------
+def test_wavefront_granularity_invariance(core):
+    """How many radiance-loop iterations a stage runs in registers before handing its rays to
+    the next stage through the queue must not change a single bit of the result."""
+    import torch
+    L = loaded(core, "indoor_tex")
+    w, h, b = 640, 360, 6
+    results = []
+    try:
+        for first, nxt in [(1, 1), (2, 1), (1, 3), (6, 1), (3, 2)]:
+            core.set_wavefront(first, nxt)
+            acc, out, rad = dev_buffers(w, h)
+            core.reset_counters()
+            for k in (1, 2):
+                core.render(L.sid, L.cid, L.sc, w, h, acc, out, rad, bounces=b, frame_nb=k)
+            torch.cuda.synchronize()
+            c = core.counters()
+            results.append((acc.cpu().numpy(), out.cpu().numpy(), rad.cpu().numpy(), c.segments, c.traced,
+                            [c.rays_per_bounce[i] for i in range(8)]))
+    finally:
+        core.set_wavefront(1, 1)
+    a0 = results[0]
+    for r in results[1:]:
+        assert (bits(r[0]) == bits(a0[0])).all() and (r[1] == a0[1]).all() and (bits(r[2]) == bits(a0[2])).all()
+        assert r[3:] == a0[3:]
+
+
+def test_interleaved_strips_equal_full_frame(core):
+    """Round-robin 16-row strips (multi-GPU load balance): every rank's band, restacked, is
+    bit-identical to the same rows of the single-GPU frame."""
+    import torch
+    L = loaded(core, "indoor_tex")
+    w, h, b = 1920, 1080, 3      # 67.5 strips: the last strip is partial
+    acc, out, rad = dev_buffers(w, h)
+    core.render(L.sid, L.cid, L.sc, w, h, acc, out, rad, bounces=b, frame_nb=2)
+    torch.cuda.synchronize()
+    acc_td = torch.flip(acc, dims=[0])
+    for world in (2, 3, 8):
+        seen = torch.zeros(h, dtype=torch.bool)
+        for rank in range(world):
+            strips = (16, world, rank)
+            bh = core.band_rows(w, h, strips=strips)
+            rows = torch.cat([torch.arange(s * 16, min(s * 16 + 16, h)) for s in range(rank, (h + 15) // 16, world)])
+            assert bh == len(rows)
+            accb, outb, radb = dev_buffers(w, bh)
+            core.render(L.sid, L.cid, L.sc, w, h, accb, outb, radb, bounces=b, frame_nb=2, strips=strips)
+            torch.cuda.synchronize()
+            idx = rows.cuda()
+            assert torch.equal(outb, out[idx])
+            assert torch.equal(radb.view(torch.int32), rad[idx].view(torch.int32))
+            assert torch.equal(torch.flip(accb, dims=[0]).view(torch.int32), acc_td[idx].view(torch.int32))
+            seen[rows] = True
+        assert bool(seen.all())
+
+
+def test_profile_frame_reports_consistent_counts(core):
+    import torch
+    L = loaded(core, "indoor_plain")
+    w, h, b = 640, 360, 3
+    acc, out, _ = dev_buffers(w, h)
+    pr = core.profile_frame(L.sid, L.cid, L.sc, w, h, acc, out, None, bounces=b, frame_nb=1, repeats=3)
+    assert len(pr["launch_ms"]) == 3 and all(ms > 0 for ms in pr["launch_ms"])
+    assert pr["segments"] == w * h * b and w * h <= pr["traced"] <= pr["segments"]
+    assert sum(pr["rays_per_bounce"]) == pr["traced"]
+    assert pr["nodes_visited"] >= pr["traced"] and pr["tris_tested"] > 0
+    assert pr["queue_rays"] == pr["rays_per_bounce"][1] + pr["rays_per_bounce"][2]
+    assert pr["frame_ms"] >= max(pr["launch_ms"])

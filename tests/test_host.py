@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     for s in syms:
         assert hasattr(lib, s), f"{s} declared in include/ptcore.h but not exported"
     assert sorted(P.core.EXPORTS) == syms
-    assert lib.ptc_abi_version() == 1
+    assert lib.ptc_abi_version() == 2
 
 
 def test_record_layouts_match_reference_contract():
@@ -43,16 +43,16 @@ def test_record_layouts_match_reference_contract():
 #include <stdio.h>
 #include <stddef.h>
 #include "ptcore.h"
-int main(void){ printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(ptc_face), sizeof(ptc_material),
+int main(void){ printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(ptc_face), sizeof(ptc_material),
   sizeof(ptc_light), sizeof(ptc_texture), sizeof(ptc_camera), sizeof(ptc_scene_desc),
-  sizeof(ptc_render_args), sizeof(ptc_counters), sizeof(ptc_scene_info)); return 0; }
+  sizeof(ptc_render_args), sizeof(ptc_counters), sizeof(ptc_scene_info), sizeof(ptc_profile)); return 0; }
 '''
     exe = "/tmp/ptc_sizes"
     subprocess.run(["gcc", "-x", "c", "-std=c99", "-I", os.path.join(REPO, "include"), "-", "-o", exe],
                    input=src.encode(), check=True)
     got = [int(x) for x in subprocess.check_output([exe]).split()]
     want = [112, 16, 32, 32, 64, C.sizeof(ps.PtcSceneDesc), C.sizeof(P.core.PtcRenderArgs),
-            C.sizeof(P.core.PtcCounters), C.sizeof(P.core.PtcSceneInfo)]
+            C.sizeof(P.core.PtcCounters), C.sizeof(P.core.PtcSceneInfo), C.sizeof(P.core.PtcProfile)]
     assert got == want
 
 
