@@ -389,7 +389,8 @@ def roofline(P, core, sid, cid, sc, w, h, r0, r1, args, accum, out, stream):
     px = (r1 - r0) * w
     b_bvh = prof["nodes_visited"] * info.bvh_node_bytes + prof["tris_tested"] * info.tri_bytes
     b_shade = prof["traced"] * (info.shade_bytes + 16)
-    b_queue = prof["queue_rays"] * prof["queue_bytes_per_ray"] * 2
+    b_queue = prof["queue_rays"] * (prof["queue_bytes_per_ray"] * 2 + prof["hit_bytes_per_ray"] * 2
+                                    + (32 if prof["hit_bytes_per_ray"] else 0))
     b_fb = px * 28
     nbytes = b_bvh + b_shade + b_queue + b_fb
     k_ms = sum(prof["launch_ms"])
@@ -398,10 +399,10 @@ def roofline(P, core, sid, cid, sc, w, h, r0, r1, args, accum, out, stream):
     fp32_peak = 148 * 128 * 2 * 1965e6 / 1e12
     n = max(1, len(prof["launch_ms"]))
     return {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": None,
-            "peak_source": how, "kernel": "ptc::k_path (extend+shade wavefront step)",
+            "peak_source": how, "kernel": "ptc::k_path + ptc::k_extend (the wavefront stages of one frame)",
             "launches_per_frame": n, "kernel_ms_per_launch": k_ms / n, "kernel_ms_per_frame": k_ms,
             "frame_ms": prof["frame_ms"], "kernel_share_of_frame": k_ms / prof["frame_ms"],
-            "launch_ms": prof["launch_ms"], "launch_iters": prof["launch_iters"],
+            "launch_ms": prof["launch_ms"], "launch_kind": prof["launch_kind"],
             "algorithmic_bytes_per_launch": nbytes / n,
             "algorithmic_bytes_per_frame": {"bvh": b_bvh, "shade": b_shade, "queue": b_queue, "framebuffer": b_fb},
             "nodes_per_ray": prof["nodes_visited"] / max(1, prof["traced"]),

@@ -51,12 +51,13 @@ class PtcSceneInfo(C.Structure):
 
 
 class PtcProfile(C.Structure):
-    _fields_ = [("n_launches", C.c_uint32), ("launch_ms", C.c_float * 66),
-                ("launch_bounce0", C.c_uint32 * 66), ("launch_iters", C.c_uint32 * 66),
+    _fields_ = [("n_launches", C.c_uint32), ("launch_ms", C.c_float * 130),
+                ("launch_kind", C.c_uint32 * 130),
+                ("launch_bounce0", C.c_uint32 * 130), ("launch_iters", C.c_uint32 * 130),
                 ("frame_ms", C.c_float), ("traced", C.c_uint64), ("segments", C.c_uint64),
                 ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
                 ("rays_per_bounce", C.c_uint64 * 16), ("queue_rays", C.c_uint64),
-                ("queue_bytes_per_ray", C.c_uint32)]
+                ("queue_bytes_per_ray", C.c_uint32), ("hit_bytes_per_ray", C.c_uint32)]
 
 
 class PtcHostBvh(C.Structure):
@@ -219,8 +220,9 @@ class Core:
         self._check(self.lib.ptc_launch_count(self.ctx, C.byref(n)), "ptc_launch_count")
         return n.value
 
-    def set_wavefront(self, first_iters=0, next_iters=0):
-        self._check(self.lib.ptc_set_wavefront(self.ctx, C.c_uint32(first_iters), C.c_uint32(next_iters)),
+    def set_wavefront(self, first_iters=0, next_iters=0, split_extend=-1, refill=0):
+        self._check(self.lib.ptc_set_wavefront(self.ctx, C.c_uint32(first_iters), C.c_uint32(next_iters),
+                                               C.c_int32(split_extend), C.c_uint32(refill)),
                     "ptc_set_wavefront")
 
     def profile_frame(self, *args, repeats=5, **kw) -> dict:
@@ -230,13 +232,16 @@ class Core:
         self._check(self.lib.ptc_profile_frame(self.ctx, C.byref(a), C.c_uint32(repeats), C.byref(pr)),
                     "ptc_profile_frame")
         n = pr.n_launches
+        kinds = ["first", "fused", "extend", "shade"]
         return {"launch_ms": [pr.launch_ms[i] for i in range(n)],
+                "launch_kind": [kinds[pr.launch_kind[i]] for i in range(n)],
                 "launch_bounce0": [pr.launch_bounce0[i] for i in range(n)],
                 "launch_iters": [pr.launch_iters[i] for i in range(n)],
                 "frame_ms": pr.frame_ms, "traced": pr.traced, "segments": pr.segments,
                 "nodes_visited": pr.nodes_visited, "tris_tested": pr.tris_tested,
                 "rays_per_bounce": [pr.rays_per_bounce[i] for i in range(16)],
-                "queue_rays": pr.queue_rays, "queue_bytes_per_ray": pr.queue_bytes_per_ray}
+                "queue_rays": pr.queue_rays, "queue_bytes_per_ray": pr.queue_bytes_per_ray,
+                "hit_bytes_per_ray": pr.hit_bytes_per_ray}
 
     def render(self, *args, **kw):
         """Device-pointer render call (accum / out_rgba / radiance_out are device buffers)."""

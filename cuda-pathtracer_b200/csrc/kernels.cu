@@ -27,9 +27,12 @@ warp_sum(uint32_t v)
   return __reduce_add_sync(0xFFFFFFFFu, v);
 }
 
-template <bool FIRST, bool STATS>
+// HITS: the closest triangle hit of every queue slot was already found by k_extend; only the
+// sphere lights are tested here before shading (n_iters must be 1).
+template <bool FIRST, bool STATS, bool HITS>
 __global__ void __launch_bounds__(kBlock, 2)
 k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, const RayQueue qin,
+       const uint4* __restrict__ hits,
        const uint32_t* __restrict__ qin_count, const RayQueue qout, uint32_t* __restrict__ qout_count,
        const FrameOut fo, Counters* __restrict__ ctr, uint32_t* __restrict__ work, const int bounce0,
        const int n_iters)
@@ -119,7 +122,13 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
         if (!done) {
           float t, u, v;
           uint32_t id, segs;
-          closest_hit<STATS>(sc, P.origin, P.dir, t, id, u, v, my_nodes, my_tris);
+          if (HITS) {
+            const uint4 h = hits[i];
+            t = __uint_as_float(h.x), id = h.y, u = __uint_as_float(h.z), v = __uint_as_float(h.w);
+            lights_hit(sc, P.origin, P.dir, t, id);
+          } else {
+            closest_hit<STATS>(sc, P.origin, P.dir, t, id, u, v, my_nodes, my_tris);
+          }
           done = shade_step(fp, sc, cube, P, rng, t, id, u, v, b, segs);
           my_segs += segs;
           my_traced++;
@@ -166,6 +175,64 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
   __syncthreads();
   if (threadIdx.x < 16 && s_rays[threadIdx.x])
     atomicAdd(&ctr->rays_per_bounce[threadIdx.x], (unsigned long long)s_rays[threadIdx.x]);
+}
+
+// ---------------------------------------------------------------------------
+// extend with per-lane refill: incoherent rays need very different numbers of node and
+// triangle tests, so a warp that traverses 32 fixed rays runs at the pace of its slowest
+// lane (measured: 13 of 32 lanes active).  Here a lane that finishes its ray stores the
+// hit and, as soon as `refill` lanes of the warp are idle, the idle lanes pull new rays
+// from the queue (one warp-aggregated atomic), so the traversal loop stays full.
+// ---------------------------------------------------------------------------
+template <bool STATS>
+__global__ void __launch_bounds__(kBlock, 3)
+k_extend(const DScene sc, const RayQueue qin, const uint32_t* __restrict__ qin_count,
+         uint4* __restrict__ hits, uint32_t* __restrict__ work, Counters* __restrict__ ctr,
+         const uint32_t refill)
+{
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t n = *qin_count;
+  uint2 stack[kStackSize];
+  Trav T;
+  bool have = false, exhausted = false;
+  uint32_t slot = 0, my_nodes = 0, my_tris = 0;
+
+  for (;;) {
+    const uint32_t idle = __ballot_sync(0xFFFFFFFFu, !have);
+    if (idle == 0xFFFFFFFFu || (!exhausted && (uint32_t)__popc(idle) >= refill)) {
+      if (!exhausted) {
+        const uint32_t want = (uint32_t)__popc(idle);
+        uint32_t base = 0;
+        if (lane == 0)
+          base = atomicAdd(work, want);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (!have) {
+          const uint32_t mine = base + __popc(idle & ((1u << lane) - 1u));
+          if (mine < n) {
+            const float4 o4 = qin.o[mine], d4 = qin.d[mine];
+            trav_init(T, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
+            slot = mine;
+            have = true;
+          }
+        }
+        exhausted = base + want >= n;
+      }
+      if (!__any_sync(0xFFFFFFFFu, have))
+        break;
+    }
+    if (have && trav_step<STATS>(sc, T, stack, my_nodes, my_tris)) {
+      hits[slot] = make_uint4(__float_as_uint(T.best_t), T.best_id, __float_as_uint(T.best_u),
+                              __float_as_uint(T.best_v));
+      have = false;
+    }
+  }
+  if (STATS) {
+    const uint32_t wn = warp_sum(my_nodes), wt = warp_sum(my_tris);
+    if (lane == 0 && (wn | wt)) {
+      atomicAdd(&ctr->nodes_visited, (unsigned long long)wn);
+      atomicAdd(&ctr->tris_tested, (unsigned long long)wt);
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------
@@ -262,20 +329,42 @@ blocks_for(uint64_t n, uint32_t block)
   return (uint32_t)((n + block - 1) / block);
 }
 
-int
-path_kernel_blocks_per_sm(bool first, bool stats)
+template <bool FIRST, bool STATS, bool HITS>
+static int
+occ()
 {
   int n = 0;
-  const void* f = first ? (stats ? (const void*)k_path<true, true> : (const void*)k_path<true, false>)
-                        : (stats ? (const void*)k_path<false, true> : (const void*)k_path<false, false>);
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, f, kBlock, 0) != cudaSuccess || n < 1)
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_path<FIRST, STATS, HITS>, kBlock, 0) != cudaSuccess || n < 1)
     n = 1;
   return n;
 }
 
+int
+path_kernel_blocks_per_sm(bool first, bool stats, bool pretraced)
+{
+  if (first)
+    return stats ? occ<true, true, false>() : occ<true, false, false>();
+  if (pretraced)
+    return stats ? occ<false, true, true>() : occ<false, false, true>();
+  return stats ? occ<false, true, false>() : occ<false, false, false>();
+}
+
+int
+extend_kernel_blocks_per_sm(bool stats)
+{
+  int n = 0;
+  cudaError_t e = stats ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_extend<true>, kBlock, 0)
+                        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_extend<false>, kBlock, 0);
+  return (e != cudaSuccess || n < 1) ? 1 : n;
+}
+
+#define PTC_LAUNCH_PATH(F, S, H)                                                                   \
+  k_path<F, S, H><<<grid, kBlock, 0, s>>>(fp, sc, cube, qin, hits, qin_count, qout, qout_count, fo, ctr, \
+                                          work, bounce0, n_iters)
+
 void
 launch_path(bool first, bool stats, uint32_t grid, const FrameParams& fp, const DScene& sc,
-            cudaTextureObject_t cube, const RayQueue& qin, const uint32_t* qin_count,
+            cudaTextureObject_t cube, const RayQueue& qin, const uint4* hits, const uint32_t* qin_count,
             const RayQueue& qout, uint32_t* qout_count, const FrameOut& fo, Counters* ctr,
             uint32_t* work, int bounce0, int n_iters, cudaStream_t s)
 {
@@ -283,15 +372,32 @@ launch_path(bool first, bool stats, uint32_t grid, const FrameParams& fp, const 
     return;
   if (first) {
     if (stats)
-      k_path<true, true><<<grid, kBlock, 0, s>>>(fp, sc, cube, qin, qin_count, qout, qout_count, fo, ctr, work, bounce0, n_iters);
+      PTC_LAUNCH_PATH(true, true, false);
     else
-      k_path<true, false><<<grid, kBlock, 0, s>>>(fp, sc, cube, qin, qin_count, qout, qout_count, fo, ctr, work, bounce0, n_iters);
+      PTC_LAUNCH_PATH(true, false, false);
+  } else if (hits) {
+    if (stats)
+      PTC_LAUNCH_PATH(false, true, true);
+    else
+      PTC_LAUNCH_PATH(false, false, true);
   } else {
     if (stats)
-      k_path<false, true><<<grid, kBlock, 0, s>>>(fp, sc, cube, qin, qin_count, qout, qout_count, fo, ctr, work, bounce0, n_iters);
+      PTC_LAUNCH_PATH(false, true, false);
     else
-      k_path<false, false><<<grid, kBlock, 0, s>>>(fp, sc, cube, qin, qin_count, qout, qout_count, fo, ctr, work, bounce0, n_iters);
+      PTC_LAUNCH_PATH(false, false, false);
   }
+}
+
+void
+launch_extend(bool stats, uint32_t grid, const DScene& sc, const RayQueue& qin, const uint32_t* qin_count,
+              uint4* hits, uint32_t* work, Counters* ctr, uint32_t refill, cudaStream_t s)
+{
+  if (!grid)
+    return;
+  if (stats)
+    k_extend<true><<<grid, kBlock, 0, s>>>(sc, qin, qin_count, hits, work, ctr, refill);
+  else
+    k_extend<false><<<grid, kBlock, 0, s>>>(sc, qin, qin_count, hits, work, ctr, refill);
 }
 
 void

@@ -5,17 +5,26 @@
 
 namespace ptc {
 
-// resident CTAs per SM of k_path<first, stats> (sizes the persistent grid)
-int path_kernel_blocks_per_sm(bool first, bool stats);
+// resident CTAs per SM of the path / extend kernels (size the persistent grids)
+int path_kernel_blocks_per_sm(bool first, bool stats, bool pretraced);
+int extend_kernel_blocks_per_sm(bool stats);
 
 // One wavefront step: `n_iters` x [extend -> shade] starting at radiance-loop iteration
 // `bounce0`.  first: rays are generated (8x4 pixel tile per warp) instead of read from
 // `qin`; survivors are appended to `qout` / `qout_count`.  `work` is a zeroed counter the
-// persistent warps pull their work items from.
+// persistent warps pull their work items from.  hits != null: the triangle hits of `qin`
+// were already found by launch_extend (n_iters must be 1).
 void launch_path(bool first, bool stats, uint32_t grid, const FrameParams& fp, const DScene& sc,
-                 cudaTextureObject_t cube, const RayQueue& qin, const uint32_t* qin_count,
-                 const RayQueue& qout, uint32_t* qout_count, const FrameOut& fo, Counters* ctr,
-                 uint32_t* work, int bounce0, int n_iters, cudaStream_t s);
+                 cudaTextureObject_t cube, const RayQueue& qin, const uint4* hits,
+                 const uint32_t* qin_count, const RayQueue& qout, uint32_t* qout_count,
+                 const FrameOut& fo, Counters* ctr, uint32_t* work, int bounce0, int n_iters,
+                 cudaStream_t s);
+
+// Closest triangle hit of every ray of `qin` -> hits[slot] = (t, face id | ~0, u, v), with
+// per-lane refill once `refill` lanes of a warp are idle.
+void launch_extend(bool stats, uint32_t grid, const DScene& sc, const RayQueue& qin,
+                   const uint32_t* qin_count, uint4* hits, uint32_t* work, Counters* ctr,
+                   uint32_t refill, cudaStream_t s);
 
 void launch_primary_hits(const FrameParams& fp, const DScene& sc, int32_t* ids, float* ts,
                          cudaStream_t s);

@@ -45,8 +45,12 @@ struct ptc_context
   uint32_t* counts = nullptr;  // one queue counter per wavefront step
   Counters* ctr = nullptr;
   int n_sms = 148;
-  int grid_first = 0, grid_next = 0, grid_first_stats = 0, grid_next_stats = 0;
+  // persistent grids, [stats]: first stage, fused later stage, shade-after-extend, extend
+  int grid_first[2] = { 0, 0 }, grid_next[2] = { 0, 0 }, grid_shade[2] = { 0, 0 }, grid_extend[2] = { 0, 0 };
   uint32_t first_iters = 1, next_iters = 1; // wavefront granularity (ptc_set_wavefront)
+  uint32_t split_extend = 1;   // later stages: separate refilling extend kernel + shade kernel
+  uint32_t refill = 8;         // idle lanes of a warp that trigger a refill in k_extend
+  uint4* hits = nullptr;       // closest triangle hit per queue slot (split stages)
   uint64_t launches = 0;
   uint32_t seed = 0;           // the reference's function-static frame counter (raytrace.cu:296)
   // staging for ptc_render_host
@@ -60,7 +64,7 @@ struct ptc_context
 namespace {
 
 constexpr int kMaxBounces = 64;
-constexpr int kCountSlots = 2 * (kMaxBounces + 2); // queue counters, then work counters
+constexpr int kCountSlots = 3 * (kMaxBounces + 2); // queue counters, then 2 work counters per step
 
 int
 fail(ptc_context* ctx, int code, const std::string& msg)
@@ -119,6 +123,8 @@ free_state(ptc_context* ctx)
     cudaFree(q.acc);
     q = RayQueue{};
   }
+  cudaFree(ctx->hits);
+  ctx->hits = nullptr;
   ctx->capacity = 0;
 }
 
@@ -134,6 +140,7 @@ ensure_capacity(ptc_context* ctx, uint32_t n)
     CUDA_TRY(ctx, cudaMalloc(&q.thr, (size_t)n * sizeof(float4)));
     CUDA_TRY(ctx, cudaMalloc(&q.acc, (size_t)n * sizeof(float4)));
   }
+  CUDA_TRY(ctx, cudaMalloc(&ctx->hits, (size_t)n * sizeof(uint4)));
   ctx->capacity = n;
   return 0;
 }
@@ -242,6 +249,8 @@ frame_schedule(const ptc_context* ctx, const FrameParams& fp, Step* steps)
   steps[n++] = Step{ true, 0, b };
   while (b < fp.max_bounces) {
     int k = (int)ctx->next_iters < fp.max_bounces - b ? (int)ctx->next_iters : fp.max_bounces - b;
+    if (ctx->split_extend)
+      k = 1;
     steps[n++] = Step{ false, b, k };
     b += k;
   }
@@ -264,25 +273,35 @@ enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp,
   Step steps[kMaxBounces + 1];
   const int n_steps = frame_schedule(ctx, fp, steps);
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->counts, 0, sizeof(uint32_t) * kCountSlots, s));
+  int n_ev = 0;
   if (ev)
     CUDA_TRY(ctx, cudaEventRecord(ev[0], s));
   const uint32_t tiles = fp.tiles_x * ((fp.band_rows + kTileH - 1) / kTileH);
   for (int k = 0; k < n_steps; ++k) {
     const Step& st = steps[k];
     uint32_t grid;
+    const uint4* hits = nullptr;
+    uint32_t* work = ctx->counts + kMaxBounces + 2 + 2 * k;
     if (st.first) {
       const uint32_t want = (tiles + kBlock / 32 - 1) / (kBlock / 32);
-      const uint32_t cap = (uint32_t)(stats ? ctx->grid_first_stats : ctx->grid_first);
+      const uint32_t cap = (uint32_t)ctx->grid_first[stats];
       grid = want < cap ? want : cap;
+    } else if (ctx->split_extend) {
+      launch_extend(stats, (uint32_t)ctx->grid_extend[stats], sc.d, ctx->queue[k & 1], ctx->counts + k,
+                    ctx->hits, work + 1, ctx->ctr, ctx->refill, s);
+      ctx->launches++;
+      if (ev)
+        CUDA_TRY(ctx, cudaEventRecord(ev[++n_ev], s));
+      hits = ctx->hits;
+      grid = (uint32_t)ctx->grid_shade[stats];
     } else {
-      grid = (uint32_t)(stats ? ctx->grid_next_stats : ctx->grid_next);
+      grid = (uint32_t)ctx->grid_next[stats];
     }
-    launch_path(st.first, stats, grid, fp, sc.d, cm.tex, ctx->queue[k & 1], ctx->counts + k,
-                ctx->queue[(k + 1) & 1], ctx->counts + k + 1, fo, ctx->ctr,
-                ctx->counts + kMaxBounces + 2 + k, st.bounce0, st.n_iters, s);
+    launch_path(st.first, stats, grid, fp, sc.d, cm.tex, ctx->queue[k & 1], hits, ctx->counts + k,
+                ctx->queue[(k + 1) & 1], ctx->counts + k + 1, fo, ctx->ctr, work, st.bounce0, st.n_iters, s);
     ctx->launches++;
     if (ev)
-      CUDA_TRY(ctx, cudaEventRecord(ev[k + 1], s));
+      CUDA_TRY(ctx, cudaEventRecord(ev[++n_ev], s));
   }
   CUDA_TRY(ctx, cudaGetLastError());
   return 0;
@@ -321,10 +340,12 @@ ptc_create(int device, ptc_context** out)
   cudaMemset(ctx->counts, 0, sizeof(uint32_t) * kCountSlots);
   cudaDeviceGetAttribute(&ctx->n_sms, cudaDevAttrMultiProcessorCount, device);
   // persistent grids: resident CTAs per SM x SMs (148 on B200)
-  ctx->grid_first = ctx->n_sms * path_kernel_blocks_per_sm(true, false);
-  ctx->grid_next = ctx->n_sms * path_kernel_blocks_per_sm(false, false);
-  ctx->grid_first_stats = ctx->n_sms * path_kernel_blocks_per_sm(true, true);
-  ctx->grid_next_stats = ctx->n_sms * path_kernel_blocks_per_sm(false, true);
+  for (int st = 0; st < 2; ++st) {
+    ctx->grid_first[st] = ctx->n_sms * path_kernel_blocks_per_sm(true, st != 0, false);
+    ctx->grid_next[st] = ctx->n_sms * path_kernel_blocks_per_sm(false, st != 0, false);
+    ctx->grid_shade[st] = ctx->n_sms * path_kernel_blocks_per_sm(false, st != 0, true);
+    ctx->grid_extend[st] = ctx->n_sms * extend_kernel_blocks_per_sm(st != 0);
+  }
   *out = ctx;
   return PTC_OK;
 }
@@ -614,10 +635,15 @@ ptc_launch_count(const ptc_context* ctx, uint64_t* out)
 }
 
 int
-ptc_set_wavefront(ptc_context* ctx, uint32_t first_iters, uint32_t next_iters)
+ptc_set_wavefront(ptc_context* ctx, uint32_t first_iters, uint32_t next_iters, int32_t split_extend,
+                  uint32_t refill)
 {
   if (!ctx)
     return PTC_ERR_INVALID;
+  if (split_extend >= 0)
+    ctx->split_extend = split_extend ? 1u : 0u;
+  if (refill)
+    ctx->refill = refill > 32 ? 32 : refill;
   if (first_iters)
     ctx->first_iters = first_iters;
   if (next_iters)
@@ -641,7 +667,20 @@ ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeat
   cudaStream_t s = (cudaStream_t)args->stream;
   Step steps[kMaxBounces + 1];
   const int n_steps = frame_schedule(ctx, fp, steps);
-  std::vector<cudaEvent_t> ev((size_t)(n_steps + 1) * repeats);
+  // the launches of one frame: kind 0 = first stage, 1 = fused later stage, 2 = extend, 3 = shade
+  struct L { uint32_t kind, bounce0, iters; };
+  std::vector<L> launches;
+  for (int k = 0; k < n_steps; ++k) {
+    if (steps[k].first)
+      launches.push_back({ 0u, 0u, (uint32_t)steps[k].n_iters });
+    else if (ctx->split_extend) {
+      launches.push_back({ 2u, (uint32_t)steps[k].bounce0, 1u });
+      launches.push_back({ 3u, (uint32_t)steps[k].bounce0, 1u });
+    } else
+      launches.push_back({ 1u, (uint32_t)steps[k].bounce0, (uint32_t)steps[k].n_iters });
+  }
+  const int n_l = (int)launches.size();
+  std::vector<cudaEvent_t> ev((size_t)(n_l + 1) * repeats);
   for (cudaEvent_t& e : ev)
     CUDA_TRY(ctx, cudaEventCreate(&e));
   // statistics pass (untimed): ray counts and BVH node / triangle visits of this frame
@@ -664,30 +703,32 @@ ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeat
   for (int k = 1; k < n_steps; ++k)
     out->queue_rays += counts[k];
   out->queue_bytes_per_ray = 4 * sizeof(float4);
+  out->hit_bytes_per_ray = ctx->split_extend ? (uint32_t)sizeof(uint4) : 0u;
   // timed passes
   for (uint32_t r = 0; r < repeats; ++r) {
     rc = enqueue_frame(ctx, args, fp, (float*)args->accum, (uint32_t*)args->out_rgba, nullptr, s, false,
-                       ev.data() + (size_t)r * (n_steps + 1));
+                       ev.data() + (size_t)r * (n_l + 1));
     if (rc)
       return rc;
   }
   CUDA_TRY(ctx, cudaStreamSynchronize(s));
-  out->n_launches = (uint32_t)n_steps;
-  for (int k = 0; k < n_steps && k < 66; ++k) {
+  out->n_launches = (uint32_t)(n_l < 130 ? n_l : 130);
+  for (int k = 0; k < n_l && k < 130; ++k) {
     float sum = 0.f;
     for (uint32_t r = 0; r < repeats; ++r) {
       float ms = 0.f;
-      cudaEventElapsedTime(&ms, ev[(size_t)r * (n_steps + 1) + k], ev[(size_t)r * (n_steps + 1) + k + 1]);
+      cudaEventElapsedTime(&ms, ev[(size_t)r * (n_l + 1) + k], ev[(size_t)r * (n_l + 1) + k + 1]);
       sum += ms;
     }
     out->launch_ms[k] = sum / repeats;
-    out->launch_bounce0[k] = (uint32_t)steps[k].bounce0;
-    out->launch_iters[k] = (uint32_t)steps[k].n_iters;
+    out->launch_kind[k] = launches[k].kind;
+    out->launch_bounce0[k] = launches[k].bounce0;
+    out->launch_iters[k] = launches[k].iters;
   }
   float total = 0.f;
   for (uint32_t r = 0; r < repeats; ++r) {
     float ms = 0.f;
-    cudaEventElapsedTime(&ms, ev[(size_t)r * (n_steps + 1)], ev[(size_t)r * (n_steps + 1) + n_steps]);
+    cudaEventElapsedTime(&ms, ev[(size_t)r * (n_l + 1)], ev[(size_t)r * (n_l + 1) + n_l]);
     total += ms;
   }
   out->frame_ms = total / repeats;

@@ -155,126 +155,143 @@ byte_unit(uint32_t w, int k)
 }
 
 
-// Closest hit with the reference's acceptance rules: triangles front-facing only,
-// 0 < t < best, lowest face index wins equal t (intersection.cuh:110,183-184);
-// then sphere lights with 0 <= t < best in light order (intersection.cuh:199-212).
+// Traversal state of one ray (registers; the stack lives in local memory, L1-resident).
+struct Trav
+{
+  float3 o, d, idir;
+  uint32_t oct, oct_inv;
+  uint2 ng; // node group: first child index, 8 hit bits (31..24) | imask (7..0)
+  uint2 tg; // triangle group: base index, 24-bit mask
+  int sp;
+  float best_t, best_u, best_v;
+  uint32_t best_id;
+};
+
+__device__ __forceinline__ void
+trav_init(Trav& T, const float3 o, const float3 d)
+{
+  T.o = o;
+  T.d = d;
+  T.best_t = kMaxDist;
+  T.best_id = 0xFFFFFFFFu;
+  T.best_u = T.best_v = 0.f;
+  // guarded reciprocal direction for the (conservative) slab tests only
+  const float eps = 1e-20f;
+  T.idir = mk3(1.0f / (fabsf(d.x) > eps ? d.x : copysignf(eps, d.x)),
+               1.0f / (fabsf(d.y) > eps ? d.y : copysignf(eps, d.y)),
+               1.0f / (fabsf(d.z) > eps ? d.z : copysignf(eps, d.z)));
+  T.oct = (d.x < 0.f ? 1u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 4u : 0u);
+  T.oct_inv = 7u - T.oct;
+  T.sp = 0;
+  T.ng = make_uint2(0u, 0x80000000u); // root as a one-entry node group
+  T.tg = make_uint2(0u, 0u);
+}
+
+// One traversal iteration: AT MOST one triangle test and one 8-wide node test.  Returns
+// true when the ray has nothing left to visit.
 //
 // Traversal order never changes the answer (the winner is the lexicographic minimum of
 // (t, face id) and boxes are only culled when strictly farther than the best hit), so the
-// loop is shaped for SIMT convergence instead: every iteration runs AT MOST one triangle
-// test and one 8-wide node test per lane, and a leaf's remaining triangles are deferred on
-// the stack instead of being looped over while the other lanes of the warp idle.
+// loop is shaped for SIMT convergence: a leaf's remaining triangles are deferred on the
+// stack instead of being looped over while the other lanes of the warp idle.
 template <bool STATS>
-__device__ __forceinline__ void
-closest_hit(const DScene& sc, const float3 o, const float3 d, float& best_t, uint32_t& best_id,
-            float& best_u, float& best_v, uint32_t& n_nodes, uint32_t& n_tris)
+__device__ __forceinline__ bool
+trav_step(const DScene& sc, Trav& T, uint2* stack, uint32_t& n_nodes, uint32_t& n_tris)
 {
-  best_t = kMaxDist;
-  best_id = 0xFFFFFFFFu;
-  best_u = best_v = 0.f;
-
-  // guarded reciprocal direction for the (conservative) slab tests only
-  const float eps = 1e-20f;
-  const float3 idir = mk3(1.0f / (fabsf(d.x) > eps ? d.x : copysignf(eps, d.x)),
-                          1.0f / (fabsf(d.y) > eps ? d.y : copysignf(eps, d.y)),
-                          1.0f / (fabsf(d.z) > eps ? d.z : copysignf(eps, d.z)));
-  const uint32_t oct = (d.x < 0.f ? 1u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 4u : 0u);
-  const uint32_t oct_inv = 7u - oct;
-
-  uint2 stack[kStackSize];
-  int sp = 0;
-  uint2 ng = make_uint2(0u, 0x80000000u); // root as a one-entry node group
-  uint2 tg = make_uint2(0u, 0u);          // triangle group: base index, 24-bit mask
-
-  for (;;) {
-    // -- at most one triangle test ------------------------------------------------------
-    if (tg.y) {
-      const uint32_t bit = __ffs(tg.y) - 1u;
-      tg.y &= tg.y - 1u;
-      const float4* tp = sc.tris + (size_t)(tg.x + bit) * kTriVec;
-      const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
-      if (STATS)
-        n_tris++;
-      float t, u, v;
-      if (tri_test(t0, t1, t2, o, d, t, u, v)) {
-        const uint32_t fid = __float_as_uint(t2.y);
-        if (t > 0.f && (t < best_t || (t == best_t && fid < best_id))) {
-          best_t = t;
-          best_id = fid;
-          best_u = u;
-          best_v = v;
-        }
+  // -- at most one triangle test ------------------------------------------------------
+  if (T.tg.y) {
+    const uint32_t bit = __ffs(T.tg.y) - 1u;
+    T.tg.y &= T.tg.y - 1u;
+    const float4* tp = sc.tris + (size_t)(T.tg.x + bit) * kTriVec;
+    const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+    if (STATS)
+      n_tris++;
+    float t, u, v;
+    if (tri_test(t0, t1, t2, T.o, T.d, t, u, v)) {
+      const uint32_t fid = __float_as_uint(t2.y);
+      if (t > 0.f && (t < T.best_t || (t == T.best_t && fid < T.best_id))) {
+        T.best_t = t;
+        T.best_id = fid;
+        T.best_u = u;
+        T.best_v = v;
       }
-    }
-
-    // -- at most one node test ------------------------------------------------------------
-    if (ng.y & 0xFF000000u) {
-      const uint32_t bit = 31u - __clz(ng.y);
-      ng.y &= ~(1u << bit);
-      const uint32_t imask = ng.y & 0xFFu;
-      if (ng.y & 0xFF000000u)
-        stack[sp++] = ng;
-      const uint32_t slot = (bit - 24u) ^ oct_inv;
-      const uint32_t rel = __popc(imask & ~(0xFFFFFFFFu << slot));
-      const uint32_t idx = ng.x + rel;
-
-      const uint4* np = sc.nodes + (size_t)idx * kNodeVec;
-      const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3),
-                  n4 = __ldg(np + 4);
-      if (STATS)
-        n_nodes++;
-
-      // plane = origin + q * 2^(e-127);  with v = 1 + q * 2^-15 (byte_unit):
-      //   t = (plane - o) * idir = v * a + b,  a = 2^(e-127+15) * idir,  b = (origin - o) * idir - a
-      // The rounding of b is far inside the pad the builder puts around every triangle box.
-      const float sx = __uint_as_float(((n0.w & 0xFFu) + 15u) << 23);
-      const float sy = __uint_as_float((((n0.w >> 8) & 0xFFu) + 15u) << 23);
-      const float sz = __uint_as_float((((n0.w >> 16) & 0xFFu) + 15u) << 23);
-      const float ax = sx * idir.x, ay = sy * idir.y, az = sz * idir.z;
-      const float bx = (__uint_as_float(n0.x) - o.x) * idir.x - ax;
-      const float by = (__uint_as_float(n0.y) - o.y) * idir.y - ay;
-      const float bz = (__uint_as_float(n0.z) - o.z) * idir.z - az;
-
-      uint32_t hitmask = 0;
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        const uint32_t meta4 = half ? n1.w : n1.z;
-        const uint32_t lox = half ? n2.y : n2.x, loy = half ? n2.w : n2.z, loz = half ? n3.y : n3.x;
-        const uint32_t hix = half ? n3.w : n3.z, hiy = half ? n4.y : n4.x, hiz = half ? n4.w : n4.z;
-        const uint32_t nx = (oct & 1u) ? hix : lox, fx = (oct & 1u) ? lox : hix;
-        const uint32_t ny = (oct & 2u) ? hiy : loy, fy = (oct & 2u) ? loy : hiy;
-        const uint32_t nz = (oct & 4u) ? hiz : loz, fz = (oct & 4u) ? loz : hiz;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const float tnx = fmaf(byte_unit(nx, k), ax, bx), tfx = fmaf(byte_unit(fx, k), ax, bx);
-          const float tny = fmaf(byte_unit(ny, k), ay, by), tfy = fmaf(byte_unit(fy, k), ay, by);
-          const float tnz = fmaf(byte_unit(nz, k), az, bz), tfz = fmaf(byte_unit(fz, k), az, bz);
-          const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
-          const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, best_t));
-          if (tmin <= tmax) {
-            const uint32_t m = (meta4 >> (8 * k)) & 0xFFu;
-            const uint32_t inner = ((m & 0x18u) == 0x18u) ? oct_inv : 0u;
-            hitmask |= (m >> 5) << ((m & 31u) ^ inner);
-          }
-        }
-      }
-      if (tg.y)
-        stack[sp++] = tg; // triangles of the previous leaf group not tested yet: defer
-      ng = make_uint2(n1.x, (hitmask & 0xFF000000u) | (n0.w >> 24));
-      tg = make_uint2(n1.y, hitmask & 0x00FFFFFFu);
-    }
-
-    if (!((ng.y & 0xFF000000u) | tg.y)) {
-      if (sp == 0)
-        break;
-      const uint2 e = stack[--sp];
-      if (e.y & 0xFF000000u)
-        ng = e; // node group (always carries at least one unvisited child)
-      else
-        tg = e; // deferred triangle group
     }
   }
 
+  // -- at most one node test ------------------------------------------------------------
+  if (T.ng.y & 0xFF000000u) {
+    const uint32_t bit = 31u - __clz(T.ng.y);
+    T.ng.y &= ~(1u << bit);
+    const uint32_t imask = T.ng.y & 0xFFu;
+    if (T.ng.y & 0xFF000000u)
+      stack[T.sp++] = T.ng;
+    const uint32_t slot = (bit - 24u) ^ T.oct_inv;
+    const uint32_t rel = __popc(imask & ~(0xFFFFFFFFu << slot));
+    const uint32_t idx = T.ng.x + rel;
+
+    const uint4* np = sc.nodes + (size_t)idx * kNodeVec;
+    const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3),
+                n4 = __ldg(np + 4);
+    if (STATS)
+      n_nodes++;
+
+    // plane = origin + q * 2^(e-127);  with v = 1 + q * 2^-15 (byte_unit):
+    //   t = (plane - o) * T.idir = v * a + b,  a = 2^(e-127+15) * T.idir,  b = (origin - o) * T.idir - a
+    // The rounding of b is far inside the pad the builder puts around every triangle box.
+    const float sx = __uint_as_float(((n0.w & 0xFFu) + 15u) << 23);
+    const float sy = __uint_as_float((((n0.w >> 8) & 0xFFu) + 15u) << 23);
+    const float sz = __uint_as_float((((n0.w >> 16) & 0xFFu) + 15u) << 23);
+    const float ax = sx * T.idir.x, ay = sy * T.idir.y, az = sz * T.idir.z;
+    const float bx = (__uint_as_float(n0.x) - T.o.x) * T.idir.x - ax;
+    const float by = (__uint_as_float(n0.y) - T.o.y) * T.idir.y - ay;
+    const float bz = (__uint_as_float(n0.z) - T.o.z) * T.idir.z - az;
+
+    uint32_t hitmask = 0;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const uint32_t meta4 = half ? n1.w : n1.z;
+      const uint32_t lox = half ? n2.y : n2.x, loy = half ? n2.w : n2.z, loz = half ? n3.y : n3.x;
+      const uint32_t hix = half ? n3.w : n3.z, hiy = half ? n4.y : n4.x, hiz = half ? n4.w : n4.z;
+      const uint32_t nx = (T.oct & 1u) ? hix : lox, fx = (T.oct & 1u) ? lox : hix;
+      const uint32_t ny = (T.oct & 2u) ? hiy : loy, fy = (T.oct & 2u) ? loy : hiy;
+      const uint32_t nz = (T.oct & 4u) ? hiz : loz, fz = (T.oct & 4u) ? loz : hiz;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float tnx = fmaf(byte_unit(nx, k), ax, bx), tfx = fmaf(byte_unit(fx, k), ax, bx);
+        const float tny = fmaf(byte_unit(ny, k), ay, by), tfy = fmaf(byte_unit(fy, k), ay, by);
+        const float tnz = fmaf(byte_unit(nz, k), az, bz), tfz = fmaf(byte_unit(fz, k), az, bz);
+        const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
+        const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, T.best_t));
+        if (tmin <= tmax) {
+          const uint32_t m = (meta4 >> (8 * k)) & 0xFFu;
+          const uint32_t inner = ((m & 0x18u) == 0x18u) ? T.oct_inv : 0u;
+          hitmask |= (m >> 5) << ((m & 31u) ^ inner);
+        }
+      }
+    }
+    if (T.tg.y)
+      stack[T.sp++] = T.tg; // triangles of the previous leaf group not tested yet: defer
+    T.ng = make_uint2(n1.x, (hitmask & 0xFF000000u) | (n0.w >> 24));
+    T.tg = make_uint2(n1.y, hitmask & 0x00FFFFFFu);
+  }
+
+
+  if (!((T.ng.y & 0xFF000000u) | T.tg.y)) {
+    if (T.sp == 0)
+      return true;
+    const uint2 e = stack[--T.sp];
+    if (e.y & 0xFF000000u)
+      T.ng = e; // node group (always carries at least one unvisited child)
+    else
+      T.tg = e; // deferred triangle group
+  }
+  return false;
+}
+
+// Sphere lights after the triangles, 0 <= t < best in light order (intersection.cuh:199-212).
+__device__ __forceinline__ void
+lights_hit(const DScene& sc, const float3 o, const float3 d, float& best_t, uint32_t& best_id)
+{
   for (uint32_t l = 0; l < sc.n_lights; ++l) {
     float t;
     if (sphere_test(sc.lights[l], o, d, t) && t < best_t && t >= 0.f) {
@@ -282,6 +299,23 @@ closest_hit(const DScene& sc, const float3 o, const float3 d, float& best_t, uin
       best_id = sc.n_faces + l;
     }
   }
+}
+
+// Closest hit with the reference's acceptance rules: triangles front-facing only,
+// 0 < t < best, lowest face index wins equal t (intersection.cuh:110,183-184); then the
+// sphere lights.
+template <bool STATS>
+__device__ __forceinline__ void
+closest_hit(const DScene& sc, const float3 o, const float3 d, float& best_t, uint32_t& best_id,
+            float& best_u, float& best_v, uint32_t& n_nodes, uint32_t& n_tris)
+{
+  Trav T;
+  uint2 stack[kStackSize];
+  trav_init(T, o, d);
+  while (!trav_step<STATS>(sc, T, stack, n_nodes, n_tris)) {
+  }
+  best_t = T.best_t, best_id = T.best_id, best_u = T.best_u, best_v = T.best_v;
+  lights_hit(sc, o, d, best_t, best_id);
 }
 
 } // namespace ptc

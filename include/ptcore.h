@@ -214,11 +214,16 @@ uint32_t ptc_band_rows(const ptc_render_args* args);
 /* Kernels this context has launched so far (host-side count). */
 int ptc_launch_count(const ptc_context* ctx, uint64_t* out);
 
-/* Wavefront granularity: how many radiance-loop iterations the first stage (generate +
- * extend + shade) and each later stage run in registers before handing the surviving rays
- * to the next stage through the compacted queue.  0 keeps the current value.  Results do
- * not depend on it (tests/test_gpu_parity.py::test_wavefront_granularity_invariance). */
-int ptc_set_wavefront(ptc_context* ctx, uint32_t first_iters, uint32_t next_iters);
+/* Wavefront schedule.  first_iters / next_iters: how many radiance-loop iterations the first
+ * stage (generate + extend + shade) and each later stage run in registers before handing the
+ * surviving rays to the next stage through the compacted queue (0 keeps the current value).
+ * split_extend: 1 = every later stage is an extend kernel with per-lane refill followed by
+ * a shade kernel (one iteration per stage; default), 0 = fused extend+shade, < 0 keeps.
+ * refill: idle lanes per warp that trigger a refill in the extend kernel (0 keeps).
+ * Results do not depend on any of it
+ * (tests/test_gpu_parity.py::test_wavefront_granularity_invariance). */
+int ptc_set_wavefront(ptc_context* ctx, uint32_t first_iters, uint32_t next_iters,
+                      int32_t split_extend, uint32_t refill);
 
 /* Measurement: renders the frame described by `args` `repeats` times with CUDA events
  * around every kernel launch on args->stream (device pointers as for ptc_render), plus one
@@ -226,15 +231,18 @@ int ptc_set_wavefront(ptc_context* ctx, uint32_t first_iters, uint32_t next_iter
 typedef struct ptc_profile
 {
   uint32_t n_launches;        /* kernel launches per frame                            */
-  float launch_ms[66];        /* mean duration of each launch over the repeats        */
-  uint32_t launch_bounce0[66];/* first radiance-loop iteration each launch handles     */
-  uint32_t launch_iters[66];
+  float launch_ms[130];       /* mean duration of each launch over the repeats        */
+  uint32_t launch_kind[130];  /* 0 first stage (generate+extend+shade), 1 fused later
+                                 stage, 2 extend (refilling traversal), 3 shade        */
+  uint32_t launch_bounce0[130];/* first radiance-loop iteration each launch handles    */
+  uint32_t launch_iters[130];
   float frame_ms;             /* mean duration of the whole frame (all launches)      */
   uint64_t traced, segments;  /* per frame                                            */
   uint64_t nodes_visited, tris_tested; /* per frame, from the statistics pass          */
   uint64_t rays_per_bounce[16];
   uint64_t queue_rays;        /* rays written to (and read back from) a queue          */
   uint32_t queue_bytes_per_ray; /* bytes per queue slot (written once + read once)     */
+  uint32_t hit_bytes_per_ray; /* hit record between extend and shade (0 when fused)    */
 } ptc_profile;
 int ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeats,
                       ptc_profile* out);
