@@ -12,9 +12,12 @@ constexpr float kMaxDist = 100000.0f; // MAX_DIST, intersection.cuh:165
 constexpr int kNodeVec = 5;           // uint4 per Node8
 constexpr int kTriVec = 3;            // float4 per TriRecord
 constexpr int kShadeVec = 5;          // float4 per ShadeRecord
-// traversal stack entries per ray: one node group + one deferred triangle group per level of
-// the wide tree (ptc_upload_scene rejects trees deeper than kStackSize / 2 - 1)
-constexpr int kStackSize = 48;
+// traversal stack per ray: node groups grow from the bottom (one per level of the wide tree:
+// ptc_upload_scene rejects trees deeper than kStackSize - kTriBacklog), deferred triangle
+// groups from the top (at most kTriBacklog; a lane with that many pending groups stops
+// descending until it has tested some triangles)
+constexpr int kStackSize = 40;
+constexpr int kTriBacklog = 8;
 constexpr int kBlock = 256;           // threads per CTA of the path kernels (8 warps)
 constexpr int kTileW = 8, kTileH = 4; // pixels one warp covers in the first wavefront stage
 

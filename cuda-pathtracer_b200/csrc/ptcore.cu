@@ -406,7 +406,7 @@ ptc_upload_scene(ptc_context* ctx, const ptc_scene_desc* desc, int32_t* scene_id
 
   HostBvh bvh;
   build_bvh(desc, bvh);
-  if (2 * (int)bvh.stats.wide_depth + 2 > kStackSize)
+  if ((int)bvh.stats.wide_depth + 1 > kStackSize - kTriBacklog)
     return fail(ctx, PTC_ERR_INVALID, "BVH too deep for the traversal stack");
   std::vector<ShadeRecord> shade;
   build_shade_records(desc, shade);

@@ -162,7 +162,8 @@ struct Trav
   uint32_t oct, oct_inv;
   uint2 ng; // node group: first child index, 8 hit bits (31..24) | imask (7..0)
   uint2 tg; // triangle group: base index, 24-bit mask
-  int sp;
+  int sp;  // node-group entries on stack[0 .. sp)
+  int tsp; // deferred triangle groups on stack[kStackSize - tsp .. kStackSize)
   float best_t, best_u, best_v;
   uint32_t best_id;
 };
@@ -183,6 +184,7 @@ trav_init(Trav& T, const float3 o, const float3 d)
   T.oct = (d.x < 0.f ? 1u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 4u : 0u);
   T.oct_inv = 7u - T.oct;
   T.sp = 0;
+  T.tsp = 0;
   T.ng = make_uint2(0u, 0x80000000u); // root as a one-entry node group
   T.tg = make_uint2(0u, 0u);
 }
@@ -198,6 +200,15 @@ template <bool STATS>
 __device__ __forceinline__ bool
 trav_step(const DScene& sc, Trav& T, uint2* stack, uint32_t& n_nodes, uint32_t& n_tris)
 {
+  // keep both tests fed: an exhausted group is replaced from its stack right away, so a lane
+  // runs a triangle test AND a node test in the same iteration whenever it has either left
+  if (!T.tg.y && T.tsp) {
+    T.tg = stack[kStackSize - T.tsp];
+    --T.tsp;
+  }
+  if (!(T.ng.y & 0xFF000000u) && T.sp)
+    T.ng = stack[--T.sp];
+
   // -- at most one triangle test ------------------------------------------------------
   if (T.tg.y) {
     const uint32_t bit = __ffs(T.tg.y) - 1u;
@@ -219,7 +230,7 @@ trav_step(const DScene& sc, Trav& T, uint2* stack, uint32_t& n_nodes, uint32_t& 
   }
 
   // -- at most one node test ------------------------------------------------------------
-  if (T.ng.y & 0xFF000000u) {
+  if ((T.ng.y & 0xFF000000u) && T.tsp < kTriBacklog) {
     const uint32_t bit = 31u - __clz(T.ng.y);
     T.ng.y &= ~(1u << bit);
     const uint32_t imask = T.ng.y & 0xFFu;
@@ -270,21 +281,14 @@ trav_step(const DScene& sc, Trav& T, uint2* stack, uint32_t& n_nodes, uint32_t& 
       }
     }
     if (T.tg.y)
-      stack[T.sp++] = T.tg; // triangles of the previous leaf group not tested yet: defer
+      stack[kStackSize - (++T.tsp)] = T.tg; // previous leaf group not finished yet: defer
     T.ng = make_uint2(n1.x, (hitmask & 0xFF000000u) | (n0.w >> 24));
     T.tg = make_uint2(n1.y, hitmask & 0x00FFFFFFu);
   }
 
 
-  if (!((T.ng.y & 0xFF000000u) | T.tg.y)) {
-    if (T.sp == 0)
-      return true;
-    const uint2 e = stack[--T.sp];
-    if (e.y & 0xFF000000u)
-      T.ng = e; // node group (always carries at least one unvisited child)
-    else
-      T.tg = e; // deferred triangle group
-  }
+  if (!((T.ng.y & 0xFF000000u) | T.tg.y | (uint32_t)T.sp | (uint32_t)T.tsp))
+    return true;
   return false;
 }
 
