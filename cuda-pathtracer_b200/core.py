@@ -72,7 +72,7 @@ EXPORTS = ["ptc_abi_version", "ptc_create", "ptc_destroy", "ptc_last_error", "pt
            "ptc_reset_accumulation", "ptc_counters_get", "ptc_counters_reset",
            "ptc_trace_primary", "ptc_intersect_rays", "ptc_debug_rng", "ptc_host_bvh_build",
            "ptc_host_bvh_free", "ptc_band_rows", "ptc_launch_count", "ptc_set_wavefront",
-           "ptc_profile_frame"]
+           "ptc_profile_frame", "ptc_render_host_async", "ptc_wait"]
 
 _lib = None
 
@@ -97,7 +97,8 @@ def load_library() -> C.CDLL:
         for name in ["ptc_upload_scene", "ptc_scene_info_get", "ptc_set_cubemap", "ptc_render",
                      "ptc_render_host", "ptc_reset_accumulation", "ptc_counters_get",
                      "ptc_counters_reset", "ptc_trace_primary", "ptc_intersect_rays", "ptc_debug_rng",
-                     "ptc_launch_count", "ptc_set_wavefront", "ptc_profile_frame"]:
+                     "ptc_launch_count", "ptc_set_wavefront", "ptc_profile_frame",
+                     "ptc_render_host_async", "ptc_wait"]:
             getattr(lib, name).restype = C.c_int
         lib.ptc_band_rows.restype = C.c_uint32
         _lib = lib
@@ -253,6 +254,16 @@ class Core:
         a = self._args(*args, **kw)
         self._check(self.lib.ptc_render_host(self.ctx, C.byref(a), C.c_int(int(upload_accum)),
                                              C.c_int(int(download_accum))), "ptc_render_host")
+
+    def render_host_async(self, *args, upload_accum=False, **kw):
+        """Pipelined host-buffer call (returns before the frame is on the host); see wait()."""
+        a = self._args(*args, **kw)
+        self._check(self.lib.ptc_render_host_async(self.ctx, C.byref(a), C.c_int(int(upload_accum))),
+                    "ptc_render_host_async")
+
+    def wait(self, accum_out=None):
+        nbytes = accum_out.nbytes if accum_out is not None else 0
+        self._check(self.lib.ptc_wait(self.ctx, _ptr(accum_out), C.c_uint64(nbytes)), "ptc_wait")
 
     def reset_accumulation(self):
         self._check(self.lib.ptc_reset_accumulation(self.ctx), "ptc_reset_accumulation")

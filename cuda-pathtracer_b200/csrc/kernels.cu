@@ -76,7 +76,8 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
     } else {
       valid = i < n_items;
       if (valid) {
-        const float4 o4 = qin.o[i], d4 = qin.d[i], t4 = qin.thr[i], a4 = qin.acc[i];
+        // queue traffic is streamed (evict-first): it must not push the texels out of L2
+        const float4 o4 = __ldcs(qin.o + i), d4 = __ldcs(qin.d + i), t4 = __ldcs(qin.thr + i), a4 = __ldcs(qin.acc + i);
         P.origin = mk3(o4.x, o4.y, o4.z);
         P.dir = mk3(d4.x, d4.y, d4.z);
         P.throughput = mk3(t4.x, t4.y, t4.z);
@@ -123,7 +124,7 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
           float t, u, v;
           uint32_t id, segs;
           if (HITS) {
-            const uint4 h = hits[i];
+            const uint4 h = __ldcs(hits + i);
             t = __uint_as_float(h.x), id = h.y, u = __uint_as_float(h.z), v = __uint_as_float(h.w);
             lights_hit(sc, P.origin, P.dir, t, id);
           } else {
@@ -150,11 +151,11 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
         slot = atomicAdd(qout_count, (uint32_t)__popc(mask));
       slot = __shfl_sync(0xFFFFFFFFu, slot, leader) + __popc(mask & ((1u << lane) - 1u));
       if (cont) {
-        qout.o[slot] = make_float4(P.origin.x, P.origin.y, P.origin.z, P.spec_carry);
-        qout.d[slot] = make_float4(P.dir.x, P.dir.y, P.dir.z, __uint_as_float(P.draws));
-        qout.thr[slot] = make_float4(P.throughput.x, P.throughput.y, P.throughput.z,
-                                     __uint_as_float(lrow * fp.width + x));
-        qout.acc[slot] = make_float4(P.acc.x, P.acc.y, P.acc.z, 0.0f);
+        __stcs(qout.o + slot, make_float4(P.origin.x, P.origin.y, P.origin.z, P.spec_carry));
+        __stcs(qout.d + slot, make_float4(P.dir.x, P.dir.y, P.dir.z, __uint_as_float(P.draws)));
+        __stcs(qout.thr + slot, make_float4(P.throughput.x, P.throughput.y, P.throughput.z,
+                                            __uint_as_float(lrow * fp.width + x)));
+        __stcs(qout.acc + slot, make_float4(P.acc.x, P.acc.y, P.acc.z, 0.0f));
       }
     }
   }
@@ -209,7 +210,7 @@ k_extend(const DScene sc, const RayQueue qin, const uint32_t* __restrict__ qin_c
         if (!have) {
           const uint32_t mine = base + __popc(idle & ((1u << lane) - 1u));
           if (mine < n) {
-            const float4 o4 = qin.o[mine], d4 = qin.d[mine];
+            const float4 o4 = __ldcs(qin.o + mine), d4 = __ldcs(qin.d + mine);
             trav_init(T, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
             slot = mine;
             have = true;
@@ -221,8 +222,8 @@ k_extend(const DScene sc, const RayQueue qin, const uint32_t* __restrict__ qin_c
         break;
     }
     if (have && trav_step<STATS>(sc, T, stack, my_nodes, my_tris)) {
-      hits[slot] = make_uint4(__float_as_uint(T.best_t), T.best_id, __float_as_uint(T.best_u),
-                              __float_as_uint(T.best_v));
+      __stcs(hits + slot, make_uint4(__float_as_uint(T.best_t), T.best_id, __float_as_uint(T.best_u),
+                                     __float_as_uint(T.best_v)));
       have = false;
     }
   }

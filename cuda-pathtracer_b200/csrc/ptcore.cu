@@ -47,7 +47,7 @@ struct ptc_context
   int n_sms = 148;
   // persistent grids, [stats]: first stage, fused later stage, shade-after-extend, extend
   int grid_first[2] = { 0, 0 }, grid_next[2] = { 0, 0 }, grid_shade[2] = { 0, 0 }, grid_extend[2] = { 0, 0 };
-  uint32_t first_iters = 1, next_iters = 1; // wavefront granularity (ptc_set_wavefront)
+  uint32_t first_iters = 2, next_iters = 1; // wavefront granularity (ptc_set_wavefront)
   uint32_t split_extend = 1;   // later stages: separate refilling extend kernel + shade kernel
   uint32_t refill = 8;         // idle lanes of a warp that trigger a refill in k_extend
   uint4* hits = nullptr;       // closest triangle hit per queue slot (split stages)
@@ -58,6 +58,12 @@ struct ptc_context
   uint32_t* h_out_dev = nullptr;
   float* h_rad_dev = nullptr;
   size_t h_px = 0;
+  // pipelined host call: second device frame + copy stream so the device->host copy of
+  // frame k overlaps the rendering of frame k+1
+  uint32_t* h_out_dev2 = nullptr;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_render[2] = { nullptr, nullptr }, ev_copy[2] = { nullptr, nullptr };
+  int async_slot = 0;
   std::string err;
 };
 
@@ -307,6 +313,28 @@ enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp,
   return 0;
 }
 
+// Device-side staging of the host-buffer calls (accumulator, two RGBA8 frames, radiance).
+int
+ensure_staging(ptc_context* ctx, size_t n, bool& fresh)
+{
+  fresh = false;
+  if (n == ctx->h_px)
+    return 0;
+  cudaFree(ctx->h_accum_dev);
+  cudaFree(ctx->h_out_dev);
+  cudaFree(ctx->h_out_dev2);
+  cudaFree(ctx->h_rad_dev);
+  ctx->h_accum_dev = nullptr, ctx->h_out_dev = nullptr, ctx->h_out_dev2 = nullptr, ctx->h_rad_dev = nullptr;
+  ctx->h_px = 0;
+  CUDA_TRY(ctx, cudaMalloc(&ctx->h_accum_dev, n * 12));
+  CUDA_TRY(ctx, cudaMalloc(&ctx->h_out_dev, n * 4));
+  CUDA_TRY(ctx, cudaMalloc(&ctx->h_out_dev2, n * 4));
+  CUDA_TRY(ctx, cudaMalloc(&ctx->h_rad_dev, n * 12));
+  ctx->h_px = n;
+  fresh = true;
+  return 0;
+}
+
 } // namespace
 
 extern "C" {
@@ -372,6 +400,15 @@ ptc_destroy(ptc_context* ctx)
   cudaFree(ctx->h_accum_dev);
   cudaFree(ctx->h_out_dev);
   cudaFree(ctx->h_rad_dev);
+  cudaFree(ctx->h_out_dev2);
+  for (int i = 0; i < 2; ++i) {
+    if (ctx->ev_render[i])
+      cudaEventDestroy(ctx->ev_render[i]);
+    if (ctx->ev_copy[i])
+      cudaEventDestroy(ctx->ev_copy[i]);
+  }
+  if (ctx->copy_stream)
+    cudaStreamDestroy(ctx->copy_stream);
   delete ctx;
 }
 
@@ -546,18 +583,12 @@ ptc_render_host(ptc_context* ctx, const ptc_render_args* args, int upload_accum,
     return fail(ctx, PTC_ERR_INVALID, "accum is required");
   const size_t n = (size_t)fp.band_rows * fp.width;
   cudaStream_t s = (cudaStream_t)args->stream;
-  if (n != ctx->h_px) {
-    cudaFree(ctx->h_accum_dev);
-    cudaFree(ctx->h_out_dev);
-    cudaFree(ctx->h_rad_dev);
-    ctx->h_accum_dev = nullptr, ctx->h_out_dev = nullptr, ctx->h_rad_dev = nullptr;
-    ctx->h_px = 0;
-    CUDA_TRY(ctx, cudaMalloc(&ctx->h_accum_dev, n * 12));
-    CUDA_TRY(ctx, cudaMalloc(&ctx->h_out_dev, n * 4));
-    CUDA_TRY(ctx, cudaMalloc(&ctx->h_rad_dev, n * 12));
-    ctx->h_px = n;
+  bool fresh = false;
+  rc = ensure_staging(ctx, n, fresh);
+  if (rc)
+    return rc;
+  if (fresh)
     upload_accum = 1; // a fresh device accumulator must be seeded from the caller's
-  }
   if (upload_accum)
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_accum_dev, args->accum, n * 12, cudaMemcpyHostToDevice, s));
   rc = enqueue_frame(ctx, args, fp, ctx->h_accum_dev, args->out_rgba ? ctx->h_out_dev : nullptr,
@@ -571,6 +602,63 @@ ptc_render_host(ptc_context* ctx, const ptc_render_args* args, int upload_accum,
   if (download_accum)
     CUDA_TRY(ctx, cudaMemcpyAsync(args->accum, ctx->h_accum_dev, n * 12, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(ctx, cudaStreamSynchronize(s));
+  return PTC_OK;
+}
+
+int
+ptc_render_host_async(ptc_context* ctx, const ptc_render_args* args, int upload_accum)
+{
+  if (!ctx)
+    return PTC_ERR_INVALID;
+  DeviceGuard g(ctx->device);
+  FrameParams fp;
+  int rc = fill_frame(ctx, args, fp, true);
+  if (rc)
+    return rc;
+  if (!args->accum || !args->out_rgba)
+    return fail(ctx, PTC_ERR_INVALID, "accum and out_rgba are required");
+  const size_t n = (size_t)fp.band_rows * fp.width;
+  cudaStream_t s = (cudaStream_t)args->stream;
+  if (!ctx->copy_stream) {
+    CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->ev_render[i], cudaEventDisableTiming));
+      CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->ev_copy[i], cudaEventDisableTiming));
+    }
+  }
+  bool fresh = false;
+  rc = ensure_staging(ctx, n, fresh);
+  if (rc)
+    return rc;
+  if (fresh || upload_accum)
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_accum_dev, args->accum, n * 12, cudaMemcpyHostToDevice, s));
+  const int slot = ctx->async_slot ^= 1;
+  uint32_t* d_out = slot ? ctx->h_out_dev2 : ctx->h_out_dev;
+  // the copy that last read this device frame must be done before it is overwritten
+  CUDA_TRY(ctx, cudaStreamWaitEvent(s, ctx->ev_copy[slot], 0));
+  rc = enqueue_frame(ctx, args, fp, ctx->h_accum_dev, d_out, nullptr, s);
+  if (rc)
+    return rc;
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev_render[slot], s));
+  CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_render[slot], 0));
+  CUDA_TRY(ctx, cudaMemcpyAsync(args->out_rgba, d_out, n * 4, cudaMemcpyDeviceToHost, ctx->copy_stream));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev_copy[slot], ctx->copy_stream));
+  return PTC_OK;
+}
+
+int
+ptc_wait(ptc_context* ctx, void* accum_out, uint64_t accum_bytes)
+{
+  if (!ctx)
+    return PTC_ERR_INVALID;
+  DeviceGuard g(ctx->device);
+  if (ctx->copy_stream)
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->copy_stream));
+  if (accum_out) {
+    if (accum_bytes != ctx->h_px * 12)
+      return fail(ctx, PTC_ERR_INVALID, "accumulator size does not match the last host-buffer call");
+    CUDA_TRY(ctx, cudaMemcpy(accum_out, ctx->h_accum_dev, accum_bytes, cudaMemcpyDeviceToHost));
+  }
   return PTC_OK;
 }
 

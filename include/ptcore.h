@@ -202,6 +202,19 @@ int ptc_render(ptc_context* ctx, const ptc_render_args* args);
 int ptc_render_host(ptc_context* ctx, const ptc_render_args* args, int upload_accum,
                     int download_accum);
 
+/* Pipelined form of ptc_render_host for a caller that consumes every frame on the host (what
+ * the reference's blit-to-window does each frame, interop.cpp:67-72): enqueues the frame and
+ * the device->host copy of its RGBA8 (on an internal copy stream, two device frames) and
+ * returns without waiting, so the copy of frame k overlaps the rendering of frame k+1.
+ * out_rgba must stay valid (and should be pinned) until ptc_wait or until the second next
+ * call returns a frame into it; use two host buffers alternately.  The accumulator stays on
+ * the device; args->accum is read only when upload_accum != 0 or the band size changed. */
+int ptc_render_host_async(ptc_context* ctx, const ptc_render_args* args, int upload_accum);
+
+/* Waits for every pending copy of ptc_render_host_async.  accum_out != NULL additionally
+ * downloads the device-side accumulator (accum_bytes = band pixels * 12). */
+int ptc_wait(ptc_context* ctx, void* accum_out, uint64_t accum_bytes);
+
 /* Resets the context's frame counter (what `moved` does, without a preview frame). */
 int ptc_reset_accumulation(ptc_context* ctx);
 

@@ -503,7 +503,7 @@ def test_wavefront_granularity_invariance(core):
             results.append((acc.cpu().numpy(), out.cpu().numpy(), rad.cpu().numpy(), c.segments, c.traced,
                             [c.rays_per_bounce[i] for i in range(8)]))
     finally:
-        core.set_wavefront(1, 1, 1, 8)
+        core.set_wavefront(2, 1, 1, 8)
     a0 = results[0]
     for r in results[1:]:
         assert (bits(r[0]) == bits(a0[0])).all() and (r[1] == a0[1]).all() and (bits(r[2]) == bits(a0[2])).all()
@@ -543,7 +543,11 @@ def test_profile_frame_reports_consistent_counts(core):
     L = loaded(core, "indoor_plain")
     w, h, b = 640, 360, 3
     acc, out, _ = dev_buffers(w, h)
-    pr = core.profile_frame(L.sid, L.cid, L.sc, w, h, acc, out, None, bounces=b, frame_nb=1, repeats=3)
+    core.set_wavefront(1, 1, 1, 8)
+    try:
+        pr = core.profile_frame(L.sid, L.cid, L.sc, w, h, acc, out, None, bounces=b, frame_nb=1, repeats=3)
+    finally:
+        core.set_wavefront(2, 1, 1, 8)
     assert pr["launch_kind"] == ["first", "extend", "shade", "extend", "shade"]
     assert all(ms > 0 for ms in pr["launch_ms"])
     assert pr["segments"] == w * h * b and w * h <= pr["traced"] <= pr["segments"]
@@ -578,3 +582,34 @@ def test_large_mesh_traversal_vs_oracle_bvh(core, oracle):
     core.render_host(sid, cid, sc, w, h, accum, None, rad, bounces=4, frame_nb=1, upload_accum=True, download_accum=True)
     c = core.counters()
     assert c.paths == w * h and c.traced >= w * h and np.isfinite(rad).mean() > 0.99
+
+
+def test_pipelined_host_call_equals_synchronous(core):
+    """ptc_render_host_async (copy of frame k overlapping the rendering of frame k+1, two host
+    buffers) delivers exactly the frames and the accumulator of the synchronous call."""
+    import torch
+    L = loaded(core, "indoor_tex")
+    w, h, b, n = 640, 360, 3, 7
+    want_frames = []
+    accum = None
+    for k in range(1, n + 1):
+        accum, rgba, _ = render_np(core, L, w, h, k, b, accum=accum)
+        want_frames.append(rgba.copy())
+    bufs = [torch.zeros(h, w, dtype=torch.int32).pin_memory() for _ in range(2)]
+    acc0 = np.zeros((h, w, 3), np.float32)
+    got = []
+    for k in range(1, n + 1):
+        buf = bufs[k & 1]
+        if k > 2:  # the frame delivered two calls ago lives in this buffer: wait, then keep it
+            core.wait()
+            got.append(bufs[k & 1].numpy().copy())
+        core.render_host_async(L.sid, L.cid, L.sc, w, h, acc0, buf.numpy(), None, bounces=b, frame_nb=k,
+                               upload_accum=(k == 1))
+    acc_out = np.zeros((h, w, 3), np.float32)
+    core.wait(acc_out)
+    got.append(bufs[(n - 1) & 1].numpy().copy())
+    got.append(bufs[n & 1].numpy().copy())
+    assert len(got) == n
+    for k in range(n):
+        assert (got[k].view(np.uint8).reshape(h, w, 4) == want_frames[k]).all(), k
+    assert (bits(acc_out) == bits(accum)).all()
