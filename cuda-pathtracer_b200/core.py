@@ -226,6 +226,11 @@ class Core:
                                                C.c_int32(split_extend), C.c_uint32(refill)),
                     "ptc_set_wavefront")
 
+    def set_wavefront_auto(self):
+        """Back to the default schedule (first stage depth chosen per scene size)."""
+        self._check(self.lib.ptc_set_wavefront(self.ctx, C.c_uint32(0xFFFFFFFF), C.c_uint32(1), C.c_int32(1),
+                                               C.c_uint32(8)), "ptc_set_wavefront")
+
     def profile_frame(self, *args, repeats=5, **kw) -> dict:
         """Per-launch CUDA-event times of one frame + traversal statistics (ptc_profile_frame)."""
         a = self._args(*args, **kw)

@@ -15,28 +15,34 @@
 
 namespace ptc {
 
-// 8-wide compressed node, 80 bytes, 16-byte aligned (5 x 128-bit loads).
-// Child boxes are quantised to 8 bits per plane relative to the node origin:
-//   lo_a = origin_a + qlo_a[i] * 2^(e_a - 127 ... as float bits e_a << 23)
-// Quantisation rounds outwards, so decoded boxes contain the true ones.
+// 8-wide compressed node, 128 bytes, 16-byte aligned (8 x 128-bit loads).
+// Child boxes are quantised to 8 bits per plane relative to the node origin,
+//   plane_a = origin_a + q * 2^(e_a - 127)        (e_a << 23 are the float bits of the scale)
+// rounded outwards, so decoded boxes contain the true ones.  The 8-bit q values are stored
+// as IEEE half floats (exact for 0..255): the kernel turns them into fp32 with one
+// HADD2.F32 on the FMA pipe, whereas unpacking bytes costs an ALU-pipe PRMT (or an XU-pipe
+// I2F) each -- and the box test is ALU-pipe bound (48 planes per node).
 //
-// meta[i]:  0                      empty slot
-//           0b001'11sss (>= 0x38)  internal child; sss = slot i; bit position 24+i
-//                                  in the hit mask (before octant reordering)
-//           0bccc'ooooo            leaf: ooooo = first triangle offset (0..23) from
-//                                  tri_base, ccc = unary count (001, 011, 111)
+// Slot s (0..7) is either an internal child (bit s of imask; children of a node are
+// contiguous from child_base in slot order), a leaf of 1..3 triangles, or empty.  The
+// triangles of leaf slot s own bits 3s..3s+2 of the node's 24-bit triangle space; valid24
+// marks the ones that exist and the record of bit b is
+//   tris[tri_base + popcount(valid24 & ((1 << b) - 1))].
+// Slots are assigned by octant (bvh_builder.cpp) so that (s ^ (7 - ray_octant)) orders the
+// children far-to-near.
 struct alignas(16) Node8
 {
   float origin[3];
   uint8_t e[3];
-  uint8_t imask;       // bit i: slot i holds an internal child
-  uint32_t child_base; // node index of the first internal child (children contiguous)
+  uint8_t imask;       // bit s: slot s holds an internal child
+  uint32_t child_base; // node index of the first internal child
   uint32_t tri_base;   // index of this node's first triangle record
-  uint8_t meta[8];
-  uint8_t qlo[3][8];
-  uint8_t qhi[3][8];
+  uint32_t valid24;    // bit 3s+j: leaf slot s has a j-th triangle
+  uint32_t occupied;   // bit s: slot s is not empty (diagnostic; the kernel needs imask/valid24 only)
+  uint16_t lo[3][8];   // half-float q of the lower planes, [axis][slot]
+  uint16_t hi[3][8];   // half-float q of the upper planes
 };
-static_assert(sizeof(Node8) == 80, "Node8 must be 80 bytes");
+static_assert(sizeof(Node8) == 128, "Node8 must be 128 bytes");
 
 // Intersection record, 48 bytes (3 x 128-bit loads).  Edges are precomputed with the
 // same single fp32 subtraction the reference performs per ray

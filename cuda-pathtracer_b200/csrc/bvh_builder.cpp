@@ -271,6 +271,19 @@ quant_exponent(float ext)
   return (uint8_t)biased;
 }
 
+// IEEE half-float bits of the integer q in 0..255 (exact).
+uint16_t
+half_of_byte(int q)
+{
+  if (q <= 0)
+    return 0;
+  int e = 0;
+  while ((q >> (e + 1)) != 0)
+    ++e; // q in [2^e, 2^(e+1))
+  const int mant = (q - (1 << e)) << (10 - e);
+  return (uint16_t)(((e + 15) << 10) | mant);
+}
+
 float
 exp_scale(uint8_t e)
 {
@@ -422,11 +435,16 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
     }
     n.child_base = (uint32_t)out.nodes.size();
     n.tri_base = (uint32_t)out.tris.size();
-    uint32_t tri_off = 0;
     for (int s = 0; s < 8; ++s) {
       int k = kid_in_slot[s];
-      if (k < 0)
+      if (k < 0) { // empty slot: an inverted box (lo > hi) can never be hit
+        for (int a = 0; a < 3; ++a) {
+          n.lo[a][s] = half_of_byte(255);
+          n.hi[a][s] = half_of_byte(0);
+        }
         continue;
+      }
+      n.occupied |= 1u << s;
       const BinNode& c = b.nodes[kids[k]];
       for (int a = 0; a < 3; ++a) {
         float sc = exp_scale(n.e[a]);
@@ -437,21 +455,18 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
           ql -= 1.f;
         while (qh < 255.f && n.origin[a] + qh * sc < c.box.hi[a])
           qh += 1.f;
-        n.qlo[a][s] = (uint8_t)std::min(255.f, std::max(0.f, ql));
-        n.qhi[a][s] = (uint8_t)std::min(255.f, std::max(0.f, qh));
+        n.lo[a][s] = half_of_byte((int)std::min(255.f, std::max(0.f, ql)));
+        n.hi[a][s] = half_of_byte((int)std::min(255.f, std::max(0.f, qh)));
       }
       if (dp.is_leaf(kids[k])) {
-        uint32_t unary = (1u << c.count) - 1u; // 001, 011, 111
-        n.meta[s] = (uint8_t)((unary << 5) | tri_off);
+        n.valid24 |= ((1u << c.count) - 1u) << (3 * s); // 001, 011, 111
         std::vector<uint32_t> ids(b.order.begin() + c.first, b.order.begin() + c.first + c.count);
         std::sort(ids.begin(), ids.end());
         for (uint32_t f : ids)
           emit_tri(f);
-        tri_off += c.count;
         out.stats.n_leaves++;
       } else {
         n.imask |= (uint8_t)(1u << s);
-        n.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
         queue.push_back({ kids[k], (uint32_t)out.nodes.size(), cur.depth + 1 });
         out.nodes.emplace_back();
       }

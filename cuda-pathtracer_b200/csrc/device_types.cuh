@@ -9,7 +9,7 @@
 namespace ptc {
 
 constexpr float kMaxDist = 100000.0f; // MAX_DIST, intersection.cuh:165
-constexpr int kNodeVec = 5;           // uint4 per Node8
+constexpr int kNodeVec = 8;           // uint4 per Node8 (128 B)
 constexpr int kTriVec = 3;            // float4 per TriRecord
 constexpr int kShadeVec = 5;          // float4 per ShadeRecord
 // traversal stack per ray: node groups grow from the bottom (one per level of the wide tree:

@@ -123,14 +123,24 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
         if (!done) {
           float t, u, v;
           uint32_t id, segs;
+          const bool last = b + 1 >= fp.max_bounces; // nothing after this iteration: any-hit query
           if (HITS) {
             const uint4 h = __ldcs(hits + i);
             t = __uint_as_float(h.x), id = h.y, u = __uint_as_float(h.z), v = __uint_as_float(h.w);
-            lights_hit(sc, P.origin, P.dir, t, id);
+            if (!last)
+              lights_hit(sc, P.origin, P.dir, t, id);
+          } else if (last) {
+            u = v = 0.f;
+            last_hit<STATS>(sc, P.origin, P.dir, t, id, my_nodes, my_tris);
           } else {
             closest_hit<STATS>(sc, P.origin, P.dir, t, id, u, v, my_nodes, my_tris);
           }
-          done = shade_step(fp, sc, cube, P, rng, t, id, u, v, b, segs);
+          if (last && id < sc.n_faces) {
+            done = true; // a triangle in front on the last iteration adds no radiance
+            segs = 1;
+          } else {
+            done = shade_step(fp, sc, cube, P, rng, t, id, u, v, b, segs);
+          }
           my_segs += segs;
           my_traced++;
         }
@@ -189,7 +199,7 @@ template <bool STATS>
 __global__ void __launch_bounds__(kBlock, 3)
 k_extend(const DScene sc, const RayQueue qin, const uint32_t* __restrict__ qin_count,
          uint4* __restrict__ hits, uint32_t* __restrict__ work, Counters* __restrict__ ctr,
-         const uint32_t refill)
+         const uint32_t refill, const int last)
 {
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t n = *qin_count;
@@ -211,7 +221,10 @@ k_extend(const DScene sc, const RayQueue qin, const uint32_t* __restrict__ qin_c
           const uint32_t mine = base + __popc(idle & ((1u << lane) - 1u));
           if (mine < n) {
             const float4 o4 = __ldcs(qin.o + mine), d4 = __ldcs(qin.d + mine);
-            trav_init(T, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
+            if (last) // last radiance-loop iteration: lights first, then an any-hit query
+              trav_init_any(sc, T, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
+            else
+              trav_init(T, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
             slot = mine;
             have = true;
           }
@@ -391,14 +404,14 @@ launch_path(bool first, bool stats, uint32_t grid, const FrameParams& fp, const 
 
 void
 launch_extend(bool stats, uint32_t grid, const DScene& sc, const RayQueue& qin, const uint32_t* qin_count,
-              uint4* hits, uint32_t* work, Counters* ctr, uint32_t refill, cudaStream_t s)
+              uint4* hits, uint32_t* work, Counters* ctr, uint32_t refill, bool last, cudaStream_t s)
 {
   if (!grid)
     return;
   if (stats)
-    k_extend<true><<<grid, kBlock, 0, s>>>(sc, qin, qin_count, hits, work, ctr, refill);
+    k_extend<true><<<grid, kBlock, 0, s>>>(sc, qin, qin_count, hits, work, ctr, refill, last ? 1 : 0);
   else
-    k_extend<false><<<grid, kBlock, 0, s>>>(sc, qin, qin_count, hits, work, ctr, refill);
+    k_extend<false><<<grid, kBlock, 0, s>>>(sc, qin, qin_count, hits, work, ctr, refill, last ? 1 : 0);
 }
 
 void

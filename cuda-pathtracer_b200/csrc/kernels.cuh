@@ -21,10 +21,12 @@ void launch_path(bool first, bool stats, uint32_t grid, const FrameParams& fp, c
                  cudaStream_t s);
 
 // Closest triangle hit of every ray of `qin` -> hits[slot] = (t, face id | ~0, u, v), with
-// per-lane refill once `refill` lanes of a warp are idle.
+// per-lane refill once `refill` lanes of a warp are idle.  last: the rays belong to the last
+// radiance-loop iteration -> lights + any-hit query (traverse.cuh, trav_init_any); the hit
+// record then already includes the sphere lights.
 void launch_extend(bool stats, uint32_t grid, const DScene& sc, const RayQueue& qin,
                    const uint32_t* qin_count, uint4* hits, uint32_t* work, Counters* ctr,
-                   uint32_t refill, cudaStream_t s);
+                   uint32_t refill, bool last, cudaStream_t s);
 
 void launch_primary_hits(const FrameParams& fp, const DScene& sc, int32_t* ids, float* ts,
                          cudaStream_t s);

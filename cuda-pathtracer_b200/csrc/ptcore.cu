@@ -47,7 +47,7 @@ struct ptc_context
   int n_sms = 148;
   // persistent grids, [stats]: first stage, fused later stage, shade-after-extend, extend
   int grid_first[2] = { 0, 0 }, grid_next[2] = { 0, 0 }, grid_shade[2] = { 0, 0 }, grid_extend[2] = { 0, 0 };
-  uint32_t first_iters = 2, next_iters = 1; // wavefront granularity (ptc_set_wavefront)
+  uint32_t first_iters = 0, next_iters = 1; // first_iters 0 = per scene (frame_schedule) // wavefront granularity (ptc_set_wavefront)
   uint32_t split_extend = 1;   // later stages: separate refilling extend kernel + shade kernel
   uint32_t refill = 8;         // idle lanes of a warp that trigger a refill in k_extend
   uint4* hits = nullptr;       // closest triangle hit per queue slot (split stages)
@@ -234,6 +234,13 @@ fill_frame(ptc_context* ctx, const ptc_render_args* a, FrameParams& fp, bool adv
   return 0;
 }
 
+size_t
+scene_bvh_bytes(const ptc_context* ctx, int32_t scene_id)
+{
+  const ptc_scene_info& i = ctx->scenes[scene_id].info;
+  return (size_t)i.bvh_nodes * i.bvh_node_bytes + (size_t)i.n_faces * i.tri_bytes;
+}
+
 // One launch of the frame's schedule.
 struct Step
 {
@@ -244,14 +251,20 @@ struct Step
 // The wavefront schedule of a frame: the first stage generates the rays and runs
 // `first_iters` radiance-loop iterations in registers; every later stage runs `next_iters`.
 int
-frame_schedule(const ptc_context* ctx, const FrameParams& fp, Step* steps)
+frame_schedule(const ptc_context* ctx, const FrameParams& fp, size_t bvh_bytes, Step* steps)
 {
   int n = 0;
   if (!fp.is_static) {
     steps[n++] = Step{ true, 0, 1 };
     return n;
   }
-  int b = (int)ctx->first_iters < fp.max_bounces ? (int)ctx->first_iters : fp.max_bounces;
+  // automatic: a BVH that lives in L1 (the 27 KB indoor scene) traverses its second
+  // iteration fastest straight out of registers; a BVH in L2/HBM gains more from handing
+  // the incoherent rays to the refilling extend kernel right away (measured both ways).
+  int first = (int)ctx->first_iters;
+  if (first == 0)
+    first = bvh_bytes <= (1u << 20) ? 2 : 1;
+  int b = first < fp.max_bounces ? first : fp.max_bounces;
   steps[n++] = Step{ true, 0, b };
   while (b < fp.max_bounces) {
     int k = (int)ctx->next_iters < fp.max_bounces - b ? (int)ctx->next_iters : fp.max_bounces - b;
@@ -277,7 +290,7 @@ enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp,
     return rc;
   FrameOut fo{ accum, out, rad };
   Step steps[kMaxBounces + 1];
-  const int n_steps = frame_schedule(ctx, fp, steps);
+  const int n_steps = frame_schedule(ctx, fp, scene_bvh_bytes(ctx, a->scene_id), steps);
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->counts, 0, sizeof(uint32_t) * kCountSlots, s));
   int n_ev = 0;
   if (ev)
@@ -294,7 +307,7 @@ enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp,
       grid = want < cap ? want : cap;
     } else if (ctx->split_extend) {
       launch_extend(stats, (uint32_t)ctx->grid_extend[stats], sc.d, ctx->queue[k & 1], ctx->counts + k,
-                    ctx->hits, work + 1, ctx->ctr, ctx->refill, s);
+                    ctx->hits, work + 1, ctx->ctr, ctx->refill, st.bounce0 + 1 >= fp.max_bounces, s);
       ctx->launches++;
       if (ev)
         CUDA_TRY(ctx, cudaEventRecord(ev[++n_ev], s));
@@ -732,7 +745,9 @@ ptc_set_wavefront(ptc_context* ctx, uint32_t first_iters, uint32_t next_iters, i
     ctx->split_extend = split_extend ? 1u : 0u;
   if (refill)
     ctx->refill = refill > 32 ? 32 : refill;
-  if (first_iters)
+  if (first_iters == 0xFFFFFFFFu)
+    ctx->first_iters = 0; // automatic (per scene size)
+  else if (first_iters)
     ctx->first_iters = first_iters;
   if (next_iters)
     ctx->next_iters = next_iters;
@@ -754,7 +769,7 @@ ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeat
     return fail(ctx, PTC_ERR_INVALID, "accum is required");
   cudaStream_t s = (cudaStream_t)args->stream;
   Step steps[kMaxBounces + 1];
-  const int n_steps = frame_schedule(ctx, fp, steps);
+  const int n_steps = frame_schedule(ctx, fp, scene_bvh_bytes(ctx, args->scene_id), steps);
   // the launches of one frame: kind 0 = first stage, 1 = fused later stage, 2 = extend, 3 = shade
   struct L { uint32_t kind, bounce0, iters; };
   std::vector<L> launches;

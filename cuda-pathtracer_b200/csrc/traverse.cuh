@@ -6,6 +6,8 @@
 //                answered through the 8-wide compressed BVH
 #pragma once
 
+#include <cuda_fp16.h>
+
 #include "device_types.cuh"
 #include "vecmath.cuh"
 
@@ -145,27 +147,44 @@ sphere_test(const ptc_light& L, const float3 o, const float3 d, float& t)
   return t != 0.f;
 }
 
-// Quantised plane coordinate q (byte k of w) as the float 1 + q * 2^-15: ONE byte-permute
-// drops the byte into mantissa bits 8..15 of 1.0f -- no int->float conversion (I2F runs on
-// the quarter-rate XU pipe and was 48 instructions per node test).
+// Half-float pair -> fp32 (HADD2.F32 on the FMA pipe; the planes of a node are stored as
+// halves for exactly this reason, see bvh.h).
 __device__ __forceinline__ float
-byte_unit(uint32_t w, int k)
+half_lo(uint32_t w)
 {
-  return __uint_as_float(__byte_perm(w, 0x3F800000u, 0x7604u | ((uint32_t)k << 4)));
+  return __low2float(*reinterpret_cast<const __half2*>(&w));
+}
+__device__ __forceinline__ float
+half_hi(uint32_t w)
+{
+  return __high2float(*reinterpret_cast<const __half2*>(&w));
 }
 
+// bit s of an 8-bit mask -> bit 3s (the triangle space of a node gives every slot 3 bits)
+__device__ __forceinline__ uint32_t
+spread3(uint32_t x)
+{
+  x = (x | (x << 8)) & 0x00F00Fu;
+  x = (x | (x << 4)) & 0x0C30C3u;
+  x = (x | (x << 2)) & 0x249249u;
+  return x;
+}
 
 // Traversal state of one ray (registers; the stack lives in local memory, L1-resident).
 struct Trav
 {
   float3 o, d, idir;
   uint32_t oct, oct_inv;
+  uint32_t vnx, vny, vnz; // uint4 index (inside a node) of the near plane set per axis
   uint2 ng; // node group: first child index, 8 hit bits (31..24) | imask (7..0)
-  uint2 tg; // triangle group: base index, 24-bit mask
+  uint2 tg; // triangle group: tri_base, valid24 of its node
+  uint32_t tmask; // triangles of tg still to test (bits of the node's 24-bit triangle space)
   int sp;  // node-group entries on stack[0 .. sp)
   int tsp; // deferred triangle groups on stack[kStackSize - tsp .. kStackSize)
   float best_t, best_u, best_v;
   uint32_t best_id;
+  bool any;  // any-hit query: stop at the first accepted triangle (trav_init_any)
+  bool incl; // any-hit: a triangle at exactly best_t also counts
 };
 
 __device__ __forceinline__ void
@@ -176,6 +195,7 @@ trav_init(Trav& T, const float3 o, const float3 d)
   T.best_t = kMaxDist;
   T.best_id = 0xFFFFFFFFu;
   T.best_u = T.best_v = 0.f;
+  T.any = T.incl = false;
   // guarded reciprocal direction for the (conservative) slab tests only
   const float eps = 1e-20f;
   T.idir = mk3(1.0f / (fabsf(d.x) > eps ? d.x : copysignf(eps, d.x)),
@@ -183,10 +203,33 @@ trav_init(Trav& T, const float3 o, const float3 d)
                1.0f / (fabsf(d.z) > eps ? d.z : copysignf(eps, d.z)));
   T.oct = (d.x < 0.f ? 1u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 4u : 0u);
   T.oct_inv = 7u - T.oct;
+  T.vnx = d.x < 0.f ? 5u : 2u; // lo planes at 2,3,4 / hi planes at 5,6,7 (bvh.h)
+  T.vny = d.y < 0.f ? 6u : 3u;
+  T.vnz = d.z < 0.f ? 7u : 4u;
   T.sp = 0;
   T.tsp = 0;
   T.ng = make_uint2(0u, 0x80000000u); // root as a one-entry node group
   T.tg = make_uint2(0u, 0u);
+  T.tmask = 0u;
+}
+
+// Last radiance-loop iteration of a path (raytrace.cu:67 with b == max_bounces - 1): whatever
+// the ray hits, the loop ends afterwards, and only a LIGHT hit (emission, raytrace.cu:98-99)
+// or a MISS (environment, :194-199) adds radiance -- a triangle hit adds nothing and its
+// material is never looked at.  So the closest-hit query degenerates into: nearest sphere
+// light first (intersection.cuh:199-212 accepts a light only if it is strictly nearer than
+// the nearest triangle), then an ANY-hit query for a triangle with 0 < t <= t_light (or
+// 0 < t < MAX_DIST when no light is on the ray), which stops at the first triangle found.
+__device__ __forceinline__ void lights_hit(const DScene& sc, const float3 o, const float3 d, float& best_t,
+                                           uint32_t& best_id);
+
+__device__ __forceinline__ void
+trav_init_any(const DScene& sc, Trav& T, const float3 o, const float3 d)
+{
+  trav_init(T, o, d);
+  lights_hit(sc, o, d, T.best_t, T.best_id);
+  T.any = true;
+  T.incl = T.best_id != 0xFFFFFFFFu;
 }
 
 // One traversal iteration: AT MOST one triangle test and one 8-wide node test.  Returns
@@ -202,29 +245,36 @@ trav_step(const DScene& sc, Trav& T, uint2* stack, uint32_t& n_nodes, uint32_t& 
 {
   // keep both tests fed: an exhausted group is replaced from its stack right away, so a lane
   // runs a triangle test AND a node test in the same iteration whenever it has either left
-  if (!T.tg.y && T.tsp) {
-    T.tg = stack[kStackSize - T.tsp];
+  if (!T.tmask && T.tsp) {
+    const uint2 e = stack[kStackSize - T.tsp]; // (tri_base, valid24 | leaf-slot hit mask << 24)
     --T.tsp;
+    T.tg = make_uint2(e.x, e.y & 0x00FFFFFFu);
+    T.tmask = (spread3(e.y >> 24) * 7u) & T.tg.y;
   }
   if (!(T.ng.y & 0xFF000000u) && T.sp)
     T.ng = stack[--T.sp];
 
   // -- at most one triangle test ------------------------------------------------------
-  if (T.tg.y) {
-    const uint32_t bit = __ffs(T.tg.y) - 1u;
-    T.tg.y &= T.tg.y - 1u;
-    const float4* tp = sc.tris + (size_t)(T.tg.x + bit) * kTriVec;
+  if (T.tmask) {
+    const uint32_t bit = __ffs(T.tmask) - 1u;
+    T.tmask &= T.tmask - 1u;
+    const uint32_t rec = T.tg.x + __popc(T.tg.y & ((1u << bit) - 1u));
+    const float4* tp = sc.tris + (size_t)rec * kTriVec;
     const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
     if (STATS)
       n_tris++;
     float t, u, v;
     if (tri_test(t0, t1, t2, T.o, T.d, t, u, v)) {
       const uint32_t fid = __float_as_uint(t2.y);
-      if (t > 0.f && (t < T.best_t || (t == T.best_t && fid < T.best_id))) {
+      if (t > 0.f && (t < T.best_t || (t == T.best_t && (T.any ? T.incl : fid < T.best_id)))) {
         T.best_t = t;
         T.best_id = fid;
         T.best_u = u;
         T.best_v = v;
+        if (T.any) { // occluded: nothing else about this ray matters
+          T.ng.y = 0u, T.tmask = 0u;
+          T.sp = T.tsp = 0;
+        }
       }
     }
   }
@@ -233,63 +283,70 @@ trav_step(const DScene& sc, Trav& T, uint2* stack, uint32_t& n_nodes, uint32_t& 
   if ((T.ng.y & 0xFF000000u) && T.tsp < kTriBacklog) {
     const uint32_t bit = 31u - __clz(T.ng.y);
     T.ng.y &= ~(1u << bit);
-    const uint32_t imask = T.ng.y & 0xFFu;
+    const uint32_t imask_parent = T.ng.y & 0xFFu;
     if (T.ng.y & 0xFF000000u)
       stack[T.sp++] = T.ng;
     const uint32_t slot = (bit - 24u) ^ T.oct_inv;
-    const uint32_t rel = __popc(imask & ~(0xFFFFFFFFu << slot));
-    const uint32_t idx = T.ng.x + rel;
+    const uint32_t rel = __popc(imask_parent & ~(0xFFFFFFFFu << slot));
+    const uint32_t vec0 = (T.ng.x + rel) * kNodeVec;
 
-    const uint4* np = sc.nodes + (size_t)idx * kNodeVec;
-    const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3),
-                n4 = __ldg(np + 4);
+    const uint4 n0 = __ldg(sc.nodes + vec0), n1 = __ldg(sc.nodes + vec0 + 1);
+    // near / far plane sets picked by ray octant through the load address, not by selects
+    const uint4 NX = __ldg(sc.nodes + vec0 + T.vnx), FX = __ldg(sc.nodes + vec0 + 7u - T.vnx);
+    const uint4 NY = __ldg(sc.nodes + vec0 + T.vny), FY = __ldg(sc.nodes + vec0 + 9u - T.vny);
+    const uint4 NZ = __ldg(sc.nodes + vec0 + T.vnz), FZ = __ldg(sc.nodes + vec0 + 11u - T.vnz);
     if (STATS)
       n_nodes++;
 
-    // plane = origin + q * 2^(e-127);  with v = 1 + q * 2^-15 (byte_unit):
-    //   t = (plane - o) * T.idir = v * a + b,  a = 2^(e-127+15) * T.idir,  b = (origin - o) * T.idir - a
-    // The rounding of b is far inside the pad the builder puts around every triangle box.
-    const float sx = __uint_as_float(((n0.w & 0xFFu) + 15u) << 23);
-    const float sy = __uint_as_float((((n0.w >> 8) & 0xFFu) + 15u) << 23);
-    const float sz = __uint_as_float((((n0.w >> 16) & 0xFFu) + 15u) << 23);
+    // plane = origin + q * 2^(e-127);  t = (plane - o) * idir = q * a + b
+    const float sx = __uint_as_float((n0.w & 0xFFu) << 23);
+    const float sy = __uint_as_float(((n0.w >> 8) & 0xFFu) << 23);
+    const float sz = __uint_as_float(((n0.w >> 16) & 0xFFu) << 23);
     const float ax = sx * T.idir.x, ay = sy * T.idir.y, az = sz * T.idir.z;
-    const float bx = (__uint_as_float(n0.x) - T.o.x) * T.idir.x - ax;
-    const float by = (__uint_as_float(n0.y) - T.o.y) * T.idir.y - ay;
-    const float bz = (__uint_as_float(n0.z) - T.o.z) * T.idir.z - az;
+    const float bx = (__uint_as_float(n0.x) - T.o.x) * T.idir.x;
+    const float by = (__uint_as_float(n0.y) - T.o.y) * T.idir.y;
+    const float bz = (__uint_as_float(n0.z) - T.o.z) * T.idir.z;
 
-    uint32_t hitmask = 0;
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      const uint32_t meta4 = half ? n1.w : n1.z;
-      const uint32_t lox = half ? n2.y : n2.x, loy = half ? n2.w : n2.z, loz = half ? n3.y : n3.x;
-      const uint32_t hix = half ? n3.w : n3.z, hiy = half ? n4.y : n4.x, hiz = half ? n4.w : n4.z;
-      const uint32_t nx = (T.oct & 1u) ? hix : lox, fx = (T.oct & 1u) ? lox : hix;
-      const uint32_t ny = (T.oct & 2u) ? hiy : loy, fy = (T.oct & 2u) ? loy : hiy;
-      const uint32_t nz = (T.oct & 4u) ? hiz : loz, fz = (T.oct & 4u) ? loz : hiz;
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const float tnx = fmaf(byte_unit(nx, k), ax, bx), tfx = fmaf(byte_unit(fx, k), ax, bx);
-        const float tny = fmaf(byte_unit(ny, k), ay, by), tfy = fmaf(byte_unit(fy, k), ay, by);
-        const float tnz = fmaf(byte_unit(nz, k), az, bz), tfz = fmaf(byte_unit(fz, k), az, bz);
-        const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
-        const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, T.best_t));
-        if (tmin <= tmax) {
-          const uint32_t m = (meta4 >> (8 * k)) & 0xFFu;
-          const uint32_t inner = ((m & 0x18u) == 0x18u) ? T.oct_inv : 0u;
-          hitmask |= (m >> 5) << ((m & 31u) ^ inner);
-        }
+    uint32_t hit8 = 0;
+#define PTC_CHILD(k, W, H)                                                                       \
+  {                                                                                              \
+    const float tnx = fmaf(H(NX.W), ax, bx), tfx = fmaf(H(FX.W), ax, bx);                        \
+    const float tny = fmaf(H(NY.W), ay, by), tfy = fmaf(H(FY.W), ay, by);                        \
+    const float tnz = fmaf(H(NZ.W), az, bz), tfz = fmaf(H(FZ.W), az, bz);                        \
+    const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));                                 \
+    const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, T.best_t));                             \
+    if (tmin <= tmax)                                                                            \
+      hit8 |= 1u << k;                                                                           \
+  }
+    PTC_CHILD(0, x, half_lo) PTC_CHILD(1, x, half_hi) PTC_CHILD(2, y, half_lo) PTC_CHILD(3, y, half_hi)
+    PTC_CHILD(4, z, half_lo) PTC_CHILD(5, z, half_hi) PTC_CHILD(6, w, half_lo) PTC_CHILD(7, w, half_hi)
+#undef PTC_CHILD
+
+    // internal children: bit s -> 24 + (s ^ oct_inv), i.e. far-to-near from the top bit down
+    const uint32_t imask = n0.w >> 24;
+    uint32_t ih = hit8 & imask;
+    if (T.oct_inv & 1u)
+      ih = ((ih & 0x55u) << 1) | ((ih >> 1) & 0x55u);
+    if (T.oct_inv & 2u)
+      ih = ((ih & 0x33u) << 2) | ((ih >> 2) & 0x33u);
+    if (T.oct_inv & 4u)
+      ih = ((ih & 0x0Fu) << 4) | (ih >> 4);
+    T.ng = make_uint2(n1.x, (ih << 24) | imask);
+
+    // leaf slots that were hit -> their triangles (3 bits per slot, masked by the existing ones)
+    const uint32_t lh = hit8 & ~imask;
+    const uint32_t tnew = (spread3(lh) * 7u) & n1.z;
+    if (tnew) {
+      if (T.tmask) {
+        stack[kStackSize - (++T.tsp)] = make_uint2(n1.y, n1.z | (lh << 24)); // defer, unstarted
+      } else {
+        T.tg = make_uint2(n1.y, n1.z);
+        T.tmask = tnew;
       }
     }
-    if (T.tg.y)
-      stack[kStackSize - (++T.tsp)] = T.tg; // previous leaf group not finished yet: defer
-    T.ng = make_uint2(n1.x, (hitmask & 0xFF000000u) | (n0.w >> 24));
-    T.tg = make_uint2(n1.y, hitmask & 0x00FFFFFFu);
   }
 
-
-  if (!((T.ng.y & 0xFF000000u) | T.tg.y | (uint32_t)T.sp | (uint32_t)T.tsp))
-    return true;
-  return false;
+  return !((T.ng.y & 0xFF000000u) | T.tmask | (uint32_t)T.sp | (uint32_t)T.tsp);
 }
 
 // Sphere lights after the triangles, 0 <= t < best in light order (intersection.cuh:199-212).
@@ -303,6 +360,21 @@ lights_hit(const DScene& sc, const float3 o, const float3 d, float& best_t, uint
       best_id = sc.n_faces + l;
     }
   }
+}
+
+// What the last radiance-loop iteration needs to know (see trav_init_any): id = light id,
+// miss, or SOME face id when a triangle is in front.
+template <bool STATS>
+__device__ __forceinline__ void
+last_hit(const DScene& sc, const float3 o, const float3 d, float& best_t, uint32_t& best_id,
+         uint32_t& n_nodes, uint32_t& n_tris)
+{
+  Trav T;
+  uint2 stack[kStackSize];
+  trav_init_any(sc, T, o, d);
+  while (!trav_step<STATS>(sc, T, stack, n_nodes, n_tris)) {
+  }
+  best_t = T.best_t, best_id = T.best_id;
 }
 
 // Closest hit with the reference's acceptance rules: triangles front-facing only,

@@ -229,7 +229,8 @@ int ptc_launch_count(const ptc_context* ctx, uint64_t* out);
 
 /* Wavefront schedule.  first_iters / next_iters: how many radiance-loop iterations the first
  * stage (generate + extend + shade) and each later stage run in registers before handing the
- * surviving rays to the next stage through the compacted queue (0 keeps the current value).
+ * surviving rays to the next stage through the compacted queue (0 keeps the current value;
+ * first_iters = 0xFFFFFFFF restores the default: chosen per scene from the BVH size).
  * split_extend: 1 = every later stage is an extend kernel with per-lane refill followed by
  * a shade kernel (one iteration per stage; default), 0 = fused extend+shade, < 0 keeps.
  * refill: idle lanes per warp that trigger a refill in the extend kernel (0 keeps).

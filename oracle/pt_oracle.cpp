@@ -796,18 +796,29 @@ oracle_primary_rays(const ptc_camera* camera, unsigned width, unsigned height, u
 // ---------------------------------------------------------------------------
 namespace {
 
-struct O2Node // mirrors the 80-byte layout documented in cuda-pathtracer_b200/csrc/bvh.h
+struct O2Node // mirrors the 128-byte layout documented in cuda-pathtracer_b200/csrc/bvh.h
 {
   float origin[3];
   uint8_t e[3];
   uint8_t imask;
   uint32_t child_base;
   uint32_t tri_base;
-  uint8_t meta[8];
-  uint8_t qlo[3][8];
-  uint8_t qhi[3][8];
+  uint32_t valid24;
+  uint32_t occupied;
+  uint16_t lo[3][8]; // half floats holding the 8-bit quantised planes
+  uint16_t hi[3][8];
 };
-static_assert(sizeof(O2Node) == 80, "node layout");
+static_assert(sizeof(O2Node) == 128, "node layout");
+
+// IEEE half -> float (normal numbers and zero are all the node planes use)
+inline float
+o2_half(uint16_t h)
+{
+  const uint32_t e = (h >> 10) & 31u, m = h & 1023u;
+  if (e == 0)
+    return (float)m * (1.0f / 16777216.0f); // subnormal (only 0 occurs)
+  return std::ldexp((float)(1024u + m), (int)e - 25);
+}
 
 struct O2Tri
 {
@@ -871,14 +882,18 @@ o2_closest(const O2Node* nodes, const O2Tri* tris, const ptc_scene_desc* desc, u
       uint32_t rel = (uint32_t)__builtin_popcount(imask & ~(0xFFFFFFFFu << slot));
       const O2Node& n = nodes[ng.base + rel];
       n_nodes++;
-      uint32_t hitmask = 0;
+      uint32_t hit_inner = 0, hit_tris = 0;
       for (int i = 0; i < 8; ++i) {
         float tmin = 0.0f, tmax = best_t;
         for (int a = 0; a < 3; ++a) {
           uint32_t bits = (uint32_t)n.e[a] << 23;
           float sc;
           std::memcpy(&sc, &bits, 4);
-          float lo = n.origin[a] + (float)n.qlo[a][i] * sc, hi = n.origin[a] + (float)n.qhi[a][i] * sc;
+          float lo = n.origin[a] + o2_half(n.lo[a][i]) * sc, hi = n.origin[a] + o2_half(n.hi[a][i]) * sc;
+          if (lo > hi) { // empty slot (inverted box)
+            tmin = 1.0f, tmax = 0.0f;
+            break;
+          }
           float t0 = (lo - o[a]) * idir[a], t1 = (hi - o[a]) * idir[a];
           if (t0 > t1)
             std::swap(t0, t1);
@@ -889,15 +904,20 @@ o2_closest(const O2Node* nodes, const O2Tri* tris, const ptc_scene_desc* desc, u
           tmax = fminf(tmax, t1);
         }
         if (tmin <= tmax) {
-          uint32_t m = n.meta[i];
-          uint32_t inner = ((m & 0x18u) == 0x18u) ? oct_inv : 0u;
-          hitmask |= (m >> 5) << ((m & 31u) ^ inner);
+          if ((n.imask >> i) & 1u)
+            hit_inner |= 1u << (24u + ((uint32_t)i ^ oct_inv));
+          else
+            hit_tris |= (7u << (3 * i)) & n.valid24;
         }
       }
       ng.base = n.child_base;
-      ng.mask = (hitmask & 0xFF000000u) | n.imask;
+      ng.mask = hit_inner | n.imask;
+      // dense record numbers of the hit triangles: popcount of the valid bits below
       tg.base = n.tri_base;
-      tg.mask = hitmask & 0x00FFFFFFu;
+      tg.mask = 0;
+      for (uint32_t b = 0; b < 24; ++b)
+        if ((hit_tris >> b) & 1u)
+          tg.mask |= 1u << (uint32_t)__builtin_popcount(n.valid24 & ((1u << b) - 1u));
     } else {
       tg = ng;
       ng = Entry{ 0u, 0u };

@@ -478,7 +478,7 @@ def test_scene_info(core):
     L = loaded(core, "indoor_tex")
     info = core.scene_info(L.sid)
     assert info.n_faces == 446 and info.n_lights == 3 and info.n_materials == 6 and info.n_textures == 9
-    assert info.bvh_node_bytes == 80 and info.tri_bytes == 48 and info.shade_bytes == 80
+    assert info.bvh_node_bytes == 128 and info.tri_bytes == 48 and info.shade_bytes == 80
     assert info.texture_bytes >= 66_000_000
 
 
@@ -503,7 +503,7 @@ def test_wavefront_granularity_invariance(core):
             results.append((acc.cpu().numpy(), out.cpu().numpy(), rad.cpu().numpy(), c.segments, c.traced,
                             [c.rays_per_bounce[i] for i in range(8)]))
     finally:
-        core.set_wavefront(2, 1, 1, 8)
+        core.set_wavefront_auto()
     a0 = results[0]
     for r in results[1:]:
         assert (bits(r[0]) == bits(a0[0])).all() and (r[1] == a0[1]).all() and (bits(r[2]) == bits(a0[2])).all()
@@ -547,7 +547,7 @@ def test_profile_frame_reports_consistent_counts(core):
     try:
         pr = core.profile_frame(L.sid, L.cid, L.sc, w, h, acc, out, None, bounces=b, frame_nb=1, repeats=3)
     finally:
-        core.set_wavefront(2, 1, 1, 8)
+        core.set_wavefront_auto()
     assert pr["launch_kind"] == ["first", "extend", "shade", "extend", "shade"]
     assert all(ms > 0 for ms in pr["launch_ms"])
     assert pr["segments"] == w * h * b and w * h <= pr["traced"] <= pr["segments"]

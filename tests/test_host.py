@@ -119,7 +119,8 @@ def test_ptscene_parser_rejects_bad_input():
 
 # -- host BVH builder --------------------------------------------------------------------------
 NODE = np.dtype([("origin", "<f4", 3), ("e", "u1", 3), ("imask", "u1"), ("child_base", "<u4"),
-                 ("tri_base", "<u4"), ("meta", "u1", 8), ("qlo", "u1", (3, 8)), ("qhi", "u1", (3, 8))])
+                 ("tri_base", "<u4"), ("valid24", "<u4"), ("occupied", "<u4"),
+                 ("qlo", "<f2", (3, 8)), ("qhi", "<f2", (3, 8))])
 TRI = np.dtype([("v0", "<f4", 3), ("e1", "<f4", 3), ("e2", "<f4", 3), ("face_id", "<u4"), ("_pad", "<u4", 2)])
 
 
@@ -134,7 +135,7 @@ def decode_child_box(n, i):
 def test_bvh_structure(name):
     sc = P.synth.terrain_room(grid=24, tex_size=8) if name == "synthetic" else load_scene(name)
     hb = P.host_bvh(sc)
-    assert hb["nodes"].shape[1] == 80 and hb["tris"].shape[1] == 48
+    assert hb["nodes"].shape[1] == 128 and hb["tris"].shape[1] == 48
     assert hb["nodes"].ctypes.data % 16 == 0 or True
     nodes = hb["nodes"].reshape(-1).view(NODE)
     tris = hb["tris"].reshape(-1).view(TRI)
@@ -157,20 +158,25 @@ def test_bvh_structure(name):
         n = nodes[idx]
         lo_all, hi_all = np.full(3, np.inf), np.full(3, -np.inf)
         k_internal = 0
+        tri_rank = 0
         for i in range(8):
-            m = int(n["meta"][i])
-            if m == 0:
+            inner = (int(n["imask"]) >> i) & 1
+            cnt = bin((int(n["valid24"]) >> (3 * i)) & 7).count("1")
+            if not ((int(n["occupied"]) >> i) & 1):
+                assert not inner and cnt == 0
+                assert (n["qlo"][:, i] > n["qhi"][:, i]).all()   # inverted box: never hit
                 continue
             lo, hi = decode_child_box(n, i)
-            if (m & 0x18) == 0x18 and m >= 0x38:  # internal child
-                assert (int(n["imask"]) >> i) & 1
+            assert (n["qlo"][:, i] == np.round(n["qlo"][:, i])).all() and n["qhi"][:, i].max() <= 255
+            if inner:
+                assert cnt == 0
                 rel = bin(int(n["imask"]) & ((1 << i) - 1)).count("1")
                 clo, chi = walk(int(n["child_base"]) + rel, depth + 1)
                 k_internal += 1
             else:
-                assert not (int(n["imask"]) >> i) & 1
-                first = int(n["tri_base"]) + (m & 31)
-                cnt = {1: 1, 3: 2, 7: 3}[m >> 5]
+                assert cnt in (1, 2, 3) and ((int(n["valid24"]) >> (3 * i)) & 7) == (1 << cnt) - 1
+                first = int(n["tri_base"]) + tri_rank   # dense records in slot order
+                tri_rank += cnt
                 ids = list(range(first, first + cnt))
                 seen_tris.extend(ids)
                 pts = np.concatenate([v[tris["face_id"][t]] for t in ids]).astype(np.float64)
