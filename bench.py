@@ -41,7 +41,9 @@ import numpy as np
 REPO = os.path.dirname(os.path.abspath(__file__))
 PKG_DIR = os.path.join(REPO, "cuda-pathtracer_b200")
 GOLDEN = os.path.join(REPO, "tests", "golden")
-WEAK_DIMS = {1: (1920, 1080), 2: (1920, 2160), 4: (3840, 2160), 8: (3840, 4320)}
+# weak scaling: N x the pixels of the SAME 16:9 view (the camera frames the same picture, so the
+# cost per ray does not change with N); 4 GPUs = BASELINE config 3's 4K frame
+WEAK_DIMS = {1: (1920, 1080), 2: (2720, 1530), 4: (3840, 2160), 8: (5440, 3060)}
 
 
 def pkg():
@@ -214,7 +216,9 @@ def config_dict(args, w, h, sc, l2):
     return {"workload": f"{args.scene} {w}x{h} 1spp/frame bounces={args.bounces} temporal accumulation "
                         f"(BASELINE.json configs[1]; cubemap = reference's constant fallback)",
             "scene": args.scene, "width": w, "height": h, "bounces": args.bounces, "faces": sc.n_faces,
-            "partition": f"{args.gpus} band(s) of 16-row strips, scene replicated", "l2": l2}
+            "partition": (f"{args.gpus} ranks, round-robin 16-row strips, scene replicated"
+                          if args.gpus > 1 and args.partition == "strips" else
+                          f"{args.gpus} contiguous band(s) of whole 16-row strips, scene replicated"), "l2": l2}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -235,13 +239,18 @@ def run_ours(args):
     P = pkg()
     sc = load_scene(P, args.scene)
     n = max(world, 1)
-    w, h = (args.width, args.height) if args.width else WEAK_DIMS.get(n, (1920, 1080 * n))
+    w, h = (args.width, args.height) if args.width else WEAK_DIMS.get(n, (1920 * n, 1080))
     core = P.Core(local)
     sid = core.upload_scene(sc)
     cid = core.set_cubemap(sc.cubemap)
-    gather = P.tiles.BandGather(h, w, world, rank)
-    r0, r1 = gather.band
-    bh = r1 - r0
+    # N > 1: round-robin 16-row strips (strip s -> rank s % N) so every rank sees the same mix
+    # of cheap (sky / far wall) and expensive rows; --partition bands gives contiguous bands
+    interleaved = world > 1 and args.partition == "strips"
+    gather = P.tiles.BandGather(h, w, world, rank, interleaved=interleaved)
+    strips = gather.strips
+    r0, r1 = (0, 0) if interleaved else gather.band
+    rows_kw = {"strips": strips} if interleaved else {"rows": (r0, r1)}
+    bh = gather.n_rows
     dev = torch.device("cuda", local)
     accum = torch.zeros(max(bh, 1), w, 3, device=dev)
     out = torch.zeros(max(bh, 1), w, dtype=torch.int32, device=dev)
@@ -252,7 +261,7 @@ def run_ours(args):
     def frame(k):
         if bh:
             core.render(sid, cid, sc, w, h, accum, out, None, bounces=args.bounces, frame_nb=k,
-                        rows=(r0, r1), stream=stream.cuda_stream)
+                        stream=stream.cuda_stream, **rows_kw)
 
     def barrier():
         if world > 1:
@@ -297,6 +306,9 @@ def run_ours(args):
         ms_total, ms_gather = float(mx[0]), float(mx[4])
     segments, traced, launches = float(stats[1]), float(stats[2]), int(stats[3])
     value = segments / (ms_total * 1e-3) / 1e6
+    if os.environ.get("PTC_BENCH_DEBUG"):
+        print(f"[rank {rank}] frames {ms_frames:.3f} ms  gather {g0.elapsed_time(g1):.3f} ms  rows {bh}",
+              file=sys.stderr, flush=True)
 
     # ---- steady state without the flush (informational) -----------------------------------
     barrier()
@@ -318,20 +330,23 @@ def run_ours(args):
     if bh:
         for k in range(1, W + 1):
             core.render_host_async(sid, cid, sc, w, h, h_accum.numpy(), h_out[k & 1].numpy(), None,
-                                   bounces=args.bounces, frame_nb=k, rows=(r0, r1), upload_accum=(k == 1),
-                                   stream=stream.cuda_stream)
+                                   bounces=args.bounces, frame_nb=k, upload_accum=(k == 1),
+                                   stream=stream.cuda_stream, **rows_kw)
         core.wait()
     barrier()
     t0 = time.perf_counter()
     for k in range(K):
         if bh:
             core.render_host_async(sid, cid, sc, w, h, h_accum.numpy(), h_out[k & 1].numpy(), None,
-                                   bounces=args.bounces, frame_nb=W + 1 + k, rows=(r0, r1),
-                                   stream=stream.cuda_stream)
+                                   bounces=args.bounces, frame_nb=W + 1 + k,
+                                   stream=stream.cuda_stream, **rows_kw)
     if bh:
         core.wait()
+    e2e_own_ms = (time.perf_counter() - t0) * 1e3
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3  # host clock: the call chain ends with frames on the host
+    if os.environ.get("PTC_BENCH_DEBUG"):
+        print(f"[rank {rank}] e2e {e2e_ms:.3f} ms (own {e2e_own_ms:.3f}) for {K} steps", file=sys.stderr, flush=True)
     t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -341,7 +356,7 @@ def run_ours(args):
     # ---- roofline of the dominant kernel (rank 0, N = 1 only needs it) ---------------------
     roof = cpu_base = gpu_base = None
     if rank == 0:
-        roof = roofline(P, core, sid, cid, sc, w, h, r0, r1, args, accum, out, stream)
+        roof = roofline(P, core, sid, cid, sc, w, h, rows_kw, args, accum, out, stream)
         if world == 1 and not args.no_cpu_baseline:
             try:
                 r = cpu_sample(P, sc, w, h, args.bounces, 3, 1, 4.0, prefer_reference=False)
@@ -373,23 +388,23 @@ def run_ours(args):
     return 0
 
 
-def roofline(P, core, sid, cid, sc, w, h, r0, r1, args, accum, out, stream):
+def roofline(P, core, sid, cid, sc, w, h, rows_kw, args, accum, out, stream):
     """The dominant kernel is k_path (extend + shade of one wavefront step; every launch of a
     frame is an instance of it).  achieved = algorithmic bytes of a frame's k_path launches /
     their CUDA-event time (ptc_profile_frame: events around every launch on the launching
-    stream).  Algorithmic bytes (DESIGN.md "Roofline"): BVH nodes visited x 80 B + triangle
+    stream).  Algorithmic bytes (DESIGN.md "Roofline"): BVH nodes visited x 128 B + triangle
     records tested x 48 B (counted by the kernel's own statistics pass) + per traced ray 96 B
     of shading record and diffuse texel + 2 x 64 B per ray handed through a queue + 28 B per
     pixel of accumulator read/write and RGBA8."""
     hbm, how = measured_peaks()
     try:
         prof = core.profile_frame(sid, cid, sc, w, h, accum, out, None, bounces=args.bounces, frame_nb=5,
-                                  rows=(r0, r1), stream=stream.cuda_stream, repeats=8)
+                                  stream=stream.cuda_stream, repeats=8, **rows_kw)
     except Exception as e:
         return {"bound": "hbm", "achieved": None, "peak": hbm, "unit": "GB/s", "frac": None, "traffic": None,
                 "note": f"profile_frame failed: {e}"}
     info = core.scene_info(sid)
-    px = (r1 - r0) * w
+    px = core.band_rows(w, h, **rows_kw) * w
     b_bvh = prof["nodes_visited"] * info.bvh_node_bytes + prof["tris_tested"] * info.tri_bytes
     b_shade = prof["traced"] * (info.shade_bytes + 16)
     b_queue = prof["queue_rays"] * (prof["queue_bytes_per_ray"] * 2 + prof["hit_bytes_per_ray"] * 2
@@ -458,6 +473,8 @@ def main():
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--bounces", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--partition", default="strips", choices=["strips", "bands"],
+                    help="N > 1: round-robin 16-row strips (default) or contiguous bands")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -46,34 +46,74 @@ def accum_band_to_image_rows(band_accum: np.ndarray) -> np.ndarray:
     return band_accum[::-1]
 
 
+def strip_rows_of(height: int, world: int, rank: int, strip: int = STRIP) -> np.ndarray:
+    """Global rows of rank ``rank`` under round-robin strip interleaving (strip s goes to
+    rank s % world), in band-local order -- the order ptc_render uses for
+    ``strip_rows=strip, strip_stride=world, strip_phase=rank`` (device_types.cuh global_row)."""
+    if height <= 0 or world <= 0 or not 0 <= rank < world:
+        raise ValueError("bad height / world / rank")
+    n_strips = (height + strip - 1) // strip
+    parts = [np.arange(s * strip, min((s + 1) * strip, height)) for s in range(rank, n_strips, world)]
+    return np.concatenate(parts) if parts else np.zeros(0, dtype=np.int64)
+
+
 class BandGather:
     """Gathers per-rank bands into the full image with one all_gather.
 
-    ``gather(t)``: ``t`` is this rank's band, shape (band_rows, width, ...) in top-down row
-    order (RGBA8 out buffer as is; accumulator via :func:`accum_band_to_image_rows` or
-    ``flip_rows=True``).  Bands are padded to the largest band so a single equal-size
-    ``all_gather_into_tensor`` (ncclAllGather on the box) moves everything; the result is the
-    full image on every rank.
+    ``interleaved=False``: rank r owns the contiguous band ``row_bands(...)[r]``.
+    ``interleaved=True``: rank r owns strips r, r+world, ... (``strip_rows_of``), which evens
+    out scene-dependent cost between ranks; pass ``strips`` to ``Core.render``.
+
+    ``gather(t)``: ``t`` is this rank's band, shape (band_rows, width, ...) in band-local
+    top-down row order (RGBA8 out buffer as is; accumulator with ``flip_rows=True``).  Bands
+    are padded to the largest band so a single equal-size ``all_gather_into_tensor``
+    (ncclAllGather on the box) moves everything; one row gather then puts every row at its
+    image position.  The result is the full image on every rank.
     """
 
-    def __init__(self, height: int, width: int, world: int, rank: int, strip: int = STRIP):
+    def __init__(self, height: int, width: int, world: int, rank: int, strip: int = STRIP,
+                 interleaved: bool = False):
         self.height, self.width, self.world, self.rank = height, width, world, rank
+        self.strip, self.interleaved = strip, interleaved
         self.bands = row_bands(height, world, strip)
-        self.max_rows = max(e - b for b, e in self.bands)
+        if interleaved:
+            self.rows = [strip_rows_of(height, world, r, strip) for r in range(world)]
+        else:
+            self.rows = [np.arange(b, e) for b, e in self.bands]
+        self.max_rows = max(len(r) for r in self.rows)
+        # image row -> row of the gathered (world * max_rows) buffer
+        src = np.zeros(height, dtype=np.int64)
+        for r, rows in enumerate(self.rows):
+            src[rows] = r * self.max_rows + np.arange(len(rows))
+        self._src = src
+        self._identity = bool(np.array_equal(src, np.arange(height)))
         self._pad = {}
         self._all = {}
+        self._idx = {}
 
     @property
     def band(self) -> Tuple[int, int]:
+        """Contiguous mode: [begin, end) of this rank."""
+        if self.interleaved:
+            raise ValueError("interleaved partition has no contiguous band; use .strips / .n_rows")
         return self.bands[self.rank]
+
+    @property
+    def n_rows(self) -> int:
+        return len(self.rows[self.rank])
+
+    @property
+    def strips(self):
+        """(strip_rows, strip_stride, strip_phase) for Core.render, or None when contiguous."""
+        return (self.strip, self.world, self.rank) if self.interleaved else None
 
     def gather(self, t, flip_rows: bool = False):
         import torch
         import torch.distributed as dist
 
-        b, e = self.band
-        if t.shape[0] != e - b or t.shape[1] != self.width:
-            raise ValueError(f"band tensor has shape {tuple(t.shape)}, expected ({e - b}, {self.width}, ...)")
+        n = self.n_rows
+        if t.shape[0] != n or t.shape[1] != self.width:
+            raise ValueError(f"band tensor has shape {tuple(t.shape)}, expected ({n}, {self.width}, ...)")
         if flip_rows:
             t = torch.flip(t, dims=[0])
         key = (t.dtype, t.device, tuple(t.shape[2:]))
@@ -82,13 +122,13 @@ class BandGather:
                                          dtype=t.dtype, device=t.device)
             self._all[key] = torch.empty((self.world * self.max_rows, self.width) + tuple(t.shape[2:]),
                                          dtype=t.dtype, device=t.device)
+            self._idx[key] = torch.from_numpy(self._src).to(t.device)
         pad, out = self._pad[key], self._all[key]
-        pad[: e - b].copy_(t)
+        pad[:n].copy_(t)
         if self.world == 1:
             out.copy_(pad)
         else:
             dist.all_gather_into_tensor(out, pad)
-        if all(eb - bb == self.max_rows for bb, eb in self.bands):
+        if self._identity:
             return out[: self.height]
-        parts = [out[r * self.max_rows: r * self.max_rows + (eb - bb)] for r, (bb, eb) in enumerate(self.bands)]
-        return torch.cat(parts, dim=0)
+        return out.index_select(0, self._idx[key])

@@ -266,6 +266,16 @@ full_acc = g.gather(band_acc_bottom_up, flip_rows=True)
 assert full_rgba.shape == (h, w, 4), full_rgba.shape
 assert (full_rgba.numpy() == rgba).all()
 assert (full_acc.numpy().view(np.uint32) == np.ascontiguousarray(acc[::-1]).view(np.uint32)).all()
+# round-robin 16-row strips (strip s -> rank s % world): same image, different ownership
+g2 = P.tiles.BandGather(h, w, world, rank, interleaved=True)
+rows = g2.rows[rank]
+assert g2.strips == (16, world, rank) and len(rows) == g2.n_rows
+assert sorted(np.concatenate(g2.rows).tolist()) == list(range(h))
+acc_top_down = np.ascontiguousarray(acc[::-1])
+full_rgba2 = g2.gather(torch.from_numpy(np.ascontiguousarray(rgba[rows])))
+full_acc2 = g2.gather(torch.from_numpy(np.ascontiguousarray(acc_top_down[rows][::-1])), flip_rows=True)
+assert (full_rgba2.numpy() == rgba).all()
+assert (full_acc2.numpy().view(np.uint32) == acc_top_down.view(np.uint32)).all()
 dist.barrier()
 dist.destroy_process_group()
 print("rank", rank, "ok")
