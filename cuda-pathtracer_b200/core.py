@@ -72,7 +72,8 @@ EXPORTS = ["ptc_abi_version", "ptc_create", "ptc_destroy", "ptc_last_error", "pt
            "ptc_reset_accumulation", "ptc_counters_get", "ptc_counters_reset",
            "ptc_trace_primary", "ptc_intersect_rays", "ptc_debug_rng", "ptc_host_bvh_build",
            "ptc_host_bvh_free", "ptc_band_rows", "ptc_launch_count", "ptc_set_wavefront",
-           "ptc_profile_frame", "ptc_render_host_async", "ptc_wait"]
+           "ptc_profile_frame", "ptc_render_host_async", "ptc_wait",
+           "ptc_upload_scene_from_device", "ptc_set_cubemap_from_array"]
 
 _lib = None
 
@@ -88,7 +89,8 @@ def load_library() -> C.CDLL:
         if not os.path.exists(LIB_PATH):
             raise PtcError(f"{LIB_PATH} is missing: run `python __graft_entry__.py` (build()) first; "
                            "this package has no CPU fallback")
-        lib = C.CDLL(LIB_PATH)
+        # PTC_LIBRARY: experiment builds of the same ABI (tools/build_variants.py)
+        lib = C.CDLL(os.environ.get("PTC_LIBRARY") or LIB_PATH)
         lib.ptc_last_error.restype = C.c_char_p
         lib.ptc_last_error.argtypes = [C.c_void_p]
         lib.ptc_destroy.restype = None

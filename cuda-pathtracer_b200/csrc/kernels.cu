@@ -35,8 +35,14 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
        const uint4* __restrict__ hits,
        const uint32_t* __restrict__ qin_count, const RayQueue qout, uint32_t* __restrict__ qout_count,
        const FrameOut fo, Counters* __restrict__ ctr, uint32_t* __restrict__ work, const int bounce0,
-       const int n_iters)
+       const int n_iters, const int stack_cap)
 {
+#ifdef PTC_STAGE_LOCAL_STACK
+  LocalStack stack;
+#else
+  extern __shared__ uint2 s_stack[]; // stack_cap entries x kBlock threads (none when HITS)
+  SharedStack stack{ s_stack + threadIdx.x, stack_cap };
+#endif
   __shared__ uint32_t s_rays[16];
   if (threadIdx.x < 16)
     s_rays[threadIdx.x] = 0;
@@ -98,7 +104,7 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
       if (valid) {
         float t, u, v;
         uint32_t id;
-        closest_hit<STATS>(sc, P.origin, P.dir, t, id, u, v, my_nodes, my_tris);
+        closest_hit<STATS>(sc, stack, P.origin, P.dir, t, id, u, v, my_nodes, my_tris);
         if (id != 0xFFFFFFFFu) {
           Surface s;
           resolve_hit(sc, id, t, u, v, P.dir, P.spec_carry, s);
@@ -131,9 +137,9 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
               lights_hit(sc, P.origin, P.dir, t, id);
           } else if (last) {
             u = v = 0.f;
-            last_hit<STATS>(sc, P.origin, P.dir, t, id, my_nodes, my_tris);
+            last_hit<STATS>(sc, stack, P.origin, P.dir, t, id, my_nodes, my_tris);
           } else {
-            closest_hit<STATS>(sc, P.origin, P.dir, t, id, u, v, my_nodes, my_tris);
+            closest_hit<STATS>(sc, stack, P.origin, P.dir, t, id, u, v, my_nodes, my_tris);
           }
           if (last && id < sc.n_faces) {
             done = true; // a triangle in front on the last iteration adds no radiance
@@ -195,15 +201,22 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
 // hit and, as soon as `refill` lanes of the warp are idle, the idle lanes pull new rays
 // from the queue (one warp-aggregated atomic), so the traversal loop stays full.
 // ---------------------------------------------------------------------------
+// (A 4-CTAs-per-SM build at 64 registers was measured: no gain on either the 28 KB or the
+// 1.4 GB scene -- the limit is issue slots / L1 wavefronts, not warps in flight.)
 template <bool STATS>
 __global__ void __launch_bounds__(kBlock, 3)
 k_extend(const DScene sc, const RayQueue qin, const uint32_t* __restrict__ qin_count,
          uint4* __restrict__ hits, uint32_t* __restrict__ work, Counters* __restrict__ ctr,
-         const uint32_t refill, const int last)
+         const uint32_t refill, const int last, const int stack_cap)
 {
+#ifdef PTC_STAGE_LOCAL_STACK
+  LocalStack stack;
+#else
+  extern __shared__ uint2 s_stack[]; // stack_cap entries x kBlock threads
+  SharedStack stack{ s_stack + threadIdx.x, stack_cap };
+#endif
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t n = *qin_count;
-  uint2 stack[kStackSize];
   Trav T;
   bool have = false, exhausted = false;
   uint32_t slot = 0, my_nodes = 0, my_tris = 0;
@@ -266,7 +279,8 @@ k_primary_hits(FrameParams fp, DScene sc, int32_t* __restrict__ ids, float* __re
   primary_ray(fp, x, global_row(fp, lrow), rng, o, d);
   float t, u, v;
   uint32_t id, nn = 0, nt = 0;
-  closest_hit<false>(sc, o, d, t, id, u, v, nn, nt);
+  LocalStack stack;
+  closest_hit<false>(sc, stack, o, d, t, id, u, v, nn, nt);
   if (ids)
     ids[p] = (int32_t)id;
   if (ts)
@@ -283,7 +297,8 @@ k_intersect_rays(DScene sc, const float* __restrict__ origins, const float* __re
     return;
   float t, u, v;
   uint32_t id, nn = 0, nt = 0;
-  closest_hit<true>(sc, mk3(origins[3 * i], origins[3 * i + 1], origins[3 * i + 2]),
+  LocalStack stack;
+  closest_hit<true>(sc, stack, mk3(origins[3 * i], origins[3 * i + 1], origins[3 * i + 2]),
                     mk3(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]), t, id, u, v, nn, nt);
   if (ids)
     ids[i] = (int32_t)id;
@@ -343,75 +358,112 @@ blocks_for(uint64_t n, uint32_t block)
   return (uint32_t)((n + block - 1) / block);
 }
 
+size_t
+stack_smem_bytes(int stack_cap)
+{
+#ifdef PTC_STAGE_LOCAL_STACK
+  return 0;
+#else
+  return (size_t)stack_cap * kBlock * sizeof(uint2);
+#endif
+}
+
+// every scene may need a different amount: opt in to the device maximum once (the attribute is
+// per function, not per launch, and must not shrink when a smaller scene is uploaded later)
+static int
+max_optin_smem()
+{
+  int dev = 0, v = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  return v - 64; // the static s_rays[16] of k_path shares the budget
+}
+
 template <bool FIRST, bool STATS, bool HITS>
 static int
-occ()
+occ(size_t smem)
 {
   int n = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_path<FIRST, STATS, HITS>, kBlock, 0) != cudaSuccess || n < 1)
-    n = 1;
+  cudaFuncSetAttribute(k_path<FIRST, STATS, HITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin_smem());
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_path<FIRST, STATS, HITS>, kBlock, smem) != cudaSuccess)
+    n = 0;
   return n;
 }
 
+// Resident CTAs per SM for a scene whose traversal stack needs `stack_cap` entries per thread
+// (0 when the stack does not fit the SM's shared memory at all).  Also opts the kernel in to
+// that much dynamic shared memory.
 int
-path_kernel_blocks_per_sm(bool first, bool stats, bool pretraced)
+path_kernel_blocks_per_sm(bool first, bool stats, bool pretraced, int stack_cap)
 {
+  const size_t smem = stack_smem_bytes(stack_cap);
   if (first)
-    return stats ? occ<true, true, false>() : occ<true, false, false>();
-  if (pretraced)
-    return stats ? occ<false, true, true>() : occ<false, false, true>();
-  return stats ? occ<false, true, false>() : occ<false, false, false>();
+    return stats ? occ<true, true, false>(smem) : occ<true, false, false>(smem);
+  if (pretraced) // shade-only stage: no traversal, no stack
+    return stats ? occ<false, true, true>(0) : occ<false, false, true>(0);
+  return stats ? occ<false, true, false>(smem) : occ<false, false, false>(smem);
 }
 
 int
-extend_kernel_blocks_per_sm(bool stats)
+extend_kernel_blocks_per_sm(bool stats, int stack_cap)
 {
+  const size_t smem = stack_smem_bytes(stack_cap);
   int n = 0;
-  cudaError_t e = stats ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_extend<true>, kBlock, 0)
-                        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_extend<false>, kBlock, 0);
-  return (e != cudaSuccess || n < 1) ? 1 : n;
+  cudaError_t e;
+  if (stats) {
+    cudaFuncSetAttribute(k_extend<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin_smem());
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_extend<true>, kBlock, smem);
+  } else {
+    cudaFuncSetAttribute(k_extend<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin_smem());
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_extend<false>, kBlock, smem);
+  }
+  return e != cudaSuccess ? 0 : n;
 }
 
-#define PTC_LAUNCH_PATH(F, S, H)                                                                   \
-  k_path<F, S, H><<<grid, kBlock, 0, s>>>(fp, sc, cube, qin, hits, qin_count, qout, qout_count, fo, ctr, \
-                                          work, bounce0, n_iters)
+#define PTC_LAUNCH_PATH(F, S, H, SMEM)                                                             \
+  k_path<F, S, H><<<grid, kBlock, SMEM, s>>>(fp, sc, cube, qin, hits, qin_count, qout, qout_count, fo, ctr, \
+                                             work, bounce0, n_iters, stack_cap)
 
 void
 launch_path(bool first, bool stats, uint32_t grid, const FrameParams& fp, const DScene& sc,
             cudaTextureObject_t cube, const RayQueue& qin, const uint4* hits, const uint32_t* qin_count,
             const RayQueue& qout, uint32_t* qout_count, const FrameOut& fo, Counters* ctr,
-            uint32_t* work, int bounce0, int n_iters, cudaStream_t s)
+            uint32_t* work, int bounce0, int n_iters, int stack_cap, cudaStream_t s)
 {
   if (!grid)
     return;
+  const size_t smem = stack_smem_bytes(stack_cap);
   if (first) {
     if (stats)
-      PTC_LAUNCH_PATH(true, true, false);
+      PTC_LAUNCH_PATH(true, true, false, smem);
     else
-      PTC_LAUNCH_PATH(true, false, false);
+      PTC_LAUNCH_PATH(true, false, false, smem);
   } else if (hits) {
     if (stats)
-      PTC_LAUNCH_PATH(false, true, true);
+      PTC_LAUNCH_PATH(false, true, true, 0);
     else
-      PTC_LAUNCH_PATH(false, false, true);
+      PTC_LAUNCH_PATH(false, false, true, 0);
   } else {
     if (stats)
-      PTC_LAUNCH_PATH(false, true, false);
+      PTC_LAUNCH_PATH(false, true, false, smem);
     else
-      PTC_LAUNCH_PATH(false, false, false);
+      PTC_LAUNCH_PATH(false, false, false, smem);
   }
 }
 
 void
 launch_extend(bool stats, uint32_t grid, const DScene& sc, const RayQueue& qin, const uint32_t* qin_count,
-              uint4* hits, uint32_t* work, Counters* ctr, uint32_t refill, bool last, cudaStream_t s)
+              uint4* hits, uint32_t* work, Counters* ctr, uint32_t refill, bool last, int stack_cap,
+              cudaStream_t s)
 {
   if (!grid)
     return;
+  const size_t smem = stack_smem_bytes(stack_cap);
+  const int l = last ? 1 : 0;
   if (stats)
-    k_extend<true><<<grid, kBlock, 0, s>>>(sc, qin, qin_count, hits, work, ctr, refill, last ? 1 : 0);
+    k_extend<true><<<grid, kBlock, smem, s>>>(sc, qin, qin_count, hits, work, ctr, refill, l, stack_cap);
   else
-    k_extend<false><<<grid, kBlock, 0, s>>>(sc, qin, qin_count, hits, work, ctr, refill, last ? 1 : 0);
+    k_extend<false><<<grid, kBlock, smem, s>>>(sc, qin, qin_count, hits, work, ctr, refill, l, stack_cap);
 }
 
 void

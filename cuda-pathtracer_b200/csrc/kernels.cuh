@@ -5,9 +5,14 @@
 
 namespace ptc {
 
-// resident CTAs per SM of the path / extend kernels (size the persistent grids)
-int path_kernel_blocks_per_sm(bool first, bool stats, bool pretraced);
-int extend_kernel_blocks_per_sm(bool stats);
+// The stage kernels keep the per-ray traversal stack in dynamic shared memory:
+// stack_cap entries (levels of the scene's wide tree + 1 + kTriBacklog) x kBlock threads x 8 B.
+size_t stack_smem_bytes(int stack_cap);
+
+// resident CTAs per SM of the path / extend kernels for that stack size (size the persistent
+// grids; 0 = the stack does not fit).  Also opts the kernel in to the shared memory it needs.
+int path_kernel_blocks_per_sm(bool first, bool stats, bool pretraced, int stack_cap);
+int extend_kernel_blocks_per_sm(bool stats, int stack_cap);
 
 // One wavefront step: `n_iters` x [extend -> shade] starting at radiance-loop iteration
 // `bounce0`.  first: rays are generated (8x4 pixel tile per warp) instead of read from
@@ -18,7 +23,7 @@ void launch_path(bool first, bool stats, uint32_t grid, const FrameParams& fp, c
                  cudaTextureObject_t cube, const RayQueue& qin, const uint4* hits,
                  const uint32_t* qin_count, const RayQueue& qout, uint32_t* qout_count,
                  const FrameOut& fo, Counters* ctr, uint32_t* work, int bounce0, int n_iters,
-                 cudaStream_t s);
+                 int stack_cap, cudaStream_t s);
 
 // Closest triangle hit of every ray of `qin` -> hits[slot] = (t, face id | ~0, u, v), with
 // per-lane refill once `refill` lanes of a warp are idle.  last: the rays belong to the last
@@ -26,7 +31,7 @@ void launch_path(bool first, bool stats, uint32_t grid, const FrameParams& fp, c
 // record then already includes the sphere lights.
 void launch_extend(bool stats, uint32_t grid, const DScene& sc, const RayQueue& qin,
                    const uint32_t* qin_count, uint4* hits, uint32_t* work, Counters* ctr,
-                   uint32_t refill, bool last, cudaStream_t s);
+                   uint32_t refill, bool last, int stack_cap, cudaStream_t s);
 
 void launch_primary_hits(const FrameParams& fp, const DScene& sc, int32_t* ids, float* ts,
                          cudaStream_t s);

@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -25,6 +26,10 @@ struct SceneDev
   DScene d{};
   std::vector<void*> allocs;
   ptc_scene_info info{};
+  // traversal stack entries per thread (levels of the wide tree + 1 + kTriBacklog) and the
+  // persistent grids that follow from it: resident CTAs per SM x SMs, [0] plain / [1] statistics
+  int stack_cap = 0;
+  int grid_first[2] = { 0, 0 }, grid_next[2] = { 0, 0 }, grid_shade[2] = { 0, 0 }, grid_extend[2] = { 0, 0 };
 };
 
 struct CubeDev
@@ -46,7 +51,6 @@ struct ptc_context
   Counters* ctr = nullptr;
   int n_sms = 148;
   // persistent grids, [stats]: first stage, fused later stage, shade-after-extend, extend
-  int grid_first[2] = { 0, 0 }, grid_next[2] = { 0, 0 }, grid_shade[2] = { 0, 0 }, grid_extend[2] = { 0, 0 };
   uint32_t first_iters = 0, next_iters = 1; // first_iters 0 = per scene (frame_schedule) // wavefront granularity (ptc_set_wavefront)
   uint32_t split_extend = 1;   // later stages: separate refilling extend kernel + shade kernel
   uint32_t refill = 8;         // idle lanes of a warp that trigger a refill in k_extend
@@ -289,7 +293,7 @@ enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp,
   if (rc)
     return rc;
   FrameOut fo{ accum, out, rad };
-  Step steps[kMaxBounces + 1];
+  Step steps[kMaxBounces + 2];
   const int n_steps = frame_schedule(ctx, fp, scene_bvh_bytes(ctx, a->scene_id), steps);
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->counts, 0, sizeof(uint32_t) * kCountSlots, s));
   int n_ev = 0;
@@ -303,21 +307,23 @@ enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp,
     uint32_t* work = ctx->counts + kMaxBounces + 2 + 2 * k;
     if (st.first) {
       const uint32_t want = (tiles + kBlock / 32 - 1) / (kBlock / 32);
-      const uint32_t cap = (uint32_t)ctx->grid_first[stats];
+      const uint32_t cap = (uint32_t)sc.grid_first[stats];
       grid = want < cap ? want : cap;
     } else if (ctx->split_extend) {
-      launch_extend(stats, (uint32_t)ctx->grid_extend[stats], sc.d, ctx->queue[k & 1], ctx->counts + k,
-                    ctx->hits, work + 1, ctx->ctr, ctx->refill, st.bounce0 + 1 >= fp.max_bounces, s);
+      launch_extend(stats, (uint32_t)sc.grid_extend[stats], sc.d, ctx->queue[k & 1], ctx->counts + k,
+                    ctx->hits, work + 1, ctx->ctr, ctx->refill, st.bounce0 + 1 >= fp.max_bounces,
+                    sc.stack_cap, s);
       ctx->launches++;
       if (ev)
         CUDA_TRY(ctx, cudaEventRecord(ev[++n_ev], s));
       hits = ctx->hits;
-      grid = (uint32_t)ctx->grid_shade[stats];
+      grid = (uint32_t)sc.grid_shade[stats];
     } else {
-      grid = (uint32_t)ctx->grid_next[stats];
+      grid = (uint32_t)sc.grid_next[stats];
     }
     launch_path(st.first, stats, grid, fp, sc.d, cm.tex, ctx->queue[k & 1], hits, ctx->counts + k,
-                ctx->queue[(k + 1) & 1], ctx->counts + k + 1, fo, ctx->ctr, work, st.bounce0, st.n_iters, s);
+                ctx->queue[(k + 1) & 1], ctx->counts + k + 1, fo, ctx->ctr, work, st.bounce0, st.n_iters,
+                sc.stack_cap, s);
     ctx->launches++;
     if (ev)
       CUDA_TRY(ctx, cudaEventRecord(ev[++n_ev], s));
@@ -380,13 +386,6 @@ ptc_create(int device, ptc_context** out)
   cudaMemset(ctx->ctr, 0, sizeof(Counters));
   cudaMemset(ctx->counts, 0, sizeof(uint32_t) * kCountSlots);
   cudaDeviceGetAttribute(&ctx->n_sms, cudaDevAttrMultiProcessorCount, device);
-  // persistent grids: resident CTAs per SM x SMs (148 on B200)
-  for (int st = 0; st < 2; ++st) {
-    ctx->grid_first[st] = ctx->n_sms * path_kernel_blocks_per_sm(true, st != 0, false);
-    ctx->grid_next[st] = ctx->n_sms * path_kernel_blocks_per_sm(false, st != 0, false);
-    ctx->grid_shade[st] = ctx->n_sms * path_kernel_blocks_per_sm(false, st != 0, true);
-    ctx->grid_extend[st] = ctx->n_sms * extend_kernel_blocks_per_sm(st != 0);
-  }
   *out = ctx;
   return PTC_OK;
 }
@@ -508,6 +507,17 @@ ptc_upload_scene(ptc_context* ctx, const ptc_scene_desc* desc, int32_t* scene_id
   if ((rc = dev_upload(ctx, s, dt.data(), dt.size(), &s.d.textures)))
     return rc;
 
+  // persistent grids: resident CTAs per SM x SMs (148 on B200), for this scene's stack size
+  s.stack_cap = (int)bvh.stats.wide_depth + 1 + kTriBacklog;
+  for (int st = 0; st < 2; ++st) {
+    s.grid_first[st] = ctx->n_sms * path_kernel_blocks_per_sm(true, st != 0, false, s.stack_cap);
+    s.grid_next[st] = ctx->n_sms * path_kernel_blocks_per_sm(false, st != 0, false, s.stack_cap);
+    s.grid_shade[st] = ctx->n_sms * path_kernel_blocks_per_sm(false, st != 0, true, s.stack_cap);
+    s.grid_extend[st] = ctx->n_sms * extend_kernel_blocks_per_sm(st != 0, s.stack_cap);
+  }
+  if (!s.grid_first[0] || !s.grid_next[0] || !s.grid_extend[0] || !s.grid_first[1] || !s.grid_extend[1])
+    return fail(ctx, PTC_ERR_INVALID, "traversal stack does not fit in shared memory");
+
   s.info.n_faces = n_faces;
   s.info.n_lights = desc->n_lights;
   s.info.n_materials = desc->n_materials;
@@ -564,6 +574,109 @@ ptc_set_cubemap(ptc_context* ctx, const float* faces, uint32_t size, int32_t* cu
   ctx->cubemaps.push_back(c);
   *cubemap_id = (int32_t)ctx->cubemaps.size() - 1;
   return PTC_OK;
+}
+
+// The reference's device tree, read back record by record (see ptcore.h).
+int
+ptc_upload_scene_from_device(ptc_context* ctx, const ptc_ref_scenes* scenes, uint32_t scene_index,
+                             int32_t* scene_id)
+{
+  if (!ctx || !scenes || !scene_id)
+    return PTC_ERR_INVALID;
+  if (!scenes->scenes)
+    return fail(ctx, PTC_ERR_INVALID, "Scenes.scenes is null");
+  DeviceGuard g(ctx->device);
+  struct RefSceneData // scene::SceneData, scene_data.h:71-76
+  {
+    ptc_ref_buffer meshes, materials, lights;
+  };
+  static_assert(sizeof(ptc_ref_buffer) == 16 && sizeof(RefSceneData) == 48, "reference layout");
+  const void* d_sd = nullptr;
+  CUDA_TRY(ctx, cudaMemcpy(&d_sd, scenes->scenes + scene_index, sizeof(void*), cudaMemcpyDeviceToHost));
+  if (!d_sd)
+    return fail(ctx, PTC_ERR_INVALID, "scene pointer is null");
+  RefSceneData sd;
+  CUDA_TRY(ctx, cudaMemcpy(&sd, d_sd, sizeof(sd), cudaMemcpyDeviceToHost));
+  std::vector<ptc_ref_buffer> meshes(sd.meshes.size); // scene::Mesh == Buffer<Face>
+  if (sd.meshes.size)
+    CUDA_TRY(ctx, cudaMemcpy(meshes.data(), sd.meshes.data, meshes.size() * sizeof(ptc_ref_buffer),
+                             cudaMemcpyDeviceToHost));
+  std::vector<uint32_t> counts(meshes.size());
+  size_t n_faces = 0;
+  for (size_t m = 0; m < meshes.size(); ++m)
+    n_faces += (counts[m] = meshes[m].size);
+  std::vector<ptc_face> faces(n_faces);
+  size_t off = 0;
+  for (size_t m = 0; m < meshes.size(); ++m) {
+    if (counts[m])
+      CUDA_TRY(ctx, cudaMemcpy(faces.data() + off, meshes[m].data, counts[m] * sizeof(ptc_face),
+                               cudaMemcpyDeviceToHost));
+    off += counts[m];
+  }
+  std::vector<ptc_material> mats(sd.materials.size);
+  std::vector<ptc_light> lights(sd.lights.size);
+  if (!mats.empty())
+    CUDA_TRY(ctx, cudaMemcpy(mats.data(), sd.materials.data, mats.size() * sizeof(ptc_material),
+                             cudaMemcpyDeviceToHost));
+  if (!lights.empty())
+    CUDA_TRY(ctx, cudaMemcpy(lights.data(), sd.lights.data, lights.size() * sizeof(ptc_light),
+                             cudaMemcpyDeviceToHost));
+  for (ptc_material& m : mats)
+    m._pad = 0;
+  // global texture table; texels come back to the host because ptc_upload_scene packs them
+  // into the context's own arena (the reference keeps one cudaMalloc per texture)
+  std::vector<ptc_texture> tex(scenes->textures.size);
+  if (!tex.empty())
+    CUDA_TRY(ctx, cudaMemcpy(tex.data(), scenes->textures.data, tex.size() * sizeof(ptc_texture),
+                             cudaMemcpyDeviceToHost));
+  std::vector<std::vector<float>> texels(tex.size());
+  for (size_t i = 0; i < tex.size(); ++i) {
+    if (tex[i].w < 0 || tex[i].h < 0 || tex[i].nb_chan < 0)
+      return fail(ctx, PTC_ERR_INVALID, "negative texture dimensions in the device table");
+    const size_t n = (size_t)tex[i].w * tex[i].h * tex[i].nb_chan;
+    texels[i].resize(n);
+    if (n)
+      CUDA_TRY(ctx, cudaMemcpy(texels[i].data(), tex[i].data, n * sizeof(float), cudaMemcpyDeviceToHost));
+    tex[i].data = texels[i].data();
+  }
+  ptc_scene_desc d;
+  memset(&d, 0, sizeof(d));
+  d.faces = faces.data();
+  d.mesh_face_counts = counts.data();
+  d.n_meshes = (uint32_t)counts.size();
+  d.materials = mats.data();
+  d.n_materials = (uint32_t)mats.size();
+  d.lights = lights.data();
+  d.n_lights = (uint32_t)lights.size();
+  d.textures = tex.data();
+  d.n_textures = (uint32_t)tex.size();
+  return ptc_upload_scene(ctx, &d, scene_id);
+}
+
+int
+ptc_set_cubemap_from_array(ptc_context* ctx, const void* cuda_array, int32_t* cubemap_id)
+{
+  if (!ctx || !cuda_array || !cubemap_id)
+    return PTC_ERR_INVALID;
+  DeviceGuard g(ctx->device);
+  cudaArray_t src = (cudaArray_t)const_cast<void*>(cuda_array);
+  cudaChannelFormatDesc desc;
+  cudaExtent ext;
+  unsigned flags = 0;
+  CUDA_TRY(ctx, cudaArrayGetInfo(&desc, &ext, &flags, src));
+  if (!(flags & cudaArrayCubemap) || ext.depth != 6 || ext.width != ext.height ||
+      desc.f != cudaChannelFormatKindFloat || desc.x != 32 || desc.y != 32 || desc.z != 32 || desc.w != 32)
+    return fail(ctx, PTC_ERR_INVALID, "expected an RGBA32F cubemap array (gpu_processor.cpp:134-152)");
+  // through the host: one-time, and keeps a single code path for array creation
+  std::vector<float> faces((size_t)ext.width * ext.height * 6 * 4);
+  cudaMemcpy3DParms p;
+  memset(&p, 0, sizeof(p));
+  p.srcArray = src;
+  p.dstPtr = make_cudaPitchedPtr(faces.data(), ext.width * sizeof(float) * 4, ext.width, ext.height);
+  p.extent = make_cudaExtent(ext.width, ext.height, 6);
+  p.kind = cudaMemcpyDeviceToHost;
+  CUDA_TRY(ctx, cudaMemcpy3D(&p));
+  return ptc_set_cubemap(ctx, faces.data(), (uint32_t)ext.width, cubemap_id);
 }
 
 int
@@ -768,7 +881,7 @@ ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeat
   if (!args->accum)
     return fail(ctx, PTC_ERR_INVALID, "accum is required");
   cudaStream_t s = (cudaStream_t)args->stream;
-  Step steps[kMaxBounces + 1];
+  Step steps[kMaxBounces + 2];
   const int n_steps = frame_schedule(ctx, fp, scene_bvh_bytes(ctx, args->scene_id), steps);
   // the launches of one frame: kind 0 = first stage, 1 = fused later stage, 2 = extend, 3 = shade
   struct L { uint32_t kind, bounce0, iters; };

@@ -170,7 +170,40 @@ spread3(uint32_t x)
   return x;
 }
 
-// Traversal state of one ray (registers; the stack lives in local memory, L1-resident).
+// Per-ray traversal stack.  Two homes with one interface:
+//  * SharedStack -- the stage kernels: entry e of thread t lives at smem[(e * kBlock + t) * 8],
+//    so whatever depth each lane is at, a warp's push/pop is one conflict-free shared-memory
+//    access (2 wavefronts for 64 bits).  In local memory the same access costs one L1 wavefront
+//    per lane that sits at a different depth (measured on the 10 M-triangle scene: 37 % of all
+//    L1 wavefronts of k_extend).  `cap` = levels of the scene's wide tree + 1 + kTriBacklog.
+//  * LocalStack -- the debug / parity kernels (one thread per ray, no shared-memory budget).
+struct LocalStack
+{
+  uint2 a[kStackSize];
+  __device__ __forceinline__ uint2 get(int i) const { return a[i]; }
+  __device__ __forceinline__ void put(int i, uint2 v) { a[i] = v; }
+  __device__ __forceinline__ int top() const { return kStackSize; }
+};
+
+struct SharedStack
+{
+  uint2* base; // smem + threadIdx.x
+  int cap;
+  __device__ __forceinline__ uint2 get(int i) const { return base[i * kBlock]; }
+  __device__ __forceinline__ void put(int i, uint2 v) { base[i * kBlock] = v; }
+  __device__ __forceinline__ int top() const { return cap; }
+};
+
+// 32-byte read-only load (sm_100: LDG.E.256): one L1 tag request where two 16-byte loads make two.
+__device__ __forceinline__ void
+ldg256(const uint4* p, uint4& a, uint4& b)
+{
+  asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+      : "l"(p));
+}
+
+// Traversal state of one ray (registers; the stack: see above).
 struct Trav
 {
   float3 o, d, idir;
@@ -180,7 +213,7 @@ struct Trav
   uint2 tg; // triangle group: tri_base, valid24 of its node
   uint32_t tmask; // triangles of tg still to test (bits of the node's 24-bit triangle space)
   int sp;  // node-group entries on stack[0 .. sp)
-  int tsp; // deferred triangle groups on stack[kStackSize - tsp .. kStackSize)
+  int tsp; // deferred triangle groups on stack[top - tsp .. top)
   float best_t, best_u, best_v;
   uint32_t best_id;
   bool any;  // any-hit query: stop at the first accepted triangle (trav_init_any)
@@ -239,22 +272,25 @@ trav_init_any(const DScene& sc, Trav& T, const float3 o, const float3 d)
 // (t, face id) and boxes are only culled when strictly farther than the best hit), so the
 // loop is shaped for SIMT convergence: a leaf's remaining triangles are deferred on the
 // stack instead of being looped over while the other lanes of the warp idle.
-template <bool STATS>
+template <bool STATS, typename Stack>
 __device__ __forceinline__ bool
-trav_step(const DScene& sc, Trav& T, uint2* stack, uint32_t& n_nodes, uint32_t& n_tris)
+trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& n_tris)
 {
   // keep both tests fed: an exhausted group is replaced from its stack right away, so a lane
   // runs a triangle test AND a node test in the same iteration whenever it has either left
   if (!T.tmask && T.tsp) {
-    const uint2 e = stack[kStackSize - T.tsp]; // (tri_base, valid24 | leaf-slot hit mask << 24)
+    const uint2 e = stack.get(stack.top() - T.tsp); // (tri_base, valid24 | leaf-slot hit mask << 24)
     --T.tsp;
     T.tg = make_uint2(e.x, e.y & 0x00FFFFFFu);
     T.tmask = (spread3(e.y >> 24) * 7u) & T.tg.y;
   }
   if (!(T.ng.y & 0xFF000000u) && T.sp)
-    T.ng = stack[--T.sp];
+    T.ng = stack.get(--T.sp);
 
   // -- at most one triangle test ------------------------------------------------------
+  // (Holding triangle tests back until N lanes of the warp have one pending was measured for
+  // N = 8..24: 4-7 % slower on both ends of the scene-size range -- the later a hit shrinks
+  // best_t, the more boxes are entered.)
   if (T.tmask) {
     const uint32_t bit = __ffs(T.tmask) - 1u;
     T.tmask &= T.tmask - 1u;
@@ -285,13 +321,19 @@ trav_step(const DScene& sc, Trav& T, uint2* stack, uint32_t& n_nodes, uint32_t& 
     T.ng.y &= ~(1u << bit);
     const uint32_t imask_parent = T.ng.y & 0xFFu;
     if (T.ng.y & 0xFF000000u)
-      stack[T.sp++] = T.ng;
+      stack.put(T.sp++, T.ng);
     const uint32_t slot = (bit - 24u) ^ T.oct_inv;
     const uint32_t rel = __popc(imask_parent & ~(0xFFFFFFFFu << slot));
     const uint32_t vec0 = (T.ng.x + rel) * kNodeVec;
 
-    const uint4 n0 = __ldg(sc.nodes + vec0), n1 = __ldg(sc.nodes + vec0 + 1);
+    uint4 n0, n1;
+#ifdef PTC_NO_LDG256
+    n0 = __ldg(sc.nodes + vec0), n1 = __ldg(sc.nodes + vec0 + 1);
+#else
+    ldg256(sc.nodes + vec0, n0, n1);
+#endif
     // near / far plane sets picked by ray octant through the load address, not by selects
+    // (measured: deriving the far index as near ^ c instead of the subtraction is slower)
     const uint4 NX = __ldg(sc.nodes + vec0 + T.vnx), FX = __ldg(sc.nodes + vec0 + 7u - T.vnx);
     const uint4 NY = __ldg(sc.nodes + vec0 + T.vny), FY = __ldg(sc.nodes + vec0 + 9u - T.vny);
     const uint4 NZ = __ldg(sc.nodes + vec0 + T.vnz), FZ = __ldg(sc.nodes + vec0 + 11u - T.vnz);
@@ -338,7 +380,7 @@ trav_step(const DScene& sc, Trav& T, uint2* stack, uint32_t& n_nodes, uint32_t& 
     const uint32_t tnew = (spread3(lh) * 7u) & n1.z;
     if (tnew) {
       if (T.tmask) {
-        stack[kStackSize - (++T.tsp)] = make_uint2(n1.y, n1.z | (lh << 24)); // defer, unstarted
+        stack.put(stack.top() - (++T.tsp), make_uint2(n1.y, n1.z | (lh << 24))); // defer, unstarted
       } else {
         T.tg = make_uint2(n1.y, n1.z);
         T.tmask = tnew;
@@ -355,7 +397,15 @@ lights_hit(const DScene& sc, const float3 o, const float3 d, float& best_t, uint
 {
   for (uint32_t l = 0; l < sc.n_lights; ++l) {
     float t;
-    if (sphere_test(sc.lights[l], o, d, t) && t < best_t && t >= 0.f) {
+    // 32-byte record in two 16-byte loads (the array comes from cudaMalloc; the C struct alone
+    // only promises 4-byte alignment, which makes the compiler emit eight scalar loads)
+    const float4* lp = reinterpret_cast<const float4*>(sc.lights + l);
+    const float4 l0 = __ldg(lp), l1 = __ldg(lp + 1);
+    ptc_light L;
+    L.color[0] = l0.x, L.color[1] = l0.y, L.color[2] = l0.z;
+    L.vec[0] = l0.w, L.vec[1] = l1.x, L.vec[2] = l1.y;
+    L.emission = l1.z, L.radius = l1.w;
+    if (sphere_test(L, o, d, t) && t < best_t && t >= 0.f) {
       best_t = t;
       best_id = sc.n_faces + l;
     }
@@ -364,13 +414,12 @@ lights_hit(const DScene& sc, const float3 o, const float3 d, float& best_t, uint
 
 // What the last radiance-loop iteration needs to know (see trav_init_any): id = light id,
 // miss, or SOME face id when a triangle is in front.
-template <bool STATS>
+template <bool STATS, typename Stack>
 __device__ __forceinline__ void
-last_hit(const DScene& sc, const float3 o, const float3 d, float& best_t, uint32_t& best_id,
+last_hit(const DScene& sc, Stack& stack, const float3 o, const float3 d, float& best_t, uint32_t& best_id,
          uint32_t& n_nodes, uint32_t& n_tris)
 {
   Trav T;
-  uint2 stack[kStackSize];
   trav_init_any(sc, T, o, d);
   while (!trav_step<STATS>(sc, T, stack, n_nodes, n_tris)) {
   }
@@ -380,13 +429,12 @@ last_hit(const DScene& sc, const float3 o, const float3 d, float& best_t, uint32
 // Closest hit with the reference's acceptance rules: triangles front-facing only,
 // 0 < t < best, lowest face index wins equal t (intersection.cuh:110,183-184); then the
 // sphere lights.
-template <bool STATS>
+template <bool STATS, typename Stack>
 __device__ __forceinline__ void
-closest_hit(const DScene& sc, const float3 o, const float3 d, float& best_t, uint32_t& best_id,
+closest_hit(const DScene& sc, Stack& stack, const float3 o, const float3 d, float& best_t, uint32_t& best_id,
             float& best_u, float& best_v, uint32_t& n_nodes, uint32_t& n_tris)
 {
   Trav T;
-  uint2 stack[kStackSize];
   trav_init(T, o, d);
   while (!trav_step<STATS>(sc, T, stack, n_nodes, n_tris)) {
   }

@@ -191,6 +191,36 @@ int ptc_scene_info_get(const ptc_context* ctx, int32_t scene_id, ptc_scene_info*
  * `faces` = 6 faces (+x,-x,+y,-y,+z,-z) of size*size RGBA floats, host memory. */
 int ptc_set_cubemap(ptc_context* ctx, const float* faces, uint32_t size, int32_t* cubemap_id);
 
+/* -- taking the reference's DEVICE data as GPUProcessor::init() leaves it --------------
+ * Layout mirrors of scene::Buffer<T> (scene_data.h:10-15, 16 bytes) and scene::Scenes
+ * (scene_data.h:83-87, 32 bytes): host structs holding device pointers.
+ *   Scenes.scenes -> device SceneData*[] -> device SceneData{meshes, materials, lights}
+ *   -> device Mesh[]{Buffer<Face>} -> device Face[]          (scene.cpp:202-283, 370-391)
+ * A caller that only has this tree (the reference discards the host Face vector after
+ * cudaMemcpy, scene.cpp:230-281) passes it here; the records are read back once, then the
+ * call does what ptc_upload_scene does.  Synchronous; caller keeps owning the tree. */
+typedef struct ptc_ref_buffer
+{
+  uint32_t size;
+  uint32_t _pad;
+  const void* data; /* DEVICE pointer */
+} ptc_ref_buffer;
+
+typedef struct ptc_ref_scenes
+{
+  ptc_ref_buffer textures;   /* device scene::Texture[] whose .data are device floats */
+  const void* const* scenes; /* device array of device scene::SceneData*              */
+  uint64_t _pad;
+} ptc_ref_scenes;
+
+int ptc_upload_scene_from_device(ptc_context* ctx, const ptc_ref_scenes* scenes, uint32_t scene_index,
+                                 int32_t* scene_id);
+
+/* Same for scene::Cubemap.cubemap (scene_data.h:21-25): `cuda_array` is the reference's
+ * RGBA32F cubemap cudaArray (gpu_processor.cpp:134-152); its six faces are copied (once,
+ * through the host) into an array owned by the context. */
+int ptc_set_cubemap_from_array(ptc_context* ctx, const void* cuda_array, int32_t* cubemap_id);
+
 /* The render call: one sample per pixel accumulated into `accum`, tonemapped
  * RGBA8 written to `out_rgba`.  Asynchronous on args->stream, no hidden syncs. */
 int ptc_render(ptc_context* ctx, const ptc_render_args* args);

@@ -144,14 +144,20 @@ def build_gpu():
     drv = os.path.join(HERE, "ref_driver", "ref_gpu_driver.cu")
     if not os.path.exists(drv):
         return None
-    if newer(out, drv, __file__):
+    pkg = os.path.join(os.path.dirname(HERE), "cuda-pathtracer_b200")
+    hdr = os.path.join(os.path.dirname(HERE), "include")
+    if newer(out, drv, __file__, os.path.join(hdr, "ptcore.h"), os.path.join(hdr, "ptcore_raytrace.hpp")):
         return out
+    if not os.path.exists(os.path.join(pkg, "libptcore.so")):
+        raise SystemExit("build_ref: build cuda-pathtracer_b200/libptcore.so first (the compat entry links it)")
     gen_gpu_source()
     # the reference's own flags: -O2, no -arch, no fast-math (CMakeLists.txt:23-25);
     # the arch is the only addition.
     run([os.path.join(CUDA, "bin", "nvcc"), "-std=c++14", "-O2", "-w", "-lineinfo",
          "-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler", "-fPIC", "-shared",
-         "-I", GEN, *INC, drv, "-o", out])
+         "-I", GEN, *INC, drv, "-o", out,
+         # ref_gpu_raytrace_compat calls the product through include/ptcore_raytrace.hpp
+         "-L", pkg, "-lptcore", "-Xlinker", "-rpath", "-Xlinker", "$ORIGIN/../../cuda-pathtracer_b200"])
     return out
 
 

@@ -14,6 +14,8 @@
 #include <vector>
 
 #include "ptcore.h"
+#define PTCORE_RAYTRACE_NO_SETUP // raytrace_gpu.cu above has the reference's own
+#include "ptcore_raytrace.hpp" // the product's source-compatible raytrace(uchar4*, ...) overload
 
 namespace {
 
@@ -241,9 +243,32 @@ ref_gpu_raytrace(void* h, const ptc_camera* camera, unsigned width, unsigned hei
   cubemaps[0].cubemap = g->cube_array;
   scene::Camera cam;
   memcpy(&cam, camera, sizeof(cam));
-  raytrace(nullptr, g->scenes, 0, cubemaps, 0, &cam, width, height, (cudaStream_t)stream,
+  raytrace((cudaArray_const_t) nullptr, g->scenes, 0, cubemaps, 0, &cam, width, height, (cudaStream_t)stream,
            (float3*)d_accum, moved != 0, post_id);
   return (int)cudaGetLastError();
+}
+
+// The PRODUCT behind the reference's call: the same Scenes tree, cubemap vector and camera
+// GPUProcessor::render passes (gpu_processor.cpp:375-377) go to the raytrace() overload of
+// include/ptcore_raytrace.hpp, which derives its own state from this device tree.  Lets the
+// parity tests check the drop-in boundary itself, not only the C ABI underneath.
+int
+ref_gpu_raytrace_compat(void* h, const ptc_camera* camera, unsigned width, unsigned height, int moved,
+                        unsigned post_id, float* d_accum, unsigned* d_out, void* stream)
+{
+  RefGpu* g = (RefGpu*)h;
+  std::vector<scene::Cubemap> cubemaps(1);
+  cubemaps[0].cubemap = g->cube_array;
+  scene::Camera cam;
+  memcpy(&cam, camera, sizeof(cam));
+  return (int)raytrace((uchar4*)d_out, g->scenes, 0, cubemaps, 0, &cam, width, height,
+                       (cudaStream_t)stream, (float3*)d_accum, moved != 0, post_id);
+}
+
+void
+ref_gpu_compat_reset()
+{
+  ptc_compat::invalidate();
 }
 
 // Same launch as raytrace.cu:315-322 but for an explicit sample number, so tests

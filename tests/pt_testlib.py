@@ -183,6 +183,19 @@ class RefGpu:
         if rc:
             raise RuntimeError(f"ref_gpu_raytrace failed: {rc}")
 
+    def raytrace_compat(self, w, h, d_accum, d_out, moved=False, post_id=0, stream=0):
+        """The PRODUCT through include/ptcore_raytrace.hpp's raytrace(uchar4*, Scenes, ...)
+        overload, fed with this handle's reference-layout device tree and cubemap array."""
+        cam = self.sc.camera_struct()
+        rc = self.lib.ref_gpu_raytrace_compat(self.h, C.byref(cam), C.c_uint(w), C.c_uint(h),
+                                              C.c_int(int(moved)), C.c_uint(post_id),
+                                              C.c_void_p(d_accum), C.c_void_p(d_out), C.c_void_p(stream))
+        if rc:
+            raise RuntimeError(f"raytrace() compat overload failed: cudaError {rc}")
+
+    def compat_reset(self):
+        self.lib.ref_gpu_compat_reset()
+
     def primary(self, w, h, frame):
         cam = self.sc.camera_struct()
         o = np.zeros((h * w, 3), np.float32)

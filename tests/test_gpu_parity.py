@@ -246,6 +246,35 @@ def test_preview_and_post_process_bit_identical_to_reference_kernel(core, g0_fac
         assert (out_m.cpu().numpy() == out_g.cpu().numpy()).all(), post
 
 
+def test_source_compatible_raytrace_overload(g0_factory):
+    """The drop-in boundary itself: the reference's caller hands its OWN device
+    tree (scene::Scenes, vector<scene::Cubemap>, Camera) to the raytrace(uchar4*, ...) overload
+    of include/ptcore_raytrace.hpp; the overload derives the BVH from that tree and follows the
+    reference's frame counter.  Every call is compared, bit for bit, with the reference's own
+    raytrace() given the same argument sequence."""
+    import torch
+    P = pkg()
+    from pt_testlib import load_scene
+    import copy
+    sc = copy.copy(load_scene("indoor_tex"))
+    sc.cubemap = P.synth.gradient_cubemap(32)
+    sc.cubemap_size = 32
+    g0 = g0_factory("indoor_tex_compat", sc)
+    w, h = 320, 180
+    acc_m, out_m, _ = dev_buffers(w, h)
+    acc_g, out_g, _ = dev_buffers(w, h)
+    try:
+        # `moved` first: resets both frame counters whatever ran before in this process
+        for i, (moved, post) in enumerate([(True, 0), (False, 0), (False, 0), (True, 2), (False, 2), (False, 3)]):
+            g0.raytrace(w, h, 3, acc_g.data_ptr(), out_g.data_ptr(), moved=moved, post_id=post)
+            g0.raytrace_compat(w, h, acc_m.data_ptr(), out_m.data_ptr(), moved=moved, post_id=post)
+            torch.cuda.synchronize()
+            assert (bits(acc_m.cpu().numpy()) == bits(acc_g.cpu().numpy())).all(), f"accumulator, call {i}"
+            assert (out_m.cpu().numpy() == out_g.cpu().numpy()).all(), f"RGBA8, call {i}"
+    finally:
+        g0.compat_reset()
+
+
 @pytest.mark.parametrize("name,bounces", [("color_sample_plain", 3), ("island_plain", 4), ("sss_crate_plain", 3),
                                           ("synth24", 6)])
 def test_radiance_vs_oracle_other_scenes(core, oracle, name, bounces):

@@ -294,3 +294,37 @@ def test_band_gather_gloo(world, tmp_path):
     for r, (p, o) in enumerate(zip(procs, outs)):
         assert p.returncode == 0, f"rank {r}:\n{o}"
         assert f"rank {r} ok" in o
+
+
+def test_raytrace_overload_header_compiles_against_reference_shaped_types(tmp_path):
+    """include/ptcore_raytrace.hpp is the source-compatible raytrace() a maintainer includes
+    instead of shaders/raytrace.h.  Compile a caller shaped like GPUProcessor::render
+    (gpu_processor.cpp:375-377) against stand-ins with the reference's layouts
+    (scene_data.h:10-25, 83-87, 123-133) -- syntax and layout asserts only, nothing runs."""
+    cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
+    if not os.path.exists(os.path.join(cuda_inc, "cuda_runtime.h")):
+        pytest.skip("CUDA headers not installed")
+    src = tmp_path / "caller.cpp"
+    src.write_text(r"""
+#include <cuda_runtime.h>
+#include <vector>
+namespace scene {
+template <typename T> struct alignas(16) Buffer { unsigned int size; T* data = nullptr; };
+struct alignas(8) Cubemap { cudaArray* cubemap; cudaChannelFormatDesc cubemap_desc; };
+struct alignas(16) Texture { int w, h, nb_chan; float* data; };
+struct SceneData;
+struct alignas(16) Scenes { Buffer<Texture> textures; SceneData** scenes; };
+struct alignas(8) Camera { float3 position, dir, u, v; float fov_x, speed, aperture, focus_dist; };
+}
+#include "ptcore_raytrace.hpp"
+cudaError_t render_like_gpu_processor(uchar4* frame, const scene::Scenes& scenes, unsigned id,
+                                      const std::vector<scene::Cubemap>& cubemaps, const scene::Camera* cam,
+                                      float3* temporal, cudaStream_t stream)
+{
+  setupFunctionTables();
+  return raytrace(frame, scenes, id, cubemaps, 0, cam, 1920u, 1080u, stream, temporal, false, 0u);
+}
+""")
+    r = subprocess.run(["g++", "-std=c++14", "-fsyntax-only", "-I", cuda_inc, "-I", os.path.join(REPO, "include"),
+                        str(src)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
