@@ -11,11 +11,15 @@
 #include "bvh.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cfloat>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <numeric>
+#include <thread>
 
 namespace ptc {
 namespace {
@@ -50,7 +54,7 @@ struct BinNode
 {
   Box box;
   int left = -1, right = -1; // children (internal) ...
-  uint32_t first = 0, count = 0; // ... or a range of `order` (leaf)
+  uint32_t first = 0, count = 0; // ... or a range of the partitioned primitive array (leaf)
   bool leaf() const { return left < 0; }
 };
 
@@ -65,34 +69,132 @@ trav_cost()
 }
 
 
+// Worker threads for the host build: hardware threads, capped; PTC_BUILD_THREADS overrides.
+static unsigned
+build_threads()
+{
+  if (const char* e = getenv("PTC_BUILD_THREADS"))
+    return (unsigned)std::max(1, atoi(e));
+  const unsigned hw = std::thread::hardware_concurrency();
+  return std::min(32u, std::max(1u, hw));
+}
+
+// f(lo, hi) over [0, n) in contiguous chunks, one per worker thread (serial when small).
+template <typename F>
+static void
+parallel_for(uint32_t n, F f)
+{
+  const unsigned t = n >= 4096 ? build_threads() : 1u;
+  if (t <= 1) {
+    f(0u, n);
+    return;
+  }
+  std::vector<std::thread> th;
+  const uint32_t per = (n + t - 1) / t;
+  for (unsigned k = 1; k < t; ++k) {
+    const uint32_t lo = std::min(n, k * per), hi = std::min(n, (k + 1) * per);
+    if (lo < hi)
+      th.emplace_back([=, &f] { f(lo, hi); });
+  }
+  f(0u, std::min(n, per));
+  for (std::thread& x : th)
+    x.join();
+}
+
+// Binned-SAH binary tree, built top-down.  Parallel in two ways (scene.cpp:202-283 builds
+// nothing, so at 10 M triangles this step IS the load time): the bin/partition passes of a
+// large node are split over the worker threads, and the two children of a node with more than
+// kSpawn primitives are built concurrently.  Node slots come from one atomic counter, so a
+// child always has a larger index than its parent (the collapse DP walks indices downwards);
+// the tree itself does not depend on the thread count or on timing -- every reduction is a
+// min/max or an integer sum.
 struct Builder
 {
-  const std::vector<Box>& boxes;
-  std::vector<float> centroid; // 3 per primitive
-  std::vector<uint32_t> order;
-  std::vector<BinNode> nodes;
-  uint32_t max_depth = 0;
+  static constexpr uint32_t kSpawn = 1u << 16;    // children of bigger nodes run as tasks
+  static constexpr uint32_t kParallel = 1u << 19; // bigger nodes bin their range in parallel
 
-  explicit Builder(const std::vector<Box>& b) : boxes(b)
+  // Primitive records are PARTITIONED IN PLACE (no index indirection): every pass over a node's
+  // range is a sequential read, which is what makes the passes scale across threads.
+  struct Prim
   {
-    centroid.resize(b.size() * 3);
-    order.resize(b.size());
-    std::iota(order.begin(), order.end(), 0u);
-    for (size_t i = 0; i < b.size(); ++i)
-      for (int a = 0; a < 3; ++a)
-        centroid[3 * i + a] = 0.5f * (b[i].lo[a] + b[i].hi[a]);
-    nodes.reserve(b.size() * 2 + 1);
+    Box box;
+    float c[3]; // centroid
+    uint32_t id;
+  };
+  std::vector<Prim> prims;
+  std::vector<BinNode> nodes;
+  std::atomic<uint32_t> n_nodes{ 0 };
+  std::atomic<uint32_t> max_depth{ 0 };
+  std::atomic<int> idle_threads;
+  const unsigned n_threads;
+
+  explicit Builder(const std::vector<Box>& b) : idle_threads(0), n_threads(build_threads())
+  {
+    idle_threads = (int)n_threads - 1;
+    prims.resize(b.size());
+    parallel_chunks(0, (uint32_t)b.size(), true, [&](uint32_t lo, uint32_t hi, unsigned) {
+      for (uint32_t i = lo; i < hi; ++i) {
+        prims[i].box = b[i];
+        prims[i].id = i;
+        for (int a = 0; a < 3; ++a)
+          prims[i].c[a] = 0.5f * (b[i].lo[a] + b[i].hi[a]);
+      }
+    });
+    nodes.resize(b.size() * 2 + 1);
   }
 
-  int build(uint32_t first, uint32_t count, uint32_t depth)
+  // f(lo, hi, chunk) over [first, last) in up to n_threads contiguous chunks
+  template <typename F>
+  void parallel_chunks(uint32_t first, uint32_t last, bool parallel, F f)
   {
-    max_depth = std::max(max_depth, depth);
-    int idx = (int)nodes.size();
-    nodes.emplace_back();
+    const uint32_t n = last - first;
+    const unsigned t = parallel && n >= kParallel ? n_threads : 1u;
+    if (t <= 1) {
+      f(first, last, 0u);
+      return;
+    }
+    std::vector<std::thread> th;
+    const uint32_t per = (n + t - 1) / t;
+    for (unsigned k = 1; k < t; ++k) {
+      const uint32_t lo = first + std::min(n, k * per), hi = first + std::min(n, (k + 1) * per);
+      if (lo < hi)
+        th.emplace_back([=, &f] { f(lo, hi, k); });
+    }
+    f(first, first + std::min(n, per), 0u);
+    for (std::thread& x : th)
+      x.join();
+  }
+
+  struct Bins
+  {
+    Box box[3][kBins];
+    uint32_t cnt[3][kBins];
+    Bins() { std::memset(cnt, 0, sizeof(cnt)); }
+  };
+
+  int build(uint32_t first, uint32_t count, uint32_t depth, bool top = true)
+  {
+    uint32_t seen = max_depth.load(std::memory_order_relaxed);
+    while (depth > seen && !max_depth.compare_exchange_weak(seen, depth, std::memory_order_relaxed)) {
+    }
+    const int idx = (int)n_nodes.fetch_add(1u);
+    // `top`: no other task is running beside this node, its passes may use all the threads
+    const bool wide = top && count >= kParallel && n_threads > 1;
+
     Box box, cbox;
-    for (uint32_t i = first; i < first + count; ++i) {
-      box.grow(boxes[order[i]]);
-      cbox.grow(&centroid[3 * order[i]]);
+    {
+      std::vector<Box> pb(wide ? n_threads : 1u), pc(wide ? n_threads : 1u);
+      parallel_chunks(first, first + count, wide, [&](uint32_t lo, uint32_t hi, unsigned k) {
+        Box bb, cc;
+        for (uint32_t i = lo; i < hi; ++i) {
+          bb.grow(prims[i].box);
+          cc.grow(prims[i].c);
+        }
+        pb[k] = bb, pc[k] = cc;
+      });
+      for (size_t k = 0; k < pb.size(); ++k)
+        if (pb[k].valid())
+          box.grow(pb[k]), cbox.grow(pc[k]);
     }
     nodes[idx].box = box;
     nodes[idx].first = first;
@@ -100,39 +202,57 @@ struct Builder
     if (count <= 1)
       return idx;
 
-    // binned SAH over the three axes
+    // binned SAH over the three axes (one pass fills the bins of all three)
+    float ext[3], scale[3];
+    for (int a = 0; a < 3; ++a) {
+      ext[a] = cbox.hi[a] - cbox.lo[a];
+      scale[a] = ext[a] > 0.f ? kBins / ext[a] : 0.f;
+    }
+    std::vector<Bins> part(wide ? n_threads : 1u);
+    parallel_chunks(first, first + count, wide, [&](uint32_t lo, uint32_t hi, unsigned k) {
+      Bins& B = part[k];
+      for (uint32_t i = lo; i < hi; ++i) {
+        const Prim& p = prims[i];
+        for (int a = 0; a < 3; ++a) {
+          if (!(ext[a] > 0.f))
+            continue;
+          const int bn = std::min(kBins - 1, (int)((p.c[a] - cbox.lo[a]) * scale[a]));
+          B.box[a][bn].grow(p.box);
+          B.cnt[a][bn]++;
+        }
+      }
+    });
+    Bins& B = part[0];
+    for (size_t k = 1; k < part.size(); ++k)
+      for (int a = 0; a < 3; ++a)
+        for (int bn = 0; bn < kBins; ++bn)
+          if (part[k].cnt[a][bn]) {
+            B.box[a][bn].grow(part[k].box[a][bn]);
+            B.cnt[a][bn] += part[k].cnt[a][bn];
+          }
+
     float best_cost = FLT_MAX;
     int best_axis = -1, best_split = -1;
     for (int a = 0; a < 3; ++a) {
-      float ext = cbox.hi[a] - cbox.lo[a];
-      if (!(ext > 0.f))
+      if (!(ext[a] > 0.f))
         continue;
-      Box bin_box[kBins];
-      uint32_t bin_cnt[kBins] = { 0 };
-      float scale = kBins / ext;
-      for (uint32_t i = first; i < first + count; ++i) {
-        uint32_t p = order[i];
-        int b = std::min(kBins - 1, (int)((centroid[3 * p + a] - cbox.lo[a]) * scale));
-        bin_box[b].grow(boxes[p]);
-        bin_cnt[b]++;
-      }
       float right_area[kBins];
       uint32_t right_cnt[kBins];
       Box acc;
       uint32_t cnt = 0;
       for (int b = kBins - 1; b > 0; --b) {
-        if (bin_cnt[b])
-          acc.grow(bin_box[b]);
-        cnt += bin_cnt[b];
+        if (B.cnt[a][b])
+          acc.grow(B.box[a][b]);
+        cnt += B.cnt[a][b];
         right_area[b] = acc.valid() ? acc.half_area() : 0.f;
         right_cnt[b] = cnt;
       }
       acc = Box();
       cnt = 0;
       for (int b = 0; b < kBins - 1; ++b) {
-        if (bin_cnt[b])
-          acc.grow(bin_box[b]);
-        cnt += bin_cnt[b];
+        if (B.cnt[a][b])
+          acc.grow(B.box[a][b]);
+        cnt += B.cnt[a][b];
         if (!cnt || !right_cnt[b + 1])
           continue;
         float cost = acc.half_area() * cnt + right_area[b + 1] * right_cnt[b + 1];
@@ -154,19 +274,38 @@ struct Builder
       float leaf_cost = box.half_area() * count;
       if (count <= kMaxLeaf && leaf_cost <= best_cost + box.half_area() * trav_cost())
         return idx; // cheaper (or as cheap) to keep as a leaf
-      float ext = cbox.hi[best_axis] - cbox.lo[best_axis];
-      float scale = kBins / ext;
-      float lo = cbox.lo[best_axis];
-      auto it = std::partition(order.begin() + first, order.begin() + first + count, [&](uint32_t p) {
-        int b = std::min(kBins - 1, (int)((centroid[3 * p + best_axis] - lo) * scale));
+      const float sc = scale[best_axis];
+      const float lo = cbox.lo[best_axis];
+      auto it = std::partition(prims.begin() + first, prims.begin() + first + count, [&](const Prim& p) {
+        int b = std::min(kBins - 1, (int)((p.c[best_axis] - lo) * sc));
         return b <= best_split;
       });
-      mid = (uint32_t)(it - order.begin());
+      mid = (uint32_t)(it - prims.begin());
       if (mid == first || mid == first + count)
         mid = first + count / 2;
     }
-    int l = build(first, mid - first, depth + 1);
-    int r = build(mid, first + count - mid, depth + 1);
+
+    int l, r;
+    const uint32_t nl = mid - first, nr = first + count - mid;
+    // both children big: build the left one on another thread if one is free.  While a node
+    // is still "top" only one of its children can stay so (the larger), the other runs beside it.
+    bool spawned = false;
+    if (std::min(nl, nr) >= kSpawn && n_threads > 1) {
+      int idle = idle_threads.load();
+      while (idle > 0 && !idle_threads.compare_exchange_weak(idle, idle - 1)) {
+      }
+      spawned = idle > 0;
+    }
+    if (spawned) {
+      std::thread t([&] { l = build(first, nl, depth + 1, false); });
+      r = build(mid, nr, depth + 1, false);
+      t.join();
+      idle_threads.fetch_add(1);
+    } else {
+      const bool keep_top = top && std::min(nl, nr) < kSpawn;
+      l = build(first, nl, depth + 1, keep_top && nl >= nr);
+      r = build(mid, nr, depth + 1, keep_top && nr > nl);
+    }
     nodes[idx].left = l;
     nodes[idx].right = r;
     return idx;
@@ -326,7 +465,7 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
       b.hi[a] += pad;
     }
 
-  auto emit_tri = [&](uint32_t f) {
+  auto emit_tri = [&](uint32_t at, uint32_t f) {
     const ptc_face& face = desc->faces[f];
     TriRecord t;
     std::memset(&t, 0, sizeof(t));
@@ -336,8 +475,8 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
       t.e2[a] = face.vertices[2][a] - face.vertices[0][a]; // intersection.cuh:107
     }
     t.face_id = f;
-    out.tris.push_back(t);
-    out.face_ids.push_back(f);
+    out.tris[at] = t;
+    out.face_ids[at] = f;
   };
 
   if (n_faces == 0) {
@@ -349,9 +488,17 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
     return;
   }
 
+  const bool timing = getenv("PTC_BUILD_TIMING") != nullptr;
+  auto now = [] { return std::chrono::steady_clock::now(); };
+  auto secs = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+    return std::chrono::duration<double>(b - a).count();
+  };
+  const auto t0 = now();
   Builder b(boxes);
   int root = b.build(0, n_faces, 0);
-  out.stats.max_depth = b.max_depth;
+  b.nodes.resize(b.n_nodes.load());
+  out.stats.max_depth = b.max_depth.load();
+  const auto t1 = now();
 
   // SAH cost of the binary tree (diagnostic)
   {
@@ -363,116 +510,174 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
   }
 
   const CollapseDp dp(b.nodes);
+  const auto t2 = now();
 
-  struct Pending
+  // Emission, level by level (== the order a serial breadth-first queue would give, so node
+  // and triangle indices do not depend on the thread count): per level, (1) every wide node
+  // picks its children and their slots in parallel, (2) one scan hands out child_base /
+  // tri_base, (3) the nodes and their triangles are written in parallel.
+  struct Item
   {
     int bin;      // binary node whose subtree this wide node covers
     uint32_t out; // index in out.nodes
-    uint32_t depth;
   };
-  std::vector<Pending> queue;
-  out.nodes.emplace_back();
-  queue.push_back({ root, 0, 1 });
-
-  for (size_t qi = 0; qi < queue.size(); ++qi) {
-    const Pending cur = queue[qi];
-    const BinNode& top = b.nodes[cur.bin];
-    out.stats.wide_depth = std::max(out.stats.wide_depth, cur.depth);
-
-    // 1. gather up to 8 children: the forest of binary subtrees the collapse DP chose
-    std::vector<int> kids;
-    if (dp.is_leaf(cur.bin))
-      kids.push_back(cur.bin);
-    else
-      dp.gather_children(cur.bin, kids);
-
-    // 2. slot assignment: slot s is visited first by rays whose direction is
-    //    negative exactly on the axes set in s, so it should hold the child that
-    //    comes first along sign_s.  Greedy on cost = centroid . sign_s.
-    Box nb = top.box;
-    float cen[3];
-    for (int a = 0; a < 3; ++a)
-      cen[a] = 0.5f * (nb.lo[a] + nb.hi[a]);
-    int slot_of[8];
+  struct Plan
+  {
+    int kids[8];
     int kid_in_slot[8];
-    std::fill(slot_of, slot_of + 8, -1);
-    std::fill(kid_in_slot, kid_in_slot + 8, -1);
-    float cost[8][8];
-    for (size_t k = 0; k < kids.size(); ++k) {
-      const Box& cb = b.nodes[kids[k]].box;
-      for (int s = 0; s < 8; ++s) {
-        float c = 0.f;
-        for (int a = 0; a < 3; ++a) {
-          float d = 0.5f * (cb.lo[a] + cb.hi[a]) - cen[a];
-          c += ((s >> a) & 1) ? -d : d;
-        }
-        cost[k][s] = c;
-      }
-    }
-    for (size_t round = 0; round < kids.size(); ++round) {
-      float bc = FLT_MAX;
-      int bk = -1, bs = -1;
-      for (size_t k = 0; k < kids.size(); ++k) {
-        if (slot_of[k] >= 0)
-          continue;
-        for (int s = 0; s < 8; ++s)
-          if (kid_in_slot[s] < 0 && cost[k][s] < bc) {
-            bc = cost[k][s];
-            bk = (int)k;
-            bs = s;
+    int n_kids;
+    uint32_t n_internal, n_tris;
+    uint32_t child_base, tri_base;
+  };
+  std::vector<Item> level{ Item{ root, 0u } }, next;
+  std::vector<Plan> plan;
+  out.nodes.resize(1);
+  uint32_t depth = 0;
+  while (!level.empty()) {
+    ++depth;
+    plan.resize(level.size());
+    // 1. children (the forest of binary subtrees the collapse DP chose) and slot assignment:
+    //    slot s is visited first by rays whose direction is negative exactly on the axes set
+    //    in s, so it should hold the child that comes first along sign_s.  Greedy on
+    //    cost = centroid . sign_s.
+    parallel_for((uint32_t)level.size(), [&](uint32_t lo, uint32_t hi) {
+      std::vector<int> kids;
+      for (uint32_t q = lo; q < hi; ++q) {
+        const int bin = level[q].bin;
+        Plan& P = plan[q];
+        kids.clear();
+        if (dp.is_leaf(bin))
+          kids.push_back(bin);
+        else
+          dp.gather_children(bin, kids);
+        P.n_kids = (int)kids.size();
+        const Box& nb = b.nodes[bin].box;
+        float cen[3];
+        for (int a = 0; a < 3; ++a)
+          cen[a] = 0.5f * (nb.lo[a] + nb.hi[a]);
+        int slot_of[8];
+        std::fill(slot_of, slot_of + 8, -1);
+        std::fill(P.kid_in_slot, P.kid_in_slot + 8, -1);
+        float cost[8][8];
+        for (int k = 0; k < P.n_kids; ++k) {
+          P.kids[k] = kids[k];
+          const Box& cb = b.nodes[kids[k]].box;
+          for (int sl = 0; sl < 8; ++sl) {
+            float c = 0.f;
+            for (int a = 0; a < 3; ++a) {
+              float d = 0.5f * (cb.lo[a] + cb.hi[a]) - cen[a];
+              c += ((sl >> a) & 1) ? -d : d;
+            }
+            cost[k][sl] = c;
           }
-      }
-      slot_of[bk] = bs;
-      kid_in_slot[bs] = bk;
-    }
-
-    // 3. emit
-    Node8 n;
-    std::memset(&n, 0, sizeof(n));
-    for (int a = 0; a < 3; ++a) {
-      n.origin[a] = nb.lo[a];
-      n.e[a] = quant_exponent(nb.hi[a] - nb.lo[a]);
-    }
-    n.child_base = (uint32_t)out.nodes.size();
-    n.tri_base = (uint32_t)out.tris.size();
-    for (int s = 0; s < 8; ++s) {
-      int k = kid_in_slot[s];
-      if (k < 0) { // empty slot: an inverted box (lo > hi) can never be hit
-        for (int a = 0; a < 3; ++a) {
-          n.lo[a][s] = half_of_byte(255);
-          n.hi[a][s] = half_of_byte(0);
         }
-        continue;
+        for (int round = 0; round < P.n_kids; ++round) {
+          float bc = FLT_MAX;
+          int bk = -1, bs = -1;
+          for (int k = 0; k < P.n_kids; ++k) {
+            if (slot_of[k] >= 0)
+              continue;
+            for (int sl = 0; sl < 8; ++sl)
+              if (P.kid_in_slot[sl] < 0 && cost[k][sl] < bc) {
+                bc = cost[k][sl];
+                bk = k;
+                bs = sl;
+              }
+          }
+          slot_of[bk] = bs;
+          P.kid_in_slot[bs] = bk;
+        }
+        P.n_internal = P.n_tris = 0;
+        for (int sl = 0; sl < 8; ++sl) {
+          const int k = P.kid_in_slot[sl];
+          if (k < 0)
+            continue;
+          if (dp.is_leaf(P.kids[k]))
+            P.n_tris += b.nodes[P.kids[k]].count;
+          else
+            P.n_internal++;
+        }
       }
-      n.occupied |= 1u << s;
-      const BinNode& c = b.nodes[kids[k]];
-      for (int a = 0; a < 3; ++a) {
-        float sc = exp_scale(n.e[a]);
-        float ql = std::floor((c.box.lo[a] - n.origin[a]) / sc);
-        float qh = std::ceil((c.box.hi[a] - n.origin[a]) / sc);
-        // guard against the division rounding the wrong way
-        while (ql > 0.f && n.origin[a] + ql * sc > c.box.lo[a])
-          ql -= 1.f;
-        while (qh < 255.f && n.origin[a] + qh * sc < c.box.hi[a])
-          qh += 1.f;
-        n.lo[a][s] = half_of_byte((int)std::min(255.f, std::max(0.f, ql)));
-        n.hi[a][s] = half_of_byte((int)std::min(255.f, std::max(0.f, qh)));
-      }
-      if (dp.is_leaf(kids[k])) {
-        n.valid24 |= ((1u << c.count) - 1u) << (3 * s); // 001, 011, 111
-        std::vector<uint32_t> ids(b.order.begin() + c.first, b.order.begin() + c.first + c.count);
-        std::sort(ids.begin(), ids.end());
-        for (uint32_t f : ids)
-          emit_tri(f);
-        out.stats.n_leaves++;
-      } else {
-        n.imask |= (uint8_t)(1u << s);
-        queue.push_back({ kids[k], (uint32_t)out.nodes.size(), cur.depth + 1 });
-        out.nodes.emplace_back();
-      }
+    });
+    // 2. index hand-out in queue order
+    uint32_t node_top = (uint32_t)out.nodes.size(), tri_top = (uint32_t)out.tris.size();
+    for (Plan& P : plan) {
+      P.child_base = node_top;
+      P.tri_base = tri_top;
+      node_top += P.n_internal;
+      tri_top += P.n_tris;
     }
-    out.nodes[cur.out] = n;
+    const uint32_t next_first = (uint32_t)out.nodes.size();
+    out.nodes.resize(node_top);
+    out.tris.resize(tri_top);
+    out.face_ids.resize(tri_top);
+    next.resize(node_top - next_first);
+    // 3. emit
+    parallel_for((uint32_t)level.size(), [&](uint32_t lo, uint32_t hi) {
+      for (uint32_t q = lo; q < hi; ++q) {
+        const Plan& P = plan[q];
+        const Box& nb = b.nodes[level[q].bin].box;
+        Node8 n;
+        std::memset(&n, 0, sizeof(n));
+        for (int a = 0; a < 3; ++a) {
+          n.origin[a] = nb.lo[a];
+          n.e[a] = quant_exponent(nb.hi[a] - nb.lo[a]);
+        }
+        n.child_base = P.child_base;
+        n.tri_base = P.tri_base;
+        uint32_t child = P.child_base, tri = P.tri_base;
+        for (int sl = 0; sl < 8; ++sl) {
+          const int k = P.kid_in_slot[sl];
+          if (k < 0) { // empty slot: an inverted box (lo > hi) can never be hit
+            for (int a = 0; a < 3; ++a) {
+              n.lo[a][sl] = half_of_byte(255);
+              n.hi[a][sl] = half_of_byte(0);
+            }
+            continue;
+          }
+          n.occupied |= 1u << sl;
+          const BinNode& c = b.nodes[P.kids[k]];
+          for (int a = 0; a < 3; ++a) {
+            float sc = exp_scale(n.e[a]);
+            float ql = std::floor((c.box.lo[a] - n.origin[a]) / sc);
+            float qh = std::ceil((c.box.hi[a] - n.origin[a]) / sc);
+            // guard against the division rounding the wrong way
+            while (ql > 0.f && n.origin[a] + ql * sc > c.box.lo[a])
+              ql -= 1.f;
+            while (qh < 255.f && n.origin[a] + qh * sc < c.box.hi[a])
+              qh += 1.f;
+            n.lo[a][sl] = half_of_byte((int)std::min(255.f, std::max(0.f, ql)));
+            n.hi[a][sl] = half_of_byte((int)std::min(255.f, std::max(0.f, qh)));
+          }
+          if (dp.is_leaf(P.kids[k])) {
+            n.valid24 |= ((1u << c.count) - 1u) << (3 * sl); // 001, 011, 111
+            uint32_t ids[kMaxLeaf];
+            for (uint32_t t = 0; t < c.count; ++t)
+              ids[t] = b.prims[c.first + t].id;
+            for (uint32_t t = 1; t < c.count; ++t) // ascending face id (<= 3 entries)
+              for (uint32_t u = t; u > 0 && ids[u] < ids[u - 1]; --u)
+                std::swap(ids[u], ids[u - 1]);
+            for (uint32_t t = 0; t < c.count; ++t)
+              emit_tri(tri++, ids[t]);
+          } else {
+            n.imask |= (uint8_t)(1u << sl);
+            next[child - next_first] = Item{ P.kids[k], child };
+            ++child;
+          }
+        }
+        out.nodes[level[q].out] = n;
+      }
+    });
+    for (const Plan& P : plan)
+      for (int sl = 0; sl < 8; ++sl)
+        if (P.kid_in_slot[sl] >= 0 && dp.is_leaf(P.kids[P.kid_in_slot[sl]]))
+          out.stats.n_leaves++;
+    level.swap(next);
   }
+  out.stats.wide_depth = depth;
+  if (timing)
+    fprintf(stderr, "build_bvh: %u faces: binary SAH %.2f s, collapse DP %.2f s, emit %.2f s\n", n_faces,
+            secs(t0, t1), secs(t1, t2), secs(t2, now()));
 }
 
 void
