@@ -73,7 +73,9 @@ EXPORTS = ["ptc_abi_version", "ptc_create", "ptc_destroy", "ptc_last_error", "pt
            "ptc_trace_primary", "ptc_intersect_rays", "ptc_debug_rng", "ptc_host_bvh_build",
            "ptc_host_bvh_free", "ptc_band_rows", "ptc_launch_count", "ptc_set_wavefront",
            "ptc_profile_frame", "ptc_render_host_async", "ptc_wait",
-           "ptc_upload_scene_from_device", "ptc_set_cubemap_from_array"]
+           "ptc_upload_scene_from_device", "ptc_set_cubemap_from_array",
+           "ptc_set_cubemap_from_cross", "ptc_cubemap_faces_from_cross",
+           "ptc_write_ppm", "ptc_accum_save", "ptc_accum_load"]
 
 _lib = None
 
@@ -100,7 +102,9 @@ def load_library() -> C.CDLL:
                      "ptc_render_host", "ptc_reset_accumulation", "ptc_counters_get",
                      "ptc_counters_reset", "ptc_trace_primary", "ptc_intersect_rays", "ptc_debug_rng",
                      "ptc_launch_count", "ptc_set_wavefront", "ptc_profile_frame",
-                     "ptc_render_host_async", "ptc_wait"]:
+                     "ptc_render_host_async", "ptc_wait", "ptc_set_cubemap_from_cross",
+                     "ptc_cubemap_faces_from_cross", "ptc_upload_scene_from_device",
+                     "ptc_set_cubemap_from_array", "ptc_write_ppm", "ptc_accum_save", "ptc_accum_load"]:
             getattr(lib, name).restype = C.c_int
         lib.ptc_band_rows.restype = C.c_uint32
         _lib = lib
@@ -115,6 +119,56 @@ def _ptr(a):
     if hasattr(a, "data_ptr"):  # torch tensor
         return C.c_void_p(a.data_ptr())
     return C.c_void_p(int(a))
+
+
+def cubemap_faces_from_cross(cross, rgb_hex: int = 0):
+    """Host-only: the six faces (6, size, size, 4) the reference cuts out of a cube cross
+    (texture_utils.cpp:5-52), or its constant-colour fallback.  Returns (faces, used_fallback)."""
+    lib = load_library()
+    size, fb = C.c_uint32(0), C.c_int32(0)
+    if cross is None:
+        out = np.zeros(24, np.float32)
+        rc = lib.ptc_cubemap_faces_from_cross(None, 0, 0, 0, C.c_uint32(rgb_hex), _ptr(out), C.c_uint64(24),
+                                              C.byref(size), C.byref(fb))
+    else:
+        cross = np.ascontiguousarray(cross, dtype=np.float32)
+        h, w, nc = cross.shape
+        out = np.zeros(max(24, (w // 4) ** 2 * 24), np.float32)
+        rc = lib.ptc_cubemap_faces_from_cross(_ptr(cross), C.c_uint32(w), C.c_uint32(h), C.c_uint32(nc),
+                                              C.c_uint32(rgb_hex), _ptr(out), C.c_uint64(out.size),
+                                              C.byref(size), C.byref(fb))
+    if rc:
+        raise PtcError(f"ptc_cubemap_faces_from_cross failed: {rc}")
+    s = size.value
+    return out[: s * s * 24].reshape(6, s, s, 4).copy(), bool(fb.value)
+
+
+def write_ppm(path: str, rgba: np.ndarray) -> None:
+    """RGBA8 frame ((h, w) uint32 or (h, w, 4) uint8, row 0 = top) -> binary PPM."""
+    rgba = np.ascontiguousarray(rgba)
+    h, w = rgba.shape[:2]
+    if load_library().ptc_write_ppm(path.encode(), _ptr(rgba), C.c_uint32(w), C.c_uint32(h)):
+        raise PtcError(f"ptc_write_ppm({path}) failed")
+
+
+def accum_save(path: str, accum: np.ndarray, samples: int) -> None:
+    accum = np.ascontiguousarray(accum, dtype=np.float32)
+    rows, w = accum.shape[:2]
+    if load_library().ptc_accum_save(path.encode(), _ptr(accum), C.c_uint32(w), C.c_uint32(rows),
+                                     C.c_uint32(samples)):
+        raise PtcError(f"ptc_accum_save({path}) failed")
+
+
+def accum_load(path: str):
+    """Returns (accum (rows, w, 3) float32, samples)."""
+    lib = load_library()
+    w, rows, n = C.c_uint32(0), C.c_uint32(0), C.c_uint32(0)
+    if lib.ptc_accum_load(path.encode(), None, C.c_uint64(0), C.byref(w), C.byref(rows), C.byref(n)):
+        raise PtcError(f"ptc_accum_load({path}): not an accumulator file")
+    out = np.zeros((rows.value, w.value, 3), np.float32)
+    if lib.ptc_accum_load(path.encode(), _ptr(out), C.c_uint64(out.size), C.byref(w), C.byref(rows), C.byref(n)):
+        raise PtcError(f"ptc_accum_load({path}) failed")
+    return out, n.value
 
 
 def host_bvh(scene: ptscene.SceneBlob) -> dict:
@@ -183,6 +237,22 @@ class Core:
         self._check(self.lib.ptc_set_cubemap(self.ctx, _ptr(faces), C.c_uint32(faces.shape[1]),
                                              C.byref(cid)), "ptc_set_cubemap")
         return cid.value
+
+    def set_cubemap_from_cross(self, cross, rgb_hex: int = 0):
+        """uploadCubemap (gpu_processor.cpp:68-161) for a (h, w, nb_chan) float cube cross, or --
+        ``cross=None`` -- for the constant-colour path.  Returns (cubemap_id, used_fallback)."""
+        cid, fb = C.c_int32(-1), C.c_int32(0)
+        if cross is None:
+            rc = self.lib.ptc_set_cubemap_from_cross(self.ctx, None, 0, 0, 0, C.c_uint32(rgb_hex),
+                                                     C.byref(cid), C.byref(fb))
+        else:
+            cross = np.ascontiguousarray(cross, dtype=np.float32)
+            h, w, nc = cross.shape
+            rc = self.lib.ptc_set_cubemap_from_cross(self.ctx, _ptr(cross), C.c_uint32(w), C.c_uint32(h),
+                                                     C.c_uint32(nc), C.c_uint32(rgb_hex), C.byref(cid),
+                                                     C.byref(fb))
+        self._check(rc, "ptc_set_cubemap_from_cross")
+        return cid.value, bool(fb.value)
 
     def scene_info(self, scene_id: int) -> PtcSceneInfo:
         info = PtcSceneInfo()

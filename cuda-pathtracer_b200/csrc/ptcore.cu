@@ -576,6 +576,127 @@ ptc_set_cubemap(ptc_context* ctx, const float* faces, uint32_t size, int32_t* cu
   return PTC_OK;
 }
 
+int
+ptc_cubemap_faces_from_cross(const float* cross, uint32_t w, uint32_t h, uint32_t nb_chan, uint32_t rgb_hex,
+                             float* faces_out, uint64_t capacity, uint32_t* size_out, int32_t* used_fallback)
+{
+  if (!faces_out || !size_out)
+    return PTC_ERR_INVALID;
+  uint32_t size = w / 4u; // gpu_processor.cpp:101
+  const bool usable = cross && nb_chan >= 3 && size > 0 && size == h / 3u && !(size & (size - 1u));
+  if (used_fallback)
+    *used_fallback = (cross && !usable) ? 1 : 0;
+  if (!usable) {
+    // createUnitTexture (gpu_processor.cpp:38-58): six 1x1 faces of one colour, alpha 0
+    const uint32_t color = (cross || !rgb_hex) ? 0x131b23u : rgb_hex;
+    if (capacity < 24)
+      return PTC_ERR_INVALID;
+    for (int f = 0; f < 6; ++f) {
+      faces_out[4 * f + 0] = (float)((color >> 16) & 0xFFu) / 255.0f;
+      faces_out[4 * f + 1] = (float)((color >> 8) & 0xFFu) / 255.0f;
+      faces_out[4 * f + 2] = (float)(color & 0xFFu) / 255.0f;
+      faces_out[4 * f + 3] = 0.0f;
+    }
+    *size_out = 1;
+    return PTC_OK;
+  }
+  if (capacity < (uint64_t)size * size * 24u)
+    return PTC_ERR_INVALID;
+  // cell (column, row) of the cross for +x, -x, +y, -y, +z, -z
+  static const uint32_t cell[6][2] = { { 2, 1 }, { 0, 1 }, { 1, 0 }, { 1, 2 }, { 1, 1 }, { 3, 1 } };
+  for (int f = 0; f < 6; ++f) {
+    float* dst = faces_out + (size_t)f * size * size * 4u;
+    for (uint32_t y = 0; y < size; ++y) {
+      const float* src = cross + ((size_t)(cell[f][1] * size + y) * w + cell[f][0] * size) * nb_chan;
+      for (uint32_t x = 0; x < size; ++x, src += nb_chan, dst += 4) {
+        dst[0] = src[0];
+        dst[1] = src[1];
+        dst[2] = src[2];
+        dst[3] = 0.0f;
+      }
+    }
+  }
+  *size_out = size;
+  return PTC_OK;
+}
+
+int
+ptc_set_cubemap_from_cross(ptc_context* ctx, const float* cross, uint32_t w, uint32_t h, uint32_t nb_chan,
+                           uint32_t rgb_hex, int32_t* cubemap_id, int32_t* used_fallback)
+{
+  if (!ctx || !cubemap_id)
+    return PTC_ERR_INVALID;
+  const uint32_t s = w / 4u;
+  const bool usable = cross && nb_chan >= 3 && s > 0 && s == h / 3u && !(s & (s - 1u));
+  std::vector<float> faces(usable ? (size_t)s * s * 24u : 24u);
+  uint32_t size = 0;
+  int rc = ptc_cubemap_faces_from_cross(cross, w, h, nb_chan, rgb_hex, faces.data(), faces.size(), &size,
+                                        used_fallback);
+  if (rc)
+    return fail(ctx, rc, "cube cross extraction failed");
+  return ptc_set_cubemap(ctx, faces.data(), size, cubemap_id);
+}
+
+int
+ptc_write_ppm(const char* path, const void* rgba, uint32_t width, uint32_t height)
+{
+  if (!path || !rgba || !width || !height)
+    return PTC_ERR_INVALID;
+  FILE* f = fopen(path, "wb");
+  if (!f)
+    return PTC_ERR_INVALID;
+  fprintf(f, "P6\n%u %u\n255\n", width, height);
+  const unsigned char* px = (const unsigned char*)rgba;
+  std::vector<unsigned char> row((size_t)width * 3);
+  bool ok = true;
+  for (uint32_t y = 0; y < height && ok; ++y) {
+    for (uint32_t x = 0; x < width; ++x) {
+      const unsigned char* p = px + ((size_t)y * width + x) * 4;
+      row[3 * x] = p[0], row[3 * x + 1] = p[1], row[3 * x + 2] = p[2];
+    }
+    ok = fwrite(row.data(), 1, row.size(), f) == row.size();
+  }
+  ok = fclose(f) == 0 && ok;
+  return ok ? PTC_OK : PTC_ERR_INVALID;
+}
+
+int
+ptc_accum_save(const char* path, const float* accum, uint32_t width, uint32_t rows, uint32_t samples)
+{
+  if (!path || !accum || !width || !rows)
+    return PTC_ERR_INVALID;
+  FILE* f = fopen(path, "wb");
+  if (!f)
+    return PTC_ERR_INVALID;
+  const uint32_t hdr[4] = { 1u, width, rows, samples };
+  const size_t n = (size_t)width * rows * 3;
+  bool ok = fwrite("PTAC", 1, 4, f) == 4 && fwrite(hdr, 4, 4, f) == 4 && fwrite(accum, 4, n, f) == n;
+  ok = fclose(f) == 0 && ok;
+  return ok ? PTC_OK : PTC_ERR_INVALID;
+}
+
+int
+ptc_accum_load(const char* path, float* accum, uint64_t capacity_floats, uint32_t* width, uint32_t* rows,
+               uint32_t* samples)
+{
+  if (!path || !width || !rows || !samples)
+    return PTC_ERR_INVALID;
+  FILE* f = fopen(path, "rb");
+  if (!f)
+    return PTC_ERR_INVALID;
+  char magic[4];
+  uint32_t hdr[4];
+  bool ok = fread(magic, 1, 4, f) == 4 && memcmp(magic, "PTAC", 4) == 0 && fread(hdr, 4, 4, f) == 4 && hdr[0] == 1u;
+  if (ok) {
+    *width = hdr[1], *rows = hdr[2], *samples = hdr[3];
+    const uint64_t n = (uint64_t)hdr[1] * hdr[2] * 3;
+    if (accum) // accum == NULL: header query only
+      ok = n <= capacity_floats && fread(accum, 4, (size_t)n, f) == (size_t)n;
+  }
+  fclose(f);
+  return ok ? PTC_OK : PTC_ERR_INVALID;
+}
+
 // The reference's device tree, read back record by record (see ptcore.h).
 int
 ptc_upload_scene_from_device(ptc_context* ctx, const ptc_ref_scenes* scenes, uint32_t scene_index,

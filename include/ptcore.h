@@ -191,6 +191,39 @@ int ptc_scene_info_get(const ptc_context* ctx, int32_t scene_id, ptc_scene_info*
  * `faces` = 6 faces (+x,-x,+y,-y,+z,-z) of size*size RGBA floats, host memory. */
 int ptc_set_cubemap(ptc_context* ctx, const float* faces, uint32_t size, int32_t* cubemap_id);
 
+/* The other half of uploadCubemap (gpu_processor.cpp:84-132, texture_utils.cpp:5-52): a
+ * 4:3 "cube cross" image of w x h pixels, nb_chan (>= 3) linear floats per pixel as
+ * stbi_loadf returns it, is cut into the six faces (+x = cell (2,1), -x = (0,1), +y = (1,0),
+ * -y = (1,2), +z = (1,1), -z = (3,1); cells of size = w/4; alpha 0) and uploaded.  Like the
+ * reference, a cross with w/4 != h/3 or a non-power-of-two size is not an error: the constant
+ * colour 0x131b23 (size 1) is used instead and *used_fallback (optional) is set.
+ * `cross` == NULL selects that constant-colour path with `rgb_hex` (0 -> 0x131b23), which is
+ * what a scene without cubemap or with a "0xRRGGBB" cubemap line gets (gpu_processor.cpp:88-93). */
+int ptc_set_cubemap_from_cross(ptc_context* ctx, const float* cross, uint32_t w, uint32_t h,
+                               uint32_t nb_chan, uint32_t rgb_hex, int32_t* cubemap_id,
+                               int32_t* used_fallback);
+
+/* Host-only half of the above (no context, no GPU): writes the faces to `faces_out`
+ * (6 * size * size * 4 floats; capacity in floats) and the size to *size_out.  Returns
+ * PTC_ERR_INVALID when the capacity is too small. */
+int ptc_cubemap_faces_from_cross(const float* cross, uint32_t w, uint32_t h, uint32_t nb_chan,
+                                 uint32_t rgb_hex, float* faces_out, uint64_t capacity,
+                                 uint32_t* size_out, int32_t* used_fallback);
+
+/* -- headless output and resume (the window is gone; raytrace.cu:260-270 wrote RGBA8 to a GL
+ * surface that interop.cpp:67-72 blitted upside down) ------------------------------------
+ * ptc_write_ppm : binary PPM (P6) of an RGBA8 HOST frame as ptc_render writes it (row 0 = top,
+ *                 alpha dropped).
+ * ptc_accum_save/load : the float3 temporal framebuffer of a band (HOST, rows bottom-up as the
+ *                 core keeps them) with the sample count it holds, so that a long accumulation
+ *                 can stop and resume: load, pass the buffer as `accum` with upload_accum = 1
+ *                 and continue with frame_nb = samples + 1.
+ *                 File: "PTAC" u32 version(1) u32 width u32 rows u32 samples, then w*rows*3 f32. */
+int ptc_write_ppm(const char* path, const void* rgba, uint32_t width, uint32_t height);
+int ptc_accum_save(const char* path, const float* accum, uint32_t width, uint32_t rows, uint32_t samples);
+int ptc_accum_load(const char* path, float* accum, uint64_t capacity_floats, uint32_t* width,
+                   uint32_t* rows, uint32_t* samples);
+
 /* -- taking the reference's DEVICE data as GPUProcessor::init() leaves it --------------
  * Layout mirrors of scene::Buffer<T> (scene_data.h:10-15, 16 bytes) and scene::Scenes
  * (scene_data.h:83-87, 32 bytes): host structs holding device pointers.

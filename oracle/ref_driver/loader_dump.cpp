@@ -106,6 +106,33 @@ stb_gamma(unsigned char v)
 int
 main(int argc, char** argv)
 {
+  // ref_loader --cross IN.f32 W H NB_CHAN OUT.f32 : the reference's own face extraction
+  // (texture::append_cube_faces in uploadCubemap's order, gpu_processor.cpp:116-127) on a raw
+  // float cube cross; writes u32 size + 6*size*size*4 floats.  Used to pin ptc_cubemap_from_cross.
+  if (argc == 7 && std::string(argv[1]) == "--cross") {
+    const int w = atoi(argv[3]), h = atoi(argv[4]), nb_chan = atoi(argv[5]);
+    std::vector<float> in((size_t)w * h * nb_chan);
+    FILE* fi = fopen(argv[2], "rb");
+    if (!fi || fread(in.data(), 4, in.size(), fi) != in.size()) {
+      perror("ref_loader: --cross input");
+      return 1;
+    }
+    fclose(fi);
+    const unsigned size = w / 4; // gpu_processor.cpp:101
+    std::vector<float> img((size_t)size * size * 4 * 6);
+    float* tmp = texture::append_cube_faces(img.data(), in.data(), w, 0, nb_chan, 4, true, true);
+    tmp = texture::append_cube_faces(tmp, in.data(), w, 1, nb_chan, 4, false, false);
+    texture::append_cube_faces(tmp, in.data(), w, 1, nb_chan, 4, true, false);
+    FILE* fo = fopen(argv[6], "wb");
+    if (!fo) {
+      perror("ref_loader: --cross output");
+      return 1;
+    }
+    fwrite(&size, 4, 1, fo);
+    fwrite(img.data(), 4, img.size(), fo);
+    fclose(fo);
+    return 0;
+  }
   if (argc < 4) {
     std::cerr << "usage: ref_loader ASSET_FOLDER SCENE_FILE OUT.ptscene\n";
     return 2;

@@ -642,3 +642,55 @@ def test_pipelined_host_call_equals_synchronous(core):
     for k in range(n):
         assert (got[k].view(np.uint8).reshape(h, w, 4) == want_frames[k]).all(), k
     assert (bits(acc_out) == bits(accum)).all()
+
+
+def test_cubemap_from_cross_equals_faces(core):
+    """uploadCubemap's cross path (ptc_set_cubemap_from_cross) gives the image the explicit-faces
+    path gives, on an open scene where most camera rays reach the environment."""
+    P = pkg()
+    sc = load_scene("color_sample_plain")
+    size = 32
+    faces = P.synth.gradient_cubemap(size)  # (6, size, size, 4)
+    cross = np.zeros((3 * size, 4 * size, 3), np.float32)
+    for f, (cx, cy) in enumerate([(2, 1), (0, 1), (1, 0), (1, 2), (1, 1), (3, 1)]):
+        cross[cy * size:(cy + 1) * size, cx * size:(cx + 1) * size] = faces[f, :, :, :3]
+    sid = core.upload_scene(sc)
+    cid_faces = core.set_cubemap(faces)
+    cid_cross, fb = core.set_cubemap_from_cross(cross)
+    assert not fb
+    w, h = 160, 90
+    imgs = []
+    for cid in (cid_faces, cid_cross):
+        accum = np.zeros((h, w, 3), np.float32)
+        rgba = np.zeros((h, w), np.uint32)
+        core.render_host(sid, cid, sc, w, h, accum, rgba, None, bounces=3, frame_nb=1, upload_accum=True,
+                         download_accum=True)
+        imgs.append((accum.copy(), rgba.copy()))
+    assert (bits(imgs[0][0]) == bits(imgs[1][0])).all() and (imgs[0][1] == imgs[1][1]).all()
+    assert imgs[0][0].any()
+
+
+def test_accumulation_resumes_from_a_saved_accumulator(core, tmp_path):
+    """Stop after 3 samples, save, reload in a fresh context, continue to 6: bit-identical to
+    6 samples in one go (the accumulator + sample count are the whole state)."""
+    P = pkg()
+    L = loaded(core, "indoor_plain")
+    w, h = 128, 72
+    one = np.zeros((h, w, 3), np.float32)
+    for k in range(1, 7):
+        one, rgba_one, _ = render_np(core, L, w, h, k, 3, accum=one)
+    part = np.zeros((h, w, 3), np.float32)
+    for k in range(1, 4):
+        part, _, _ = render_np(core, L, w, h, k, 3, accum=part)
+    path = str(tmp_path / "acc.ptac")
+    P.core.accum_save(path, part, 3)
+    core2 = P.Core(0)
+    try:
+        L2 = Loaded(core2, L.sc)
+        acc, n = P.core.accum_load(path)
+        assert n == 3
+        for k in range(n + 1, 7):
+            acc, rgba_two, _ = render_np(core2, L2, w, h, k, 3, accum=acc)
+    finally:
+        core2.close()
+    assert (bits(acc) == bits(one)).all() and (rgba_two == rgba_one).all()

@@ -328,3 +328,77 @@ cudaError_t render_like_gpu_processor(uchar4* frame, const scene::Scenes& scenes
     r = subprocess.run(["g++", "-std=c++14", "-fsyntax-only", "-I", cuda_inc, "-I", os.path.join(REPO, "include"),
                         str(src)], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
+
+
+def test_parallel_bvh_build_is_thread_count_invariant(monkeypatch):
+    """The host build runs its bin passes and subtrees on worker threads
+    (bvh_builder.cpp); nodes and triangle order must not depend on how many.  600x600 grid =
+    720 k triangles: above both the parallel-pass and the task-spawn thresholds."""
+    sc = P.synth.terrain_room(600)
+    out = []
+    for threads in ("1", "3", "8"):
+        monkeypatch.setenv("PTC_BUILD_THREADS", threads)
+        hb = P.host_bvh(sc)
+        out.append((hb["nodes"].tobytes(), hb["tris"].tobytes(), hb["face_ids"].tobytes(), hb["max_depth"]))
+    assert out[0] == out[1] == out[2]
+    assert sorted(np.frombuffer(out[0][2], np.uint32).tolist()) == list(range(sc.n_faces))
+
+
+def test_cube_cross_faces_match_reference_extraction():
+    """ptc_cubemap_faces_from_cross against the frozen output of the reference's own
+    texture::append_cube_faces in uploadCubemap's order (tests/golden/cubemap_cross_kat.npz,
+    made with oracle/_ref/ref_loader --cross), plus the reference's fallbacks
+    (gpu_processor.cpp:88-93, 101-132)."""
+    kat = np.load(os.path.join(GOLDEN, "cubemap_cross_kat.npz"))
+    for tag in ("a", "b"):
+        faces, fb = P.core.cubemap_faces_from_cross(kat[f"cross_{tag}"])
+        assert not fb
+        assert faces.shape == kat[f"faces_{tag}"].shape
+        assert (faces.view(np.uint32) == kat[f"faces_{tag}"].view(np.uint32)).all()
+    default = np.array([0x13, 0x1b, 0x23], np.float32) / np.float32(255.0)
+    # no cubemap / hexadecimal colour line
+    faces, fb = P.core.cubemap_faces_from_cross(None)
+    assert faces.shape == (6, 1, 1, 4) and not fb and (faces[..., :3] == default).all() and (faces[..., 3] == 0).all()
+    faces, fb = P.core.cubemap_faces_from_cross(None, 0xFF8000)
+    assert (faces[0, 0, 0] == np.array([1.0, 128 / 255.0, 0.0, 0.0], np.float32)).all()
+    # not 4:3, and not a power of two: the reference falls back to the default colour, no error
+    for shape in ((10, 16, 3), (9, 12, 3), (36, 48, 3)):
+        faces, fb = P.core.cubemap_faces_from_cross(np.ones(shape, np.float32))
+        assert fb and faces.shape == (6, 1, 1, 4) and (faces[..., :3] == default).all()
+
+
+def test_cube_cross_faces_live_against_reference_code(tmp_path):
+    exe = os.path.join(REPO, "oracle", "_ref", "ref_loader")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/ref_loader not built")
+    rng = np.random.default_rng(11)
+    for w, h, nc in ((64, 48, 3), (8, 6, 4), (128, 96, 3)):
+        cross = rng.random((h, w, nc), dtype=np.float32)
+        cross.tofile(tmp_path / "c.f32")
+        subprocess.check_call([exe, "--cross", str(tmp_path / "c.f32"), str(w), str(h), str(nc),
+                               str(tmp_path / "f.f32")])
+        raw = np.fromfile(tmp_path / "f.f32", dtype=np.float32)
+        size = int(raw[:1].view(np.uint32)[0])
+        faces, fb = P.core.cubemap_faces_from_cross(cross)
+        assert not fb and (faces.view(np.uint32) == raw[1:].reshape(6, size, size, 4).view(np.uint32)).all()
+
+
+def test_ppm_and_accumulator_files(tmp_path):
+    """Headless output: PPM of the RGBA8 frame, accumulator save/load round trip."""
+    rng = np.random.default_rng(3)
+    rgba = rng.integers(0, 256, (5, 7, 4), dtype=np.uint8)
+    p = str(tmp_path / "f.ppm")
+    P.core.write_ppm(p, rgba)
+    raw = open(p, "rb").read()
+    assert raw.startswith(b"P6\n7 5\n255\n")
+    assert np.frombuffer(raw[len(b"P6\n7 5\n255\n"):], np.uint8).reshape(5, 7, 3).tolist() == rgba[..., :3].tolist()
+    P.core.write_ppm(p, rgba.view(np.uint32).reshape(5, 7))  # the (h, w) uint32 form ptc_render fills
+    assert open(p, "rb").read() == raw
+    acc = rng.random((5, 7, 3), dtype=np.float32)
+    a = str(tmp_path / "a.ptac")
+    P.core.accum_save(a, acc, 41)
+    back, n = P.core.accum_load(a)
+    assert n == 41 and (back.view(np.uint32) == acc.view(np.uint32)).all()
+    open(a, "wb").write(b"nope")
+    with pytest.raises(P.core.PtcError):
+        P.core.accum_load(a)
