@@ -64,7 +64,7 @@ def loaded(core, name):
                 # mis-parses into fov_x = 0 -> NaN rays; give it a usable camera
                 import copy
                 sc = copy.copy(sc)
-                sc.camera = P.synth.camera_array((0.3, 1.2, 4.0), (-0.05, -0.15, -1.0), aperture=0.02, focus_dist=3.0)
+                sc.camera = P.synth.camera_array((-2.7, 2.06, 2.52), (0.62, -0.348, -0.7), aperture=0.02, focus_dist=3.555)
         _loaded[name] = Loaded(core, sc)
     return _loaded[name]
 
