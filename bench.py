@@ -416,7 +416,25 @@ def roofline(P, core, sid, cid, sc, w, h, rows_kw, args, accum, out, stream):
     flops = prof["nodes_visited"] * 160.0 + prof["tris_tested"] * 37.0
     fp32_peak = 148 * 128 * 2 * 1965e6 / 1e12
     n = max(1, len(prof["launch_ms"]))
-    return {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": None,
+    # Which memory tier the BVH bytes actually come from, and that tier's MEASURED read bandwidth
+    # on this box (ptc_debug_read_bandwidth: the traversal's 16-byte read-only loads over a working
+    # set of that size).  t_roof = bvh bytes / tier bandwidth + every other byte / HBM bandwidth.
+    bvh_resident = info.bvh_nodes * info.bvh_node_bytes + info.n_faces * info.tri_bytes
+    tier = "l1" if bvh_resident <= (64 << 10) else ("l2" if bvh_resident <= (64 << 20) else "hbm")
+    tiers = None
+    try:
+        tiers = {"l1_gbs": core.read_bandwidth(32 << 10, 48 << 30), "l2_gbs": core.read_bandwidth(32 << 20, 24 << 30),
+                 "hbm_read_gbs": core.read_bandwidth(4 << 30, 16 << 30)}
+        tier_bw = {"l1": tiers["l1_gbs"], "l2": tiers["l2_gbs"], "hbm": tiers["hbm_read_gbs"]}[tier]
+        t_roof_ms = (b_bvh / tier_bw + (nbytes - b_bvh) / hbm) / 1e9 * 1e3
+        tiers.update({"bvh_resident_bytes": bvh_resident, "bvh_tier": tier, "t_roof_ms": t_roof_ms,
+                      "frac_of_tier_roofline": t_roof_ms / k_ms,
+                      "how": "16-byte read-only loads from all SMs over a zeroed working set of 32 KB / 32 MB / 4 GB"})
+    except Exception as e:
+        tiers = {"error": str(e)}
+    traffic = dram_traffic_per_launch(args, w, h, n)
+    return {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": traffic,
+            "cache_tiers": tiers,
             "peak_source": how, "kernel": "ptc::k_path + ptc::k_extend (the wavefront stages of one frame)",
             "launches_per_frame": n, "kernel_ms_per_launch": k_ms / n, "kernel_ms_per_frame": k_ms,
             "frame_ms": prof["frame_ms"], "kernel_share_of_frame": k_ms / prof["frame_ms"],
@@ -430,8 +448,21 @@ def roofline(P, core, sid, cid, sc, w, h, rows_kw, args, accum, out, stream):
                            "achieved_tflops": flops / (k_ms * 1e-3) / 1e12,
                            "peak_tflops_at_max_clock": fp32_peak,
                            "frac": flops / (k_ms * 1e-3) / 1e12 / fp32_peak},
-            "note": "27 KB of BVH + triangles is L1/L2-resident: the kernel is issue/latency-bound, "
-                    "neither term is expected near 1 on this scene"}
+            "note": "achieved counts ALGORITHMIC bytes; BVH bytes of a cache-resident scene never reach HBM "
+                    "(traffic = measured DRAM bytes), so frac against the HBM peak says how hard the caches "
+                    "are driven; cache_tiers gives the roofline against the tier the BVH lives in"}
+
+
+def dram_traffic_per_launch(args, w, h, n_launches):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the frame's stage kernels from the committed
+    `ncu --set full` capture of this workload (profiles/dram_traffic.json), per launch; None for a
+    workload that has no capture."""
+    try:
+        table = json.load(open(os.path.join(REPO, "profiles", "dram_traffic.json")))
+        ent = table.get(f"{args.scene} {w}x{h} b={args.bounces}")
+        return ent["dram_bytes_per_frame"] / n_launches if ent else None
+    except Exception:
+        return None
 
 
 def reference_kernel_on_gpu(sc, w, h, bounces, K, W):

@@ -75,7 +75,7 @@ EXPORTS = ["ptc_abi_version", "ptc_create", "ptc_destroy", "ptc_last_error", "pt
            "ptc_profile_frame", "ptc_render_host_async", "ptc_wait",
            "ptc_upload_scene_from_device", "ptc_set_cubemap_from_array",
            "ptc_set_cubemap_from_cross", "ptc_cubemap_faces_from_cross",
-           "ptc_write_ppm", "ptc_accum_save", "ptc_accum_load"]
+           "ptc_write_ppm", "ptc_accum_save", "ptc_accum_load", "ptc_debug_read_bandwidth"]
 
 _lib = None
 
@@ -104,7 +104,8 @@ def load_library() -> C.CDLL:
                      "ptc_launch_count", "ptc_set_wavefront", "ptc_profile_frame",
                      "ptc_render_host_async", "ptc_wait", "ptc_set_cubemap_from_cross",
                      "ptc_cubemap_faces_from_cross", "ptc_upload_scene_from_device",
-                     "ptc_set_cubemap_from_array", "ptc_write_ppm", "ptc_accum_save", "ptc_accum_load"]:
+                     "ptc_set_cubemap_from_array", "ptc_write_ppm", "ptc_accum_save", "ptc_accum_load",
+                     "ptc_debug_read_bandwidth"]:
             getattr(lib, name).restype = C.c_int
         lib.ptc_band_rows.restype = C.c_uint32
         _lib = lib
@@ -253,6 +254,14 @@ class Core:
                                                      C.byref(fb))
         self._check(rc, "ptc_set_cubemap_from_cross")
         return cid.value, bool(fb.value)
+
+    def read_bandwidth(self, working_set_bytes: int, total_bytes: int) -> float:
+        """Measured GB/s of 16-byte read-only loads over a working set of that size."""
+        out = C.c_float(0)
+        self._check(self.lib.ptc_debug_read_bandwidth(self.ctx, C.c_uint64(working_set_bytes),
+                                                      C.c_uint64(total_bytes), C.byref(out)),
+                    "ptc_debug_read_bandwidth")
+        return float(out.value)
 
     def scene_info(self, scene_id: int) -> PtcSceneInfo:
         info = PtcSceneInfo()

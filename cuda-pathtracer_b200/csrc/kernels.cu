@@ -29,8 +29,16 @@ warp_sum(uint32_t v)
 
 // HITS: the closest triangle hit of every queue slot was already found by k_extend; only the
 // sphere lights are tested here before shading (n_iters must be 1).
+// Register budget of the path kernels = 65536 / (256 x PTC_PATH_BLOCKS).  The fused first stage
+// wants 126 registers (2 CTAs per SM), but it is bound by latency (texel fetches, dependent
+// traversal steps), not by registers: capped at 64 it spills a few words and runs 4 CTAs per SM --
+// measured -3 % (indoor 1080p) to -10 % (color_sample 4K) frame time; 3 CTAs (80 registers) is
+// within 0.5 % of that.
+#ifndef PTC_PATH_BLOCKS
+#define PTC_PATH_BLOCKS 4
+#endif
 template <bool FIRST, bool STATS, bool HITS>
-__global__ void __launch_bounds__(kBlock, 2)
+__global__ void __launch_bounds__(kBlock, PTC_PATH_BLOCKS)
 k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, const RayQueue qin,
        const uint4* __restrict__ hits,
        const uint32_t* __restrict__ qin_count, const RayQueue qout, uint32_t* __restrict__ qout_count,
@@ -203,8 +211,11 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
 // ---------------------------------------------------------------------------
 // (A 4-CTAs-per-SM build at 64 registers was measured: no gain on either the 28 KB or the
 // 1.4 GB scene -- the limit is issue slots / L1 wavefronts, not warps in flight.)
+#ifndef PTC_EXTEND_BLOCKS
+#define PTC_EXTEND_BLOCKS 3
+#endif
 template <bool STATS>
-__global__ void __launch_bounds__(kBlock, 3)
+__global__ void __launch_bounds__(kBlock, PTC_EXTEND_BLOCKS)
 k_extend(const DScene sc, const RayQueue qin, const uint32_t* __restrict__ qin_count,
          uint4* __restrict__ hits, uint32_t* __restrict__ work, Counters* __restrict__ ctr,
          const uint32_t refill, const int last, const int stack_cap)
@@ -480,6 +491,35 @@ launch_intersect_rays(const DScene& sc, const float* origins, const float* dirs,
 {
   if (n)
     k_intersect_rays<<<blocks_for(n, 128), 128, 0, s>>>(sc, origins, dirs, n, ids, ts, ctr);
+}
+
+// Read-bandwidth probe: every thread streams 16-byte read-only loads (the traversal's load
+// path) over a working set of ws_vec uint4 (power of two), wrapping around, four loads in
+// flight.  A working set that fits L1 / L2 / neither measures that tier.
+__global__ void __launch_bounds__(256)
+k_debug_read_bw(const uint4* __restrict__ p, uint32_t ws_mask, uint64_t per_thread, uint32_t* sink)
+{
+  const uint32_t stride = gridDim.x * blockDim.x;
+  uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  uint4 a = make_uint4(0, 0, 0, 0);
+  for (uint64_t i = 0; i < per_thread; i += 4) {
+    const uint4 v0 = __ldg(p + (k & ws_mask));
+    const uint4 v1 = __ldg(p + ((k + stride) & ws_mask));
+    const uint4 v2 = __ldg(p + ((k + 2u * stride) & ws_mask));
+    const uint4 v3 = __ldg(p + ((k + 3u * stride) & ws_mask));
+    k += 4u * stride;
+    a.x ^= v0.x ^ v1.x ^ v2.x ^ v3.x, a.y ^= v0.y ^ v1.y ^ v2.y ^ v3.y;
+    a.z ^= v0.z ^ v1.z ^ v2.z ^ v3.z, a.w ^= v0.w ^ v1.w ^ v2.w ^ v3.w;
+  }
+  if ((a.x ^ a.y ^ a.z ^ a.w) == 0x9E3779B9u) // never true for a zeroed buffer; keeps the loads
+    *sink = a.x;
+}
+
+void
+launch_debug_read_bw(const uint4* p, uint32_t ws_vec, uint64_t per_thread, uint32_t grid, uint32_t* sink,
+                     cudaStream_t s)
+{
+  k_debug_read_bw<<<grid, 256, 0, s>>>(p, ws_vec - 1u, per_thread, sink);
 }
 
 void

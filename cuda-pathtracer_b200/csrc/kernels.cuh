@@ -37,6 +37,9 @@ void launch_primary_hits(const FrameParams& fp, const DScene& sc, int32_t* ids, 
                          cudaStream_t s);
 void launch_intersect_rays(const DScene& sc, const float* origins, const float* dirs, uint64_t n,
                            int32_t* ids, float* ts, Counters* ctr, cudaStream_t s);
+// read-bandwidth probe over a working set of ws_vec (power of two) uint4
+void launch_debug_read_bw(const uint4* p, uint32_t ws_vec, uint64_t per_thread, uint32_t grid, uint32_t* sink,
+                          cudaStream_t s);
 void launch_debug_rng(const uint32_t* seeds, uint32_t n_seeds, uint32_t n_draws, float* out,
                       cudaStream_t s);
 // toolkit cuRAND on the device, for the RNG known-answer test

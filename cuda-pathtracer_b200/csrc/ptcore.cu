@@ -19,6 +19,7 @@
 
 using namespace ptc;
 
+
 namespace {
 
 struct SceneDev
@@ -52,8 +53,8 @@ struct ptc_context
   int n_sms = 148;
   // persistent grids, [stats]: first stage, fused later stage, shade-after-extend, extend
   uint32_t first_iters = 0, next_iters = 1; // first_iters 0 = per scene (frame_schedule) // wavefront granularity (ptc_set_wavefront)
-  uint32_t split_extend = 1;   // later stages: separate refilling extend kernel + shade kernel
-  uint32_t refill = 8;         // idle lanes of a warp that trigger a refill in k_extend
+  int32_t split_extend = -1;   // later stages as refilling extend kernel + shade kernel: 1 / 0, -1 = per scene
+  uint32_t refill = 12;        // idle lanes of a warp that trigger a refill in k_extend
   uint4* hits = nullptr;       // closest triangle hit per queue slot (split stages)
   uint64_t launches = 0;
   uint32_t seed = 0;           // the reference's function-static frame counter (raytrace.cu:296)
@@ -255,24 +256,31 @@ struct Step
 // The wavefront schedule of a frame: the first stage generates the rays and runs
 // `first_iters` radiance-loop iterations in registers; every later stage runs `next_iters`.
 int
-frame_schedule(const ptc_context* ctx, const FrameParams& fp, size_t bvh_bytes, Step* steps)
+frame_schedule(const ptc_context* ctx, const FrameParams& fp, size_t bvh_bytes, Step* steps, bool* split_out)
 {
   int n = 0;
+  // automatic (measured on B200 with the path kernels at 4 CTAs per SM, tools/sweep2.py):
+  //  * nodes + triangles <= 1 MB (cache-resident; the reference's scenes are 10-30 KB): one
+  //    radiance-loop iteration per launch, each launch traverses AND shades -- 0.646 ms against
+  //    0.672 ms for the split form on the 1080p indoor frame;
+  //  * larger (L2/HBM-resident): two iterations fused into the first stage, then the refilling
+  //    extend kernel + a shade kernel per iteration -- 2.70 ms against 3.42 ms on 10 M triangles.
+  const bool small = bvh_bytes <= (1u << 20);
+  const bool split = ctx->split_extend >= 0 ? ctx->split_extend != 0 : !small;
+  if (split_out)
+    *split_out = split;
   if (!fp.is_static) {
     steps[n++] = Step{ true, 0, 1 };
     return n;
   }
-  // automatic: a BVH that lives in L1 (the 27 KB indoor scene) traverses its second
-  // iteration fastest straight out of registers; a BVH in L2/HBM gains more from handing
-  // the incoherent rays to the refilling extend kernel right away (measured both ways).
   int first = (int)ctx->first_iters;
   if (first == 0)
-    first = bvh_bytes <= (1u << 20) ? 2 : 1;
+    first = small ? 1 : 2;
   int b = first < fp.max_bounces ? first : fp.max_bounces;
   steps[n++] = Step{ true, 0, b };
   while (b < fp.max_bounces) {
     int k = (int)ctx->next_iters < fp.max_bounces - b ? (int)ctx->next_iters : fp.max_bounces - b;
-    if (ctx->split_extend)
+    if (split)
       k = 1;
     steps[n++] = Step{ false, b, k };
     b += k;
@@ -294,7 +302,8 @@ enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp,
     return rc;
   FrameOut fo{ accum, out, rad };
   Step steps[kMaxBounces + 2];
-  const int n_steps = frame_schedule(ctx, fp, scene_bvh_bytes(ctx, a->scene_id), steps);
+  bool split = false;
+  const int n_steps = frame_schedule(ctx, fp, scene_bvh_bytes(ctx, a->scene_id), steps, &split);
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->counts, 0, sizeof(uint32_t) * kCountSlots, s));
   int n_ev = 0;
   if (ev)
@@ -309,7 +318,7 @@ enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp,
       const uint32_t want = (tiles + kBlock / 32 - 1) / (kBlock / 32);
       const uint32_t cap = (uint32_t)sc.grid_first[stats];
       grid = want < cap ? want : cap;
-    } else if (ctx->split_extend) {
+    } else if (split) {
       launch_extend(stats, (uint32_t)sc.grid_extend[stats], sc.d, ctx->queue[k & 1], ctx->counts + k,
                     ctx->hits, work + 1, ctx->ctr, ctx->refill, st.bounce0 + 1 >= fp.max_bounces,
                     sc.stack_cap, s);
@@ -976,12 +985,14 @@ ptc_set_wavefront(ptc_context* ctx, uint32_t first_iters, uint32_t next_iters, i
   if (!ctx)
     return PTC_ERR_INVALID;
   if (split_extend >= 0)
-    ctx->split_extend = split_extend ? 1u : 0u;
+    ctx->split_extend = split_extend ? 1 : 0;
   if (refill)
     ctx->refill = refill > 32 ? 32 : refill;
-  if (first_iters == 0xFFFFFFFFu)
-    ctx->first_iters = 0; // automatic (per scene size)
-  else if (first_iters)
+  if (first_iters == 0xFFFFFFFFu) {
+    ctx->first_iters = 0; // automatic (per scene size) ...
+    ctx->split_extend = -1; // ... for the whole schedule
+    ctx->next_iters = 1;
+  } else if (first_iters)
     ctx->first_iters = first_iters;
   if (next_iters)
     ctx->next_iters = next_iters;
@@ -1003,14 +1014,15 @@ ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeat
     return fail(ctx, PTC_ERR_INVALID, "accum is required");
   cudaStream_t s = (cudaStream_t)args->stream;
   Step steps[kMaxBounces + 2];
-  const int n_steps = frame_schedule(ctx, fp, scene_bvh_bytes(ctx, args->scene_id), steps);
+  bool split = false;
+  const int n_steps = frame_schedule(ctx, fp, scene_bvh_bytes(ctx, args->scene_id), steps, &split);
   // the launches of one frame: kind 0 = first stage, 1 = fused later stage, 2 = extend, 3 = shade
   struct L { uint32_t kind, bounce0, iters; };
   std::vector<L> launches;
   for (int k = 0; k < n_steps; ++k) {
     if (steps[k].first)
       launches.push_back({ 0u, 0u, (uint32_t)steps[k].n_iters });
-    else if (ctx->split_extend) {
+    else if (split) {
       launches.push_back({ 2u, (uint32_t)steps[k].bounce0, 1u });
       launches.push_back({ 3u, (uint32_t)steps[k].bounce0, 1u });
     } else
@@ -1040,7 +1052,7 @@ ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeat
   for (int k = 1; k < n_steps; ++k)
     out->queue_rays += counts[k];
   out->queue_bytes_per_ray = 4 * sizeof(float4);
-  out->hit_bytes_per_ray = ctx->split_extend ? (uint32_t)sizeof(uint4) : 0u;
+  out->hit_bytes_per_ray = split ? (uint32_t)sizeof(uint4) : 0u;
   // timed passes
   for (uint32_t r = 0; r < repeats; ++r) {
     rc = enqueue_frame(ctx, args, fp, (float*)args->accum, (uint32_t*)args->out_rgba, nullptr, s, false,
@@ -1144,6 +1156,47 @@ ptc_intersect_rays(ptc_context* ctx, int32_t scene_id, const float* origins, con
   cudaFree(d_o), cudaFree(d_d), cudaFree(d_i), cudaFree(d_t);
   if (e != cudaSuccess)
     return fail(ctx, (int)e, cudaGetErrorString(e));
+  return PTC_OK;
+}
+
+int
+ptc_debug_read_bandwidth(ptc_context* ctx, uint64_t working_set_bytes, uint64_t total_bytes, float* gb_per_s)
+{
+  if (!ctx || !gb_per_s || working_set_bytes < 16 || !total_bytes)
+    return PTC_ERR_INVALID;
+  DeviceGuard g(ctx->device);
+  uint64_t ws_vec = 1;
+  while (ws_vec * 2 * 16 <= working_set_bytes && ws_vec < (1ull << 31))
+    ws_vec *= 2; // power of two <= the request
+  uint4* buf = nullptr;
+  uint32_t* sink = nullptr;
+  CUDA_TRY(ctx, cudaMalloc(&buf, ws_vec * 16));
+  CUDA_TRY(ctx, cudaMalloc(&sink, 4));
+  cudaMemset(buf, 0, ws_vec * 16);
+  const uint32_t grid = (uint32_t)ctx->n_sms * 8u;
+  const uint64_t threads = (uint64_t)grid * 256u;
+  uint64_t per_thread = (total_bytes / 16 + threads - 1) / threads;
+  per_thread = (per_thread + 3) & ~(uint64_t)3;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0), cudaEventCreate(&e1);
+  float best = 0.f;
+  for (int rep = 0; rep < 4; ++rep) { // rep 0 warms the cache tier under test
+    cudaEventRecord(e0, 0);
+    launch_debug_read_bw(buf, (uint32_t)ws_vec, per_thread, grid, sink, 0);
+    cudaEventRecord(e1, 0);
+    cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const float gbs = (float)((double)per_thread * threads * 16.0 / (ms * 1e-3) / 1e9);
+    if (rep && gbs > best)
+      best = gbs;
+  }
+  cudaEventDestroy(e0), cudaEventDestroy(e1);
+  cudaError_t e = cudaDeviceSynchronize();
+  cudaFree(buf), cudaFree(sink);
+  if (e != cudaSuccess)
+    return fail(ctx, (int)e, cudaGetErrorString(e));
+  *gb_per_s = best;
   return PTC_OK;
 }
 

@@ -292,11 +292,13 @@ int ptc_launch_count(const ptc_context* ctx, uint64_t* out);
 
 /* Wavefront schedule.  first_iters / next_iters: how many radiance-loop iterations the first
  * stage (generate + extend + shade) and each later stage run in registers before handing the
- * surviving rays to the next stage through the compacted queue (0 keeps the current value;
- * first_iters = 0xFFFFFFFF restores the default: chosen per scene from the BVH size).
+ * surviving rays to the next stage through the compacted queue (0 keeps the current value).
  * split_extend: 1 = every later stage is an extend kernel with per-lane refill followed by
- * a shade kernel (one iteration per stage; default), 0 = fused extend+shade, < 0 keeps.
- * refill: idle lanes per warp that trigger a refill in the extend kernel (0 keeps).
+ * a shade kernel (one iteration per stage), 0 = fused extend+shade, < 0 keeps.
+ * refill: idle lanes per warp that trigger a refill in the extend kernel (0 keeps; default 12).
+ * Default: chosen per scene from the size of its BVH (cache-resident: 1 iteration per stage,
+ * fused; larger: 2 iterations in the first stage, then split stages);
+ * first_iters = 0xFFFFFFFF restores that default for all three.
  * Results do not depend on any of it
  * (tests/test_gpu_parity.py::test_wavefront_granularity_invariance). */
 int ptc_set_wavefront(ptc_context* ctx, uint32_t first_iters, uint32_t next_iters,
@@ -342,6 +344,13 @@ int ptc_intersect_rays(ptc_context* ctx, int32_t scene_id, const float* origins,
  * the toolkit's curand_kernel.h on the device. out[n_seeds*n_draws] HOST. */
 int ptc_debug_rng(ptc_context* ctx, const uint32_t* seeds, uint32_t n_seeds,
                   uint32_t n_draws, int reference_impl, float* out);
+
+/* Measured read bandwidth (GB/s) of the traversal's load path (16-byte read-only loads, all
+ * SMs) over a zeroed working set of `working_set_bytes` (rounded down to a power of two),
+ * reading `total_bytes` in all: a working set that fits L1 (<= 64 KB), L2 (e.g. 32 MB) or
+ * neither gives the denominator of that tier for the roofline in bench.py. */
+int ptc_debug_read_bandwidth(ptc_context* ctx, uint64_t working_set_bytes, uint64_t total_bytes,
+                             float* gb_per_s);
 
 /* -- host-only helpers (no GPU needed) ----------------------------------------- */
 
