@@ -27,13 +27,26 @@ struct DTexture // arena-resident copy of scene::Texture (scene_data.h:31-37)
   int32_t w, h, nb_chan, _pad;
 };
 
+// What shading needs to know about a material in ONE table entry (3 x LDG.128): the reference
+// walks Material -> Texture[diffuse_spec_map] -> texels and Texture[normal_map] -> texels
+// (intersection.cuh:216-242), i.e. two dependent loads before the texel address is known.
+struct __align__(16) DMaterial
+{
+  const float* diffuse; // RGBA float texels (rgb = diffuse, a = specular mix)
+  const float* normal;  // RGB float texels, or null
+  int32_t dw, dh;       // diffuse/specular map size
+  int32_t nw, nh;       // normal map size
+  float ior;
+  uint32_t _pad[3];
+};
+static_assert(sizeof(DMaterial) == 48, "DMaterial is read as three 16-byte loads");
+
 struct DScene
 {
   const uint4* nodes;
   const float4* tris;
   const float4* shade;
-  const ptc_material* materials;
-  const DTexture* textures;
+  const DMaterial* mats;
   const ptc_light* lights;
   uint32_t n_faces;
   uint32_t n_lights;

@@ -478,7 +478,6 @@ ptc_upload_scene(ptc_context* ctx, const ptc_scene_desc* desc, int32_t* scene_id
   if ((rc = dev_upload(ctx, s, bvh.nodes.data(), bvh.nodes.size(), &d_nodes)) ||
       (rc = dev_upload(ctx, s, bvh.tris.data(), bvh.tris.size(), &d_tris)) ||
       (rc = dev_upload(ctx, s, shade.data(), shade.size(), &d_shade)) ||
-      (rc = dev_upload(ctx, s, desc->materials, desc->n_materials, &s.d.materials)) ||
       (rc = dev_upload(ctx, s, desc->lights, desc->n_lights, &s.d.lights)))
     return rc;
   s.d.nodes = (const uint4*)d_nodes;
@@ -513,7 +512,22 @@ ptc_upload_scene(ptc_context* ctx, const ptc_scene_desc* desc, int32_t* scene_id
     dt[i].nb_chan = t.nb_chan;
     dt[i]._pad = 0;
   }
-  if ((rc = dev_upload(ctx, s, dt.data(), dt.size(), &s.d.textures)))
+  // one merged entry per material: texel pointers + sizes + ior (device_types.cuh DMaterial)
+  std::vector<DMaterial> dm(desc->n_materials);
+  for (uint32_t i = 0; i < desc->n_materials; ++i) {
+    const ptc_material& m = desc->materials[i];
+    memset(&dm[i], 0, sizeof(DMaterial));
+    dm[i].diffuse = dt[m.diffuse_spec_map].data;
+    dm[i].dw = dt[m.diffuse_spec_map].w;
+    dm[i].dh = dt[m.diffuse_spec_map].h;
+    if (m.normal_map >= 0) {
+      dm[i].normal = dt[m.normal_map].data;
+      dm[i].nw = dt[m.normal_map].w;
+      dm[i].nh = dt[m.normal_map].h;
+    }
+    dm[i].ior = m.ior;
+  }
+  if ((rc = dev_upload(ctx, s, dm.data(), dm.size(), &s.d.mats)))
     return rc;
 
   // persistent grids: resident CTAs per SM x SMs (148 on B200), for this scene's stack size

@@ -28,11 +28,11 @@ struct Surface // what intersect() leaves in IntersectionData (intersection.cuh:
 
 // nearest texel, no filtering, no V flip: intersection.cuh:20-26
 __device__ __forceinline__ int
-texel_index(const DTexture& tex, float2 uv)
+texel_index(int w, int h, int nb_chan, float2 uv)
 {
-  int x = (int)(uv.x * (float)(tex.w - 1));
-  int y = (int)(uv.y * (float)(tex.h - 1));
-  return (y * tex.w + x) * tex.nb_chan;
+  int x = (int)(uv.x * (float)(w - 1));
+  int y = (int)(uv.y * (float)(h - 1));
+  return (y * w + x) * nb_chan;
 }
 
 // Material / normal resolve for the winning hit: intersection.cuh:183-243.
@@ -42,7 +42,7 @@ resolve_hit(const DScene& sc, uint32_t id, float t, float u, float v, float3 dir
             Surface& s)
 {
   if (id >= sc.n_faces) { // sphere light, intersection.cuh:199-212
-    const ptc_light L = sc.lights[id - sc.n_faces];
+    const ptc_light L = load_light(sc, id - sc.n_faces);
     s.is_light = true;
     s.light_color = mk3(L.color[0], L.color[1], L.color[2]);
     s.light_emission = L.emission;
@@ -67,17 +67,23 @@ resolve_hit(const DScene& sc, uint32_t id, float t, float u, float v, float3 dir
   uv.x = uv.x - floorf(uv.x / 1.0f);
   uv.y = uv.y - floorf(uv.y / 1.0f);
 
-  const ptc_material m = sc.materials[material_id];
-  s.ior = m.ior;
-  const DTexture dt = sc.textures[m.diffuse_spec_map];
-  const int idx = texel_index(dt, uv);
-  s.diffuse_col = mk3(dt.data[idx], dt.data[idx + 1], dt.data[idx + 2]);
-  s.specular_col = dt.data[idx + 3];
+  const float4* mp = reinterpret_cast<const float4*>(sc.mats + material_id);
+  const float4 m0 = __ldg(mp), m1 = __ldg(mp + 1), m2 = __ldg(mp + 2);
+  const float* diffuse = reinterpret_cast<const float*>(
+    (uintptr_t)__float_as_uint(m0.x) | ((uintptr_t)__float_as_uint(m0.y) << 32));
+  const float* nmap = reinterpret_cast<const float*>(
+    (uintptr_t)__float_as_uint(m0.z) | ((uintptr_t)__float_as_uint(m0.w) << 32));
+  const int dw = __float_as_int(m1.x), dh = __float_as_int(m1.y);
+  const int nw = __float_as_int(m1.z), nh = __float_as_int(m1.w);
+  s.ior = m2.x;
+  // RGBA texel in one 16-byte load (4 channels checked at upload, arena 256-byte aligned)
+  const float4 tx4 = __ldg(reinterpret_cast<const float4*>(diffuse + texel_index(dw, dh, 4, uv)));
+  s.diffuse_col = mk3(tx4.x, tx4.y, tx4.z);
+  s.specular_col = tx4.w;
   s.normal = surface_normal;
-  if (m.normal_map >= 0) { // intersection.cuh:228-242
-    const DTexture nt = sc.textures[m.normal_map];
-    const int nidx = texel_index(nt, uv);
-    float3 n = mk3(nt.data[nidx], nt.data[nidx + 1], nt.data[nidx + 2]);
+  if (nmap) { // intersection.cuh:228-242
+    const int nidx = texel_index(nw, nh, 3, uv);
+    float3 n = mk3(__ldg(nmap + nidx), __ldg(nmap + nidx + 1), __ldg(nmap + nidx + 2));
     n = normalize((n * 2.0f) - 1.0f);
     const float3 binormal = normalize(cross(tangent, surface_normal));
     const float3 tx = tangent, ty = -binormal, tz = surface_normal;

@@ -391,20 +391,27 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
   return !((T.ng.y & 0xFF000000u) | T.tmask | (uint32_t)T.sp | (uint32_t)T.tsp);
 }
 
+// 32-byte light record in two 16-byte loads (the array comes from cudaMalloc; the C struct alone
+// only promises 4-byte alignment, which makes the compiler emit eight scalar loads).
+__device__ __forceinline__ ptc_light
+load_light(const DScene& sc, uint32_t l)
+{
+  const float4* lp = reinterpret_cast<const float4*>(sc.lights + l);
+  const float4 l0 = __ldg(lp), l1 = __ldg(lp + 1);
+  ptc_light L;
+  L.color[0] = l0.x, L.color[1] = l0.y, L.color[2] = l0.z;
+  L.vec[0] = l0.w, L.vec[1] = l1.x, L.vec[2] = l1.y;
+  L.emission = l1.z, L.radius = l1.w;
+  return L;
+}
+
 // Sphere lights after the triangles, 0 <= t < best in light order (intersection.cuh:199-212).
 __device__ __forceinline__ void
 lights_hit(const DScene& sc, const float3 o, const float3 d, float& best_t, uint32_t& best_id)
 {
   for (uint32_t l = 0; l < sc.n_lights; ++l) {
     float t;
-    // 32-byte record in two 16-byte loads (the array comes from cudaMalloc; the C struct alone
-    // only promises 4-byte alignment, which makes the compiler emit eight scalar loads)
-    const float4* lp = reinterpret_cast<const float4*>(sc.lights + l);
-    const float4 l0 = __ldg(lp), l1 = __ldg(lp + 1);
-    ptc_light L;
-    L.color[0] = l0.x, L.color[1] = l0.y, L.color[2] = l0.z;
-    L.vec[0] = l0.w, L.vec[1] = l1.x, L.vec[2] = l1.y;
-    L.emission = l1.z, L.radius = l1.w;
+    const ptc_light L = load_light(sc, l);
     if (sphere_test(L, o, d, t) && t < best_t && t >= 0.f) {
       best_t = t;
       best_id = sc.n_faces + l;
