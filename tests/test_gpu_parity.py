@@ -694,3 +694,35 @@ def test_accumulation_resumes_from_a_saved_accumulator(core, tmp_path):
     finally:
         core2.close()
     assert (bits(acc) == bits(one)).all() and (rgba_two == rgba_one).all()
+
+
+def test_frame_is_cuda_graph_capturable(core):
+    """every launch of a frame goes to the caller's stream with no host
+    synchronisation, so after a first call at that size (which allocates the queues) a frame can
+    be captured into a CUDA graph and replayed.  Replay == eager, bit for bit."""
+    import torch
+    L = loaded(core, "indoor_tex")
+    w, h = 320, 180
+    acc_e, out_e, _ = dev_buffers(w, h)
+    acc_g, out_g, _ = dev_buffers(w, h)
+    core.render(L.sid, L.cid, L.sc, w, h, acc_e, out_e, None, bounces=4, frame_nb=3)  # allocates
+    acc_e.zero_()
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(graph, stream=side):
+            core.render(L.sid, L.cid, L.sc, w, h, acc_g, out_g, None, bounces=4, frame_nb=3,
+                        stream=side.cuda_stream)
+    acc_g.zero_()
+    out_g.zero_()
+    torch.cuda.synchronize()
+    graph.replay()
+    core.render(L.sid, L.cid, L.sc, w, h, acc_e, out_e, None, bounces=4, frame_nb=3)
+    torch.cuda.synchronize()
+    assert acc_g.any()
+    assert (bits(acc_g.cpu().numpy()) == bits(acc_e.cpu().numpy())).all()
+    assert (out_g.cpu().numpy() == out_e.cpu().numpy()).all()
+    graph.replay()  # accumulates a second sample of the same frame on top
+    torch.cuda.synchronize()
+    assert (acc_g.cpu().numpy() >= acc_e.cpu().numpy()).all()
