@@ -199,7 +199,7 @@ def run_reference_arm(args):
     r = cpu_sample(P, sc, w, h, args.bounces, args.steps, args.warmup, min(2.0, 150.0 / total))
     ms = r["seconds"] / args.steps * 1e3
     frames_full = r["pixels"] / float(w * h)
-    line = {"impl": "reference", "metric": "Mrays/s @1080p 1spp indoor", "value": r["mrays"], "unit": "Mrays/s",
+    line = {"impl": "reference", "metric": "Mrays/s @1080p 1spp, README indoor scene", "value": r["mrays"], "unit": "Mrays/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "frames_per_s": frames_full / r["seconds"],
@@ -292,7 +292,8 @@ def run_ours(args):
     barrier()
     t_wall1 = time.time()
     clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
-    ms_frames = sum(a.elapsed_time(b) for a, b in ev)
+    per_frame = sorted(a.elapsed_time(b) for a, b in ev)
+    ms_frames = sum(per_frame)
     ms_gather = g0.elapsed_time(g1)
     ms_total = ms_frames + ms_gather
     c = core.counters()
@@ -367,12 +368,14 @@ def run_ours(args):
             gpu_base = reference_kernel_on_gpu(sc, w, h, args.bounces, K, W)
 
     if rank == 0:
-        line = {"metric": "Mrays/s @1080p 1spp indoor", "value": value, "unit": "Mrays/s", "n_gpus": world,
+        line = {"metric": "Mrays/s @1080p 1spp, README indoor scene", "value": value, "unit": "Mrays/s", "n_gpus": world,
                 "steps": K, "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "frames_per_s": K / (ms_total * 1e-3), "segments_per_step": segments / K,
                 "traced_per_step": traced / K, "ms_per_step_steady_no_flush": ms_steady,
                 "ms_gather_once": ms_gather,
+                "ms_per_frame_rank0": {"min": per_frame[0], "median": per_frame[len(per_frame) // 2],
+                                       "max": per_frame[-1]},
                 "config": config_dict(args, w, h, sc, "512 MB memset between timed frames (outside the per-frame "
                                                      "event pairs); steady-state figure without flush alongside"),
                 "clocks": clocks,

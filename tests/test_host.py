@@ -402,3 +402,37 @@ def test_ppm_and_accumulator_files(tmp_path):
     open(a, "wb").write(b"nope")
     with pytest.raises(P.core.PtcError):
         P.core.accum_load(a)
+
+
+def _run_bench(*argv, env=None):
+    return subprocess.run([sys.executable, os.path.join(REPO, "bench.py"), *argv], capture_output=True, text=True,
+                          env=dict(os.environ, **(env or {})), timeout=300)
+
+
+def test_bench_reference_arm_contract():
+    """`bench.py --impl reference`: the reference's own code (oracle/_ref) or the oracle port on
+    host cores, one JSON line with the contract's keys; ranks other than 0 print nothing."""
+    r = _run_bench("--impl", "reference", "--steps", "1", "--warmup", "1", "--width", "64", "--height", "36")
+    assert r.returncode == 0, r.stderr
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = __import__("json").loads(lines[0])
+    assert d["impl"] == "reference" and d["unit"] == "Mrays/s" and d["higher_is_better"] is True
+    assert d["value"] > 0 and d["steps"] == 1 and d["warmup"] == 1 and d["vs_baseline"] is None
+    assert d["cpu_baseline"]["kind"] in ("reference", "port") and d["cpu_baseline"]["cores"] >= 1
+    assert d["cpu_baseline"]["value"] == d["value"] == d["e2e"]["value"]
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
+    assert d["gpu_launches"] == 0 and "workload" in d["config"]
+    r = _run_bench("--impl", "reference", "--steps", "1", "--warmup", "0", "--width", "64", "--height", "36",
+                   env={"RANK": "1", "WORLD_SIZE": "2"})
+    assert r.returncode == 0 and not r.stdout.strip()
+
+
+def test_bench_has_no_cpu_fallback():
+    """Our arm refuses to run without a CUDA device instead of timing something else."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    r = _run_bench("--steps", "1", "--warmup", "0")
+    assert r.returncode != 0 and "no CPU fallback" in (r.stderr + r.stdout)
+    assert not [l for l in r.stdout.splitlines() if l.startswith("{")]
