@@ -28,7 +28,9 @@
 extern "C" {
 #endif
 
-#define PTC_ABI_VERSION 2
+/* 3: device-tree upload, cube-cross cubemaps, PPM / accumulator files, read-bandwidth probe;
+ * the structs of version 2 are unchanged. */
+#define PTC_ABI_VERSION 3
 
 typedef enum ptc_status
 {
