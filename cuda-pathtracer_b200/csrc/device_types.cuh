@@ -90,6 +90,8 @@ struct FrameParams
   uint32_t strip_rows;         // interleaved bands: rows per strip ...
   uint32_t strip_stride;       // ... every strip_stride-th strip ...
   uint32_t strip_phase;        // ... starting at strip strip_phase (1, x, 0 = contiguous)
+  uint32_t part_row0;          // the launches of this pipeline generate band-local rows
+  uint32_t part_rows;          // [part_row0, part_row0 + part_rows) only (a frame may run as two halves)
   uint32_t tiles_x;            // ceil(width / kTileW)
   uint32_t hash_seed;          // WangHash(frame_nb), raytrace.cu:321
   int32_t frame_nb;

@@ -57,7 +57,7 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
   __syncthreads();
 
   const uint32_t lane = threadIdx.x & 31u;
-  const uint32_t tiles_y = (fp.band_rows + kTileH - 1) / kTileH;
+  const uint32_t tiles_y = (fp.part_rows + kTileH - 1) / kTileH;
   const uint32_t n_items = FIRST ? fp.tiles_x * tiles_y * 32u : *qin_count;
 
   uint32_t my_segs = 0, my_traced = 0, my_nodes = 0, my_tris = 0;
@@ -78,8 +78,8 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
     if (FIRST) {
       const uint32_t wi = base >> 5;
       x = (wi % fp.tiles_x) * kTileW + (lane & (kTileW - 1));
-      lrow = (wi / fp.tiles_x) * kTileH + (lane / kTileW);
-      valid = x < fp.width && lrow < fp.band_rows;
+      lrow = fp.part_row0 + (wi / fp.tiles_x) * kTileH + (lane / kTileW);
+      valid = x < fp.width && lrow < fp.part_row0 + fp.part_rows;
       if (valid) {
         primary_ray(fp, x, global_row(fp, lrow), rng, P.origin, P.dir);
         P.throughput = mk3(1.0f, 1.0f, 1.0f);

@@ -56,6 +56,11 @@ struct ptc_context
   int32_t split_extend = -1;   // later stages as refilling extend kernel + shade kernel: 1 / 0, -1 = per scene
   uint32_t refill = 12;        // idle lanes of a warp that trigger a refill in k_extend
   uint4* hits = nullptr;       // closest triangle hit per queue slot (split stages)
+  // a frame runs as TWO half-band pipelines on two streams, so that the tail of every stage of
+  // one half (SMs draining while the last warps finish) is filled by the other half's stage
+  int dual = 1;                // extra pipelines (0..3); PTC_DUAL overrides (experiments)
+  cudaStream_t side_stream[3] = { nullptr, nullptr, nullptr };
+  cudaEvent_t ev_fork = nullptr, ev_join[3] = { nullptr, nullptr, nullptr };
   uint64_t launches = 0;
   uint32_t seed = 0;           // the reference's function-static frame counter (raytrace.cu:296)
   // staging for ptc_render_host
@@ -288,56 +293,109 @@ frame_schedule(const ptc_context* ctx, const FrameParams& fp, size_t bvh_bytes, 
   return n;
 }
 
-// Enqueues one frame; accum/out/rad are device pointers.  `ev` (optional) receives one
-// event before the first launch and one after every launch.
+// Queues, hit records and counters one pipeline of launches works on.
+struct Lane
+{
+  RayQueue q[2];
+  uint4* hits;
+  uint32_t* counts;
+};
+
+// Enqueues the launches that render band-local rows [fp.part_row0, +fp.part_rows) of a frame.
+// `ev` (optional) receives one event before the first launch and one after every launch.
 int
-enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp, float* accum,
-              uint32_t* out, float* rad, cudaStream_t s, bool stats = false, cudaEvent_t* ev = nullptr)
+enqueue_part(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp, const FrameOut& fo,
+             cudaStream_t s, const Lane& L, bool stats, cudaEvent_t* ev)
 {
   const SceneDev& sc = ctx->scenes[a->scene_id];
   const CubeDev& cm = ctx->cubemaps[a->cubemap_id];
-  const uint32_t n = fp.band_rows * fp.width;
-  int rc = ensure_capacity(ctx, n);
-  if (rc)
-    return rc;
-  FrameOut fo{ accum, out, rad };
   Step steps[kMaxBounces + 2];
   bool split = false;
   const int n_steps = frame_schedule(ctx, fp, scene_bvh_bytes(ctx, a->scene_id), steps, &split);
-  CUDA_TRY(ctx, cudaMemsetAsync(ctx->counts, 0, sizeof(uint32_t) * kCountSlots, s));
+  CUDA_TRY(ctx, cudaMemsetAsync(L.counts, 0, sizeof(uint32_t) * kCountSlots, s));
   int n_ev = 0;
   if (ev)
     CUDA_TRY(ctx, cudaEventRecord(ev[0], s));
-  const uint32_t tiles = fp.tiles_x * ((fp.band_rows + kTileH - 1) / kTileH);
+  const uint32_t tiles = fp.tiles_x * ((fp.part_rows + kTileH - 1) / kTileH);
   for (int k = 0; k < n_steps; ++k) {
     const Step& st = steps[k];
     uint32_t grid;
     const uint4* hits = nullptr;
-    uint32_t* work = ctx->counts + kMaxBounces + 2 + 2 * k;
+    uint32_t* work = L.counts + kMaxBounces + 2 + 2 * k;
     if (st.first) {
       const uint32_t want = (tiles + kBlock / 32 - 1) / (kBlock / 32);
       const uint32_t cap = (uint32_t)sc.grid_first[stats];
       grid = want < cap ? want : cap;
     } else if (split) {
-      launch_extend(stats, (uint32_t)sc.grid_extend[stats], sc.d, ctx->queue[k & 1], ctx->counts + k,
-                    ctx->hits, work + 1, ctx->ctr, ctx->refill, st.bounce0 + 1 >= fp.max_bounces,
-                    sc.stack_cap, s);
+      launch_extend(stats, (uint32_t)sc.grid_extend[stats], sc.d, L.q[k & 1], L.counts + k, L.hits, work + 1,
+                    ctx->ctr, ctx->refill, st.bounce0 + 1 >= fp.max_bounces, sc.stack_cap, s);
       ctx->launches++;
       if (ev)
         CUDA_TRY(ctx, cudaEventRecord(ev[++n_ev], s));
-      hits = ctx->hits;
+      hits = L.hits;
       grid = (uint32_t)sc.grid_shade[stats];
     } else {
       grid = (uint32_t)sc.grid_next[stats];
     }
-    launch_path(st.first, stats, grid, fp, sc.d, cm.tex, ctx->queue[k & 1], hits, ctx->counts + k,
-                ctx->queue[(k + 1) & 1], ctx->counts + k + 1, fo, ctx->ctr, work, st.bounce0, st.n_iters,
-                sc.stack_cap, s);
+    launch_path(st.first, stats, grid, fp, sc.d, cm.tex, L.q[k & 1], hits, L.counts + k, L.q[(k + 1) & 1],
+                L.counts + k + 1, fo, ctx->ctr, work, st.bounce0, st.n_iters, sc.stack_cap, s);
     ctx->launches++;
     if (ev)
       CUDA_TRY(ctx, cudaEventRecord(ev[++n_ev], s));
   }
   CUDA_TRY(ctx, cudaGetLastError());
+  return 0;
+}
+
+// Enqueues one frame; accum/out/rad are device pointers.  Profiling calls (stats / ev) run
+// the frame as one pipeline; otherwise a frame of at least 256 K pixels runs as two halves
+// (whole 16-row strips) on the caller's stream and an internal one, joined before returning
+// to the caller's stream order.
+int
+enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp_in, float* accum,
+              uint32_t* out, float* rad, cudaStream_t s, bool stats = false, cudaEvent_t* ev = nullptr)
+{
+  FrameParams fp = fp_in;
+  const uint32_t n = fp.band_rows * fp.width;
+  int rc = ensure_capacity(ctx, n);
+  if (rc)
+    return rc;
+  const FrameOut fo{ accum, out, rad };
+  Lane A{ { ctx->queue[0], ctx->queue[1] }, ctx->hits, ctx->counts };
+  fp.part_row0 = 0;
+  fp.part_rows = fp.band_rows;
+  int parts = ctx->dual && !stats && !ev && fp.is_static && n >= (1u << 18) ? ctx->dual + 1 : 1;
+  const uint32_t strips = (fp.band_rows + 15u) / 16u;
+  if ((uint32_t)parts > strips)
+    parts = (int)strips;
+  if (parts <= 1)
+    return enqueue_part(ctx, a, fp, fo, s, A, stats, ev);
+
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev_fork, s));
+  uint32_t row0 = 0;
+  for (int i = 0; i < parts; ++i) {
+    const uint32_t s0 = (uint32_t)((uint64_t)strips * i / parts), s1 = (uint32_t)((uint64_t)strips * (i + 1) / parts);
+    const uint32_t rows = (i == parts - 1 ? fp.band_rows : s1 * 16u) - s0 * 16u;
+    const size_t off = (size_t)row0 * fp.width; // queue slots of the parts before this one
+    Lane L = A;
+    for (RayQueue& q : L.q)
+      q.o += off, q.d += off, q.thr += off, q.acc += off;
+    L.hits += off;
+    L.counts += (size_t)kCountSlots * i;
+    FrameParams f = fp;
+    f.part_row0 = row0;
+    f.part_rows = rows;
+    cudaStream_t st = i == 0 ? s : ctx->side_stream[i - 1];
+    if (i)
+      CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->ev_fork, 0));
+    if ((rc = enqueue_part(ctx, a, f, fo, st, L, false, nullptr)))
+      return rc;
+    if (i) {
+      CUDA_TRY(ctx, cudaEventRecord(ctx->ev_join[i - 1], st));
+      CUDA_TRY(ctx, cudaStreamWaitEvent(s, ctx->ev_join[i - 1], 0));
+    }
+    row0 += rows;
+  }
   return 0;
 }
 
@@ -388,12 +446,21 @@ ptc_create(int device, ptc_context** out)
   ctx->device = device;
   DeviceGuard g(device);
   if (cudaMalloc(&ctx->ctr, sizeof(Counters)) != cudaSuccess ||
-      cudaMalloc(&ctx->counts, sizeof(uint32_t) * kCountSlots) != cudaSuccess) {
+      cudaMalloc(&ctx->counts, sizeof(uint32_t) * kCountSlots * 4) != cudaSuccess) {
     delete ctx;
     return PTC_ERR_ALLOC;
   }
   cudaMemset(ctx->ctr, 0, sizeof(Counters));
-  cudaMemset(ctx->counts, 0, sizeof(uint32_t) * kCountSlots);
+  cudaMemset(ctx->counts, 0, sizeof(uint32_t) * kCountSlots * 4);
+  cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming);
+  for (int i = 0; i < 3; ++i) {
+    cudaStreamCreateWithFlags(&ctx->side_stream[i], cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming);
+  }
+  if (const char* e = getenv("PTC_DUAL")) {
+    ctx->dual = atoi(e);
+    ctx->dual = ctx->dual < 0 ? 0 : (ctx->dual > 3 ? 3 : ctx->dual);
+  }
   cudaDeviceGetAttribute(&ctx->n_sms, cudaDevAttrMultiProcessorCount, device);
   *out = ctx;
   return PTC_OK;
@@ -418,6 +485,14 @@ ptc_destroy(ptc_context* ctx)
   }
   cudaFree(ctx->ctr);
   cudaFree(ctx->counts);
+  for (int i = 0; i < 3; ++i) {
+    if (ctx->side_stream[i])
+      cudaStreamDestroy(ctx->side_stream[i]);
+    if (ctx->ev_join[i])
+      cudaEventDestroy(ctx->ev_join[i]);
+  }
+  if (ctx->ev_fork)
+    cudaEventDestroy(ctx->ev_fork);
   cudaFree(ctx->h_accum_dev);
   cudaFree(ctx->h_out_dev);
   cudaFree(ctx->h_rad_dev);

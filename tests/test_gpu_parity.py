@@ -726,3 +726,35 @@ def test_frame_is_cuda_graph_capturable(core):
     graph.replay()  # accumulates a second sample of the same frame on top
     torch.cuda.synchronize()
     assert (acc_g.cpu().numpy() >= acc_e.cpu().numpy()).all()
+
+
+def test_two_half_pipelines_equal_single_pipeline(core, monkeypatch):
+    """Frames of >= 256 K pixels run as two half-band pipelines on two streams (ptcore.cu
+    enqueue_frame) so that stage tails overlap; a context created with PTC_DUAL=0 renders the
+    frame as one pipeline.  Same bits, including an odd height whose halves are ragged."""
+    import torch
+    P = pkg()
+    L = loaded(core, "indoor_tex")
+    monkeypatch.setenv("PTC_DUAL", "0")
+    single = P.Core(0)
+    monkeypatch.delenv("PTC_DUAL")
+    try:
+        L1 = Loaded(single, L.sc)
+        for w, h, b in ((1920, 1080, 3), (1001, 523, 4)):
+            acc_d, out_d, _ = dev_buffers(w, h)
+            acc_s, out_s, _ = dev_buffers(w, h)
+            for k in (1, 2):
+                core.render(L.sid, L.cid, L.sc, w, h, acc_d, out_d, None, bounces=b, frame_nb=k)
+                single.render(L1.sid, L1.cid, L.sc, w, h, acc_s, out_s, None, bounces=b, frame_nb=k)
+            torch.cuda.synchronize()
+            assert (bits(acc_d.cpu().numpy()) == bits(acc_s.cpu().numpy())).all(), (w, h)
+            assert (out_d.cpu().numpy() == out_s.cpu().numpy()).all(), (w, h)
+        # the default context really launched twice as many kernels per frame
+        n0, m0 = core.launch_count(), single.launch_count()
+        acc_d, out_d, _ = dev_buffers(1920, 1080)
+        core.render(L.sid, L.cid, L.sc, 1920, 1080, acc_d, out_d, None, bounces=3, frame_nb=1)
+        single.render(L1.sid, L1.cid, L.sc, 1920, 1080, acc_d, out_d, None, bounces=3, frame_nb=1)
+        torch.cuda.synchronize()
+        assert core.launch_count() - n0 == 2 * (single.launch_count() - m0)
+    finally:
+        single.close()
