@@ -264,13 +264,15 @@ int
 frame_schedule(const ptc_context* ctx, const FrameParams& fp, size_t bvh_bytes, Step* steps, bool* split_out)
 {
   int n = 0;
-  // automatic (measured on B200 with the path kernels at 4 CTAs per SM, tools/sweep2.py):
-  //  * nodes + triangles <= 1 MB (cache-resident; the reference's scenes are 10-30 KB): one
-  //    radiance-loop iteration per launch, each launch traverses AND shades -- 0.646 ms against
-  //    0.672 ms for the split form on the 1080p indoor frame;
-  //  * larger (L2/HBM-resident): two iterations fused into the first stage, then the refilling
-  //    extend kernel + a shade kernel per iteration -- 2.70 ms against 3.42 ms on 10 M triangles.
-  const bool small = bvh_bytes <= (1u << 20);
+  // automatic (measured on B200 with the path kernels at 4 CTAs per SM and two half-frame
+  // pipelines, tools/sweep2.py): ONE radiance-loop iteration per stage everywhere, and
+  //  * nodes + triangles <= 64 KB (L1-resident; the reference's scenes are 10-30 KB): every
+  //    later stage traverses AND shades in one launch -- 0.638 ms against 0.671 ms for the split
+  //    form on the 1080p indoor frame;
+  //  * larger: the refilling extend kernel + a shade kernel per iteration -- already 1.5 % ahead
+  //    at 70 KB (1 164 triangles), 9 % at 1.2 MB, 2.59 ms against 3.09 ms fused on 10 M triangles
+  //    (tools/sweep_split.py).
+  const bool small = bvh_bytes <= (64u << 10);
   const bool split = ctx->split_extend >= 0 ? ctx->split_extend != 0 : !small;
   if (split_out)
     *split_out = split;
@@ -280,7 +282,7 @@ frame_schedule(const ptc_context* ctx, const FrameParams& fp, size_t bvh_bytes, 
   }
   int first = (int)ctx->first_iters;
   if (first == 0)
-    first = small ? 1 : 2;
+    first = 1;
   int b = first < fp.max_bounces ? first : fp.max_bounces;
   steps[n++] = Step{ true, 0, b };
   while (b < fp.max_bounces) {

@@ -298,8 +298,8 @@ int ptc_launch_count(const ptc_context* ctx, uint64_t* out);
  * split_extend: 1 = every later stage is an extend kernel with per-lane refill followed by
  * a shade kernel (one iteration per stage), 0 = fused extend+shade, < 0 keeps.
  * refill: idle lanes per warp that trigger a refill in the extend kernel (0 keeps; default 12).
- * Default: chosen per scene from the size of its BVH (cache-resident: 1 iteration per stage,
- * fused; larger: 2 iterations in the first stage, then split stages);
+ * Default: 1 iteration per stage; later stages fused when nodes + triangles fit 64 KB (L1),
+ * split otherwise;
  * first_iters = 0xFFFFFFFF restores that default for all three.
  * Results do not depend on any of it
  * (tests/test_gpu_parity.py::test_wavefront_granularity_invariance). */
