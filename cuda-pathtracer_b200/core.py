@@ -319,7 +319,7 @@ class Core:
         self._check(self.lib.ptc_profile_frame(self.ctx, C.byref(a), C.c_uint32(repeats), C.byref(pr)),
                     "ptc_profile_frame")
         n = pr.n_launches
-        kinds = ["first", "fused", "extend", "shade"]
+        kinds = ["first", "fused", "extend", "shade", "generate+intersect", "shade+intersect"]
         return {"launch_ms": [pr.launch_ms[i] for i in range(n)],
                 "launch_kind": [kinds[pr.launch_kind[i]] for i in range(n)],
                 "launch_bounce0": [pr.launch_bounce0[i] for i in range(n)],

@@ -43,7 +43,8 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
        const uint4* __restrict__ hits,
        const uint32_t* __restrict__ qin_count, const RayQueue qout, uint32_t* __restrict__ qout_count,
        const FrameOut fo, Counters* __restrict__ ctr, uint32_t* __restrict__ work, const int bounce0,
-       const int n_iters, const int stack_cap)
+       const int n_iters, const int stack_cap, float4* __restrict__ done_q, uint32_t* __restrict__ done_ctl,
+       const int done_mode)
 {
 #ifdef PTC_STAGE_LOCAL_STACK
   LocalStack stack;
@@ -52,8 +53,17 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
   SharedStack stack{ s_stack + threadIdx.x, stack_cap };
 #endif
   __shared__ uint32_t s_rays[16];
+  __shared__ float s_cam[8]; // camera basis of the frame, evaluated once per CTA (FIRST)
   if (threadIdx.x < 16)
     s_rays[threadIdx.x] = 0;
+#ifndef PTC_NO_CAM_HOIST
+  if (FIRST && threadIdx.x == 32) {
+    const CamBasis B = camera_basis(fp);
+    s_cam[0] = B.screen_dist;
+    s_cam[1] = B.cu.x, s_cam[2] = B.cu.y, s_cam[3] = B.cu.z;
+    s_cam[4] = B.cv.x, s_cam[5] = B.cv.y, s_cam[6] = B.cv.z;
+  }
+#endif
   __syncthreads();
 
   const uint32_t lane = threadIdx.x & 31u;
@@ -81,7 +91,15 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
       lrow = fp.part_row0 + (wi / fp.tiles_x) * kTileH + (lane / kTileW);
       valid = x < fp.width && lrow < fp.part_row0 + fp.part_rows;
       if (valid) {
+#ifndef PTC_NO_CAM_HOIST
+        CamBasis B;
+        B.screen_dist = s_cam[0];
+        B.cu = mk3(s_cam[1], s_cam[2], s_cam[3]);
+        B.cv = mk3(s_cam[4], s_cam[5], s_cam[6]);
+        primary_ray(fp, B, x, global_row(fp, lrow), rng, P.origin, P.dir);
+#else
         primary_ray(fp, x, global_row(fp, lrow), rng, P.origin, P.dir);
+#endif
         P.throughput = mk3(1.0f, 1.0f, 1.0f);
         P.acc = mk3(0.0f, 0.0f, 0.0f);
         P.spec_carry = 0.0f; // IntersectionData zero-initialised at path start (Q3)
@@ -161,9 +179,26 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
       }
     }
 
-    // finished paths: accumulate + tonemap + RGBA8 in place
-    if (valid && done)
+    // finished paths: accumulate + tonemap + RGBA8 -- in place in the frame's LAST stage, where every
+    // path of the warp finishes together.  In an earlier stage only some lanes of a warp finish (on the
+    // indoor view 44 % of the paths leave through a window at their second segment), and the ~400
+    // instructions of the epilogue (three powf, six IEEE divisions) would run for them alone: those
+    // pixels are parked as (radiance, pixel) and the last stage runs their epilogue 32 at a time.
+    const bool fin = valid && done;
+    if (done_mode & kDoneDefer) {
+      const uint32_t fm = __ballot_sync(0xFFFFFFFFu, fin);
+      if (fm) {
+        uint32_t slot = 0;
+        const uint32_t leader = __ffs(fm) - 1u;
+        if (lane == leader)
+          slot = atomicAdd(done_ctl, (uint32_t)__popc(fm));
+        slot = __shfl_sync(0xFFFFFFFFu, slot, leader) + __popc(fm & ((1u << lane) - 1u));
+        if (fin)
+          __stcs(done_q + slot, make_float4(P.acc.x, P.acc.y, P.acc.z, __uint_as_float(lrow * fp.width + x)));
+      }
+    } else if (fin) {
       epilogue(fp, fo, x, lrow, P.acc);
+    }
 
     // survivors: warp-aggregated append to the next queue
     const bool cont = valid && !done;
@@ -184,6 +219,24 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
     }
   }
 
+  // last stage: the pixels earlier stages parked (their count is final: stream order)
+  if (done_mode & kDoneDrain) {
+    const uint32_t n_done = done_ctl[0];
+    for (;;) {
+      uint32_t base = 0;
+      if (lane == 0)
+        base = atomicAdd(done_ctl + 1, 32u);
+      base = __shfl_sync(0xFFFFFFFFu, base, 0);
+      if (base >= n_done)
+        break;
+      if (base + lane < n_done) {
+        const float4 e = __ldcs(done_q + base + lane);
+        const uint32_t p = __float_as_uint(e.w);
+        epilogue(fp, fo, p % fp.width, p / fp.width, mk3(e.x, e.y, e.z));
+      }
+    }
+  }
+
   // ray counters: one set of atomics per warp / per CTA for the whole launch
   const uint32_t wsegs = warp_sum(my_segs), wtraced = warp_sum(my_traced);
   if (lane == 0 && wtraced) {
@@ -200,6 +253,199 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
   __syncthreads();
   if (threadIdx.x < 16 && s_rays[threadIdx.x])
     atomicAdd(&ctr->rays_per_bounce[threadIdx.x], (unsigned long long)s_rays[threadIdx.x]);
+}
+
+// ---------------------------------------------------------------------------
+// k_wave -- the stage of the SHIFTED schedule: the stage boundary sits between a path's
+// intersection and its shading, not after the shading.
+//
+//   k_wave<FIRST>   generate -> intersect (iteration 0)
+//   k_wave<!FIRST>  load ray + hit of iteration b-1 -> shade it -> intersect the new ray (iteration b)
+//   both            a ray that MISSES is finished at once (environment + the arithmetic tail of the
+//                   reference's loop, shade_step); only rays that HIT something are queued, with
+//                   their hit record, for the next stage
+//
+// Why: with the boundary after the shading (k_path), every stage shades the rays it traced -- hits
+// and misses side by side in a warp.  On the indoor view 44 % of the second segments leave through
+// a window, so the ~600-instruction material/BRDF part ran with 56 % of a warp's lanes.  Here the
+// queue holds hits only: the shading of a stage is fully populated, and the misses never occupy a
+// queue slot.  The last iteration (any-hit query, lights and environment only) ends in the stage
+// that traced it.  Same arithmetic per path, so the same bits as k_path.
+// ---------------------------------------------------------------------------
+template <bool FIRST, bool STATS>
+__global__ void __launch_bounds__(kBlock, PTC_PATH_BLOCKS)
+k_wave(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, const RayQueue qin,
+       const uint4* __restrict__ hin, const uint32_t* __restrict__ qin_count, const RayQueue qout,
+       uint4* __restrict__ hout, uint32_t* __restrict__ qout_count, const FrameOut fo,
+       Counters* __restrict__ ctr, uint32_t* __restrict__ work, const int b, const int stack_cap,
+       float4* __restrict__ done_q, uint32_t* __restrict__ done_ctl, const int done_mode)
+{
+  extern __shared__ uint2 s_stack[]; // stack_cap entries x kBlock threads
+  SharedStack stack{ s_stack + threadIdx.x, stack_cap };
+  __shared__ uint32_t s_nrays;
+  __shared__ float s_cam[8];
+  if (threadIdx.x == 0)
+    s_nrays = 0;
+  if (FIRST && threadIdx.x == 32) {
+    const CamBasis B = camera_basis(fp);
+    s_cam[0] = B.screen_dist;
+    s_cam[1] = B.cu.x, s_cam[2] = B.cu.y, s_cam[3] = B.cu.z;
+    s_cam[4] = B.cv.x, s_cam[5] = B.cv.y, s_cam[6] = B.cv.z;
+  }
+  __syncthreads();
+
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t tiles_y = (fp.part_rows + kTileH - 1) / kTileH;
+  const uint32_t n_items = FIRST ? fp.tiles_x * tiles_y * 32u : *qin_count;
+  const bool last = b + 1 >= fp.max_bounces; // nothing after this iteration: any-hit query
+
+  uint32_t my_segs = 0, my_traced = 0, my_nodes = 0, my_tris = 0;
+
+  for (;;) {
+    uint32_t base = 0;
+    if (lane == 0)
+      base = atomicAdd(work, 32u);
+    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+    if (base >= n_items)
+      break;
+    const uint32_t i = base + lane;
+    bool valid;
+    uint32_t x = 0, lrow = 0;
+    Path P;
+    Rng rng;
+    bool done;
+    if (FIRST) {
+      const uint32_t wi = base >> 5;
+      x = (wi % fp.tiles_x) * kTileW + (lane & (kTileW - 1));
+      lrow = fp.part_row0 + (wi / fp.tiles_x) * kTileH + (lane / kTileW);
+      valid = x < fp.width && lrow < fp.part_row0 + fp.part_rows;
+      if (valid) {
+        CamBasis B;
+        B.screen_dist = s_cam[0];
+        B.cu = mk3(s_cam[1], s_cam[2], s_cam[3]);
+        B.cv = mk3(s_cam[4], s_cam[5], s_cam[6]);
+        primary_ray(fp, B, x, global_row(fp, lrow), rng, P.origin, P.dir);
+        P.throughput = mk3(1.0f, 1.0f, 1.0f);
+        P.acc = mk3(0.0f, 0.0f, 0.0f);
+        P.spec_carry = 0.0f; // IntersectionData zero-initialised at path start (Q3)
+        P.draws = 2;
+      }
+      done = !valid;
+    } else {
+      valid = i < n_items;
+      done = true;
+      if (valid) {
+        const float4 o4 = __ldcs(qin.o + i), d4 = __ldcs(qin.d + i), t4 = __ldcs(qin.thr + i), a4 = __ldcs(qin.acc + i);
+        const uint4 h = __ldcs(hin + i);
+        P.origin = mk3(o4.x, o4.y, o4.z);
+        P.dir = mk3(d4.x, d4.y, d4.z);
+        P.throughput = mk3(t4.x, t4.y, t4.z);
+        P.acc = mk3(a4.x, a4.y, a4.z);
+        P.spec_carry = o4.w;
+        P.draws = __float_as_uint(d4.w);
+        const uint32_t p = __float_as_uint(t4.w);
+        x = p % fp.width;
+        lrow = p / fp.width;
+        rng_init(rng, fp.hash_seed + reference_tid(x, global_row(fp, lrow), fp.width));
+        rng_skip(rng, P.draws);
+        // iteration b-1: every queued ray hit a face or a light
+        uint32_t segs;
+        done = shade_step(fp, sc, cube, P, rng, __uint_as_float(h.x), h.y, __uint_as_float(h.z),
+                          __uint_as_float(h.w), b - 1, segs);
+        my_segs += segs;
+      }
+    }
+
+    // iteration b: intersect; a miss (and the whole last iteration) is finished here
+    const uint32_t active = __ballot_sync(0xFFFFFFFFu, !done);
+    if (lane == 0 && active)
+      atomicAdd(&s_nrays, (uint32_t)__popc(active));
+    float t = 0.f, u = 0.f, v = 0.f;
+    uint32_t id = 0xFFFFFFFFu;
+    if (!done) {
+      my_traced++;
+      if (last)
+        last_hit<STATS>(sc, stack, P.origin, P.dir, t, id, my_nodes, my_tris);
+      else
+        closest_hit<STATS>(sc, stack, P.origin, P.dir, t, id, u, v, my_nodes, my_tris);
+      if (last && id < sc.n_faces) {
+        done = true; // a triangle in front on the last iteration adds no radiance
+        my_segs++;
+      } else if (last || id == 0xFFFFFFFFu) {
+        uint32_t segs;
+        done = shade_step(fp, sc, cube, P, rng, t, id, u, v, b, segs); // always finishes the path
+        my_segs += segs;
+      }
+    }
+
+    const bool fin = valid && done;
+    if (done_mode & kDoneDefer) {
+      const uint32_t fm = __ballot_sync(0xFFFFFFFFu, fin);
+      if (fm) {
+        uint32_t slot = 0;
+        const uint32_t leader = __ffs(fm) - 1u;
+        if (lane == leader)
+          slot = atomicAdd(done_ctl, (uint32_t)__popc(fm));
+        slot = __shfl_sync(0xFFFFFFFFu, slot, leader) + __popc(fm & ((1u << lane) - 1u));
+        if (fin)
+          __stcs(done_q + slot, make_float4(P.acc.x, P.acc.y, P.acc.z, __uint_as_float(lrow * fp.width + x)));
+      }
+    } else if (fin) {
+      epilogue(fp, fo, x, lrow, P.acc);
+    }
+
+    // rays that hit: warp-aggregated append of ray + hit record to the next stage's queue
+    const bool cont = valid && !done;
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, cont);
+    if (mask) {
+      uint32_t slot = 0;
+      const uint32_t leader = __ffs(mask) - 1u;
+      if (lane == leader)
+        slot = atomicAdd(qout_count, (uint32_t)__popc(mask));
+      slot = __shfl_sync(0xFFFFFFFFu, slot, leader) + __popc(mask & ((1u << lane) - 1u));
+      if (cont) {
+        __stcs(qout.o + slot, make_float4(P.origin.x, P.origin.y, P.origin.z, P.spec_carry));
+        __stcs(qout.d + slot, make_float4(P.dir.x, P.dir.y, P.dir.z, __uint_as_float(P.draws)));
+        __stcs(qout.thr + slot, make_float4(P.throughput.x, P.throughput.y, P.throughput.z,
+                                            __uint_as_float(lrow * fp.width + x)));
+        __stcs(qout.acc + slot, make_float4(P.acc.x, P.acc.y, P.acc.z, 0.0f));
+        __stcs(hout + slot, make_uint4(__float_as_uint(t), id, __float_as_uint(u), __float_as_uint(v)));
+      }
+    }
+  }
+
+  if (done_mode & kDoneDrain) {
+    const uint32_t n_done = done_ctl[0];
+    for (;;) {
+      uint32_t base = 0;
+      if (lane == 0)
+        base = atomicAdd(done_ctl + 1, 32u);
+      base = __shfl_sync(0xFFFFFFFFu, base, 0);
+      if (base >= n_done)
+        break;
+      if (base + lane < n_done) {
+        const float4 e = __ldcs(done_q + base + lane);
+        const uint32_t p = __float_as_uint(e.w);
+        epilogue(fp, fo, p % fp.width, p / fp.width, mk3(e.x, e.y, e.z));
+      }
+    }
+  }
+
+  const uint32_t wsegs = warp_sum(my_segs), wtraced = warp_sum(my_traced);
+  if (lane == 0 && (wsegs | wtraced)) {
+    atomicAdd(&ctr->segments, (unsigned long long)wsegs);
+    atomicAdd(&ctr->traced, (unsigned long long)wtraced);
+  }
+  if (STATS) {
+    const uint32_t wn = warp_sum(my_nodes), wt = warp_sum(my_tris);
+    if (lane == 0 && (wn | wt)) {
+      atomicAdd(&ctr->nodes_visited, (unsigned long long)wn);
+      atomicAdd(&ctr->tris_tested, (unsigned long long)wt);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0 && s_nrays)
+    atomicAdd(&ctr->rays_per_bounce[b < 16 ? b : 15], (unsigned long long)s_nrays);
 }
 
 // ---------------------------------------------------------------------------
@@ -258,7 +504,7 @@ k_extend(const DScene sc, const RayQueue qin, const uint32_t* __restrict__ qin_c
       if (!__any_sync(0xFFFFFFFFu, have))
         break;
     }
-    if (have && trav_step<STATS>(sc, T, stack, my_nodes, my_tris)) {
+    if (have && trav_step<STATS, decltype(stack), true>(sc, T, stack, my_nodes, my_tris)) {
       __stcs(hits + slot, make_uint4(__float_as_uint(T.best_t), T.best_id, __float_as_uint(T.best_u),
                                      __float_as_uint(T.best_v)));
       have = false;
@@ -387,7 +633,7 @@ max_optin_smem()
   int dev = 0, v = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-  return v - 64; // the static s_rays[16] of k_path shares the budget
+  return v - 128; // the static s_rays[16] + s_cam[8] of k_path share the budget
 }
 
 template <bool FIRST, bool STATS, bool HITS>
@@ -415,6 +661,26 @@ path_kernel_blocks_per_sm(bool first, bool stats, bool pretraced, int stack_cap)
   return stats ? occ<false, true, false>(smem) : occ<false, false, false>(smem);
 }
 
+template <bool FIRST, bool STATS>
+static int
+occ_wave(size_t smem)
+{
+  int n = 0;
+  cudaFuncSetAttribute(k_wave<FIRST, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin_smem());
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_wave<FIRST, STATS>, kBlock, smem) != cudaSuccess)
+    n = 0;
+  return n;
+}
+
+int
+wave_kernel_blocks_per_sm(bool first, bool stats, int stack_cap)
+{
+  const size_t smem = stack_smem_bytes(stack_cap);
+  if (first)
+    return stats ? occ_wave<true, true>(smem) : occ_wave<true, false>(smem);
+  return stats ? occ_wave<false, true>(smem) : occ_wave<false, false>(smem);
+}
+
 int
 extend_kernel_blocks_per_sm(bool stats, int stack_cap)
 {
@@ -433,13 +699,14 @@ extend_kernel_blocks_per_sm(bool stats, int stack_cap)
 
 #define PTC_LAUNCH_PATH(F, S, H, SMEM)                                                             \
   k_path<F, S, H><<<grid, kBlock, SMEM, s>>>(fp, sc, cube, qin, hits, qin_count, qout, qout_count, fo, ctr, \
-                                             work, bounce0, n_iters, stack_cap)
+                                             work, bounce0, n_iters, stack_cap, done_q, done_ctl, done_mode)
 
 void
 launch_path(bool first, bool stats, uint32_t grid, const FrameParams& fp, const DScene& sc,
             cudaTextureObject_t cube, const RayQueue& qin, const uint4* hits, const uint32_t* qin_count,
             const RayQueue& qout, uint32_t* qout_count, const FrameOut& fo, Counters* ctr,
-            uint32_t* work, int bounce0, int n_iters, int stack_cap, cudaStream_t s)
+            uint32_t* work, int bounce0, int n_iters, int stack_cap, float4* done_q, uint32_t* done_ctl,
+            int done_mode, cudaStream_t s)
 {
   if (!grid)
     return;
@@ -459,6 +726,33 @@ launch_path(bool first, bool stats, uint32_t grid, const FrameParams& fp, const 
       PTC_LAUNCH_PATH(false, true, false, smem);
     else
       PTC_LAUNCH_PATH(false, false, false, smem);
+  }
+}
+
+#define PTC_LAUNCH_WAVE(F, S)                                                                      \
+  k_wave<F, S><<<grid, kBlock, smem, s>>>(fp, sc, cube, qin, hin, qin_count, qout, hout, qout_count, fo, ctr, \
+                                          work, bounce, stack_cap, done_q, done_ctl, done_mode)
+
+void
+launch_wave(bool first, bool stats, uint32_t grid, const FrameParams& fp, const DScene& sc,
+            cudaTextureObject_t cube, const RayQueue& qin, const uint4* hin, const uint32_t* qin_count,
+            const RayQueue& qout, uint4* hout, uint32_t* qout_count, const FrameOut& fo, Counters* ctr,
+            uint32_t* work, int bounce, int stack_cap, float4* done_q, uint32_t* done_ctl, int done_mode,
+            cudaStream_t s)
+{
+  if (!grid)
+    return;
+  const size_t smem = stack_smem_bytes(stack_cap);
+  if (first) {
+    if (stats)
+      PTC_LAUNCH_WAVE(true, true);
+    else
+      PTC_LAUNCH_WAVE(true, false);
+  } else {
+    if (stats)
+      PTC_LAUNCH_WAVE(false, true);
+    else
+      PTC_LAUNCH_WAVE(false, false);
   }
 }
 

@@ -19,11 +19,25 @@ int extend_kernel_blocks_per_sm(bool stats, int stack_cap);
 // `qin`; survivors are appended to `qout` / `qout_count`.  `work` is a zeroed counter the
 // persistent warps pull their work items from.  hits != null: the triangle hits of `qin`
 // were already found by launch_extend (n_iters must be 1).
+// done_mode: kDoneDefer = paths that finish in this stage are parked in done_q (count in
+// done_ctl[0]) instead of running the per-pixel epilogue; kDoneDrain = this is the frame's last
+// stage, which also runs the epilogue of every parked pixel (done_ctl[1] = its work counter).
+constexpr int kDoneDefer = 1, kDoneDrain = 2;
 void launch_path(bool first, bool stats, uint32_t grid, const FrameParams& fp, const DScene& sc,
                  cudaTextureObject_t cube, const RayQueue& qin, const uint4* hits,
                  const uint32_t* qin_count, const RayQueue& qout, uint32_t* qout_count,
                  const FrameOut& fo, Counters* ctr, uint32_t* work, int bounce0, int n_iters,
-                 int stack_cap, cudaStream_t s);
+                 int stack_cap, float4* done_q, uint32_t* done_ctl, int done_mode, cudaStream_t s);
+
+// One stage of the SHIFTED schedule (k_wave): shade iteration bounce-1 from the queued hit records
+// `hin` (not for the first stage), intersect iteration `bounce`, finish the rays that miss, queue
+// the rays that hit with their hit records in `qout` / `hout`.
+int wave_kernel_blocks_per_sm(bool first, bool stats, int stack_cap);
+void launch_wave(bool first, bool stats, uint32_t grid, const FrameParams& fp, const DScene& sc,
+                 cudaTextureObject_t cube, const RayQueue& qin, const uint4* hin,
+                 const uint32_t* qin_count, const RayQueue& qout, uint4* hout, uint32_t* qout_count,
+                 const FrameOut& fo, Counters* ctr, uint32_t* work, int bounce, int stack_cap,
+                 float4* done_q, uint32_t* done_ctl, int done_mode, cudaStream_t s);
 
 // Closest triangle hit of every ray of `qin` -> hits[slot] = (t, face id | ~0, u, v), with
 // per-lane refill once `refill` lanes of a warp are idle.  last: the rays belong to the last

@@ -31,6 +31,7 @@ struct SceneDev
   // persistent grids that follow from it: resident CTAs per SM x SMs, [0] plain / [1] statistics
   int stack_cap = 0;
   int grid_first[2] = { 0, 0 }, grid_next[2] = { 0, 0 }, grid_shade[2] = { 0, 0 }, grid_extend[2] = { 0, 0 };
+  int grid_wave_first[2] = { 0, 0 }, grid_wave_next[2] = { 0, 0 }; // shifted schedule (k_wave)
 };
 
 struct CubeDev
@@ -53,9 +54,13 @@ struct ptc_context
   int n_sms = 148;
   // persistent grids, [stats]: first stage, fused later stage, shade-after-extend, extend
   uint32_t first_iters = 0, next_iters = 1; // first_iters 0 = per scene (frame_schedule) // wavefront granularity (ptc_set_wavefront)
-  int32_t split_extend = -1;   // later stages as refilling extend kernel + shade kernel: 1 / 0, -1 = per scene
+  int32_t split_extend = -1;   // form of the stages: 0 fused, 1 refilling extend kernel + shade kernel, 2 shifted (k_wave), -1 = per scene
+  int wave_small = 0;          // automatic choice for L1-resident scenes: 1 shifted, 0 fused; PTC_WAVE overrides (experiments)
   uint32_t refill = 12;        // idle lanes of a warp that trigger a refill in k_extend
-  uint4* hits = nullptr;       // closest triangle hit per queue slot (split stages)
+  uint4* hits = nullptr;       // closest triangle hit per queue slot (split stages; shifted stages: even queue)
+  uint4* hits2 = nullptr;      // shifted stages: hit records of the odd queue
+  float4* done = nullptr;      // (radiance, pixel) of paths that finished before the last stage
+  int defer = 1;               // epilogue of those pixels runs in the last stage; PTC_DEFER=0: in place
   // a frame runs as TWO half-band pipelines on two streams, so that the tail of every stage of
   // one half (SMs draining while the last warps finish) is filled by the other half's stage
   int dual = 1;                // extra pipelines (0..3); PTC_DUAL overrides (experiments)
@@ -80,7 +85,9 @@ struct ptc_context
 namespace {
 
 constexpr int kMaxBounces = 64;
-constexpr int kCountSlots = 3 * (kMaxBounces + 2); // queue counters, then 2 work counters per step
+// queue counters, then 2 work counters per step; the last two slots: parked-pixel count and the
+// work counter of their drain (kernels.cuh, kDoneDefer / kDoneDrain)
+constexpr int kCountSlots = 3 * (kMaxBounces + 2);
 
 int
 fail(ptc_context* ctx, int code, const std::string& msg)
@@ -140,7 +147,11 @@ free_state(ptc_context* ctx)
     q = RayQueue{};
   }
   cudaFree(ctx->hits);
+  cudaFree(ctx->hits2);
+  cudaFree(ctx->done);
   ctx->hits = nullptr;
+  ctx->hits2 = nullptr;
+  ctx->done = nullptr;
   ctx->capacity = 0;
 }
 
@@ -157,6 +168,8 @@ ensure_capacity(ptc_context* ctx, uint32_t n)
     CUDA_TRY(ctx, cudaMalloc(&q.acc, (size_t)n * sizeof(float4)));
   }
   CUDA_TRY(ctx, cudaMalloc(&ctx->hits, (size_t)n * sizeof(uint4)));
+  CUDA_TRY(ctx, cudaMalloc(&ctx->hits2, (size_t)n * sizeof(uint4)));
+  CUDA_TRY(ctx, cudaMalloc(&ctx->done, (size_t)n * sizeof(float4)));
   ctx->capacity = n;
   return 0;
 }
@@ -261,7 +274,8 @@ struct Step
 // The wavefront schedule of a frame: the first stage generates the rays and runs
 // `first_iters` radiance-loop iterations in registers; every later stage runs `next_iters`.
 int
-frame_schedule(const ptc_context* ctx, const FrameParams& fp, size_t bvh_bytes, Step* steps, bool* split_out)
+frame_schedule(const ptc_context* ctx, const FrameParams& fp, size_t bvh_bytes, Step* steps, bool* split_out,
+               bool* wave_out = nullptr)
 {
   int n = 0;
   // automatic (measured on B200 with the path kernels at 4 CTAs per SM and two half-frame
@@ -273,11 +287,21 @@ frame_schedule(const ptc_context* ctx, const FrameParams& fp, size_t bvh_bytes, 
   //    at 70 KB (1 164 triangles), 9 % at 1.2 MB, 2.59 ms against 3.09 ms fused on 10 M triangles
   //    (tools/sweep_split.py).
   const bool small = bvh_bytes <= (64u << 10);
-  const bool split = ctx->split_extend >= 0 ? ctx->split_extend != 0 : !small;
+  const bool split = ctx->split_extend >= 0 ? ctx->split_extend == 1 : !small;
+  // shifted form (k_wave, kernels.cu): stage k intersects iteration k and shades iteration k-1, so
+  // that only rays that hit are queued and shaded -- the L1-resident scenes' default
+  const bool wave = fp.is_static && (ctx->split_extend >= 0 ? ctx->split_extend == 2 : small && ctx->wave_small);
   if (split_out)
     *split_out = split;
+  if (wave_out)
+    *wave_out = wave;
   if (!fp.is_static) {
     steps[n++] = Step{ true, 0, 1 };
+    return n;
+  }
+  if (wave) {
+    for (int b = 0; b < fp.max_bounces; ++b)
+      steps[n++] = Step{ b == 0, b, 1 };
     return n;
   }
   int first = (int)ctx->first_iters;
@@ -300,6 +324,8 @@ struct Lane
 {
   RayQueue q[2];
   uint4* hits;
+  uint4* hits2;
+  float4* done;
   uint32_t* counts;
 };
 
@@ -312,8 +338,8 @@ enqueue_part(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp, 
   const SceneDev& sc = ctx->scenes[a->scene_id];
   const CubeDev& cm = ctx->cubemaps[a->cubemap_id];
   Step steps[kMaxBounces + 2];
-  bool split = false;
-  const int n_steps = frame_schedule(ctx, fp, scene_bvh_bytes(ctx, a->scene_id), steps, &split);
+  bool split = false, wave = false;
+  const int n_steps = frame_schedule(ctx, fp, scene_bvh_bytes(ctx, a->scene_id), steps, &split, &wave);
   CUDA_TRY(ctx, cudaMemsetAsync(L.counts, 0, sizeof(uint32_t) * kCountSlots, s));
   int n_ev = 0;
   if (ev)
@@ -324,6 +350,20 @@ enqueue_part(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp, 
     uint32_t grid;
     const uint4* hits = nullptr;
     uint32_t* work = L.counts + kMaxBounces + 2 + 2 * k;
+    if (wave) {
+      const uint32_t want = (tiles + kBlock / 32 - 1) / (kBlock / 32);
+      const uint32_t cap = (uint32_t)sc.grid_wave_first[stats];
+      grid = st.first ? (want < cap ? want : cap) : (uint32_t)sc.grid_wave_next[stats];
+      const int done_mode = ctx->defer && n_steps > 1 ? (k + 1 < n_steps ? kDoneDefer : kDoneDrain) : 0;
+      uint4* const hb[2] = { L.hits, L.hits2 };
+      launch_wave(st.first, stats, grid, fp, sc.d, cm.tex, L.q[k & 1], hb[k & 1], L.counts + k, L.q[(k + 1) & 1],
+                  hb[(k + 1) & 1], L.counts + k + 1, fo, ctx->ctr, work, st.bounce0, sc.stack_cap, L.done,
+                  L.counts + kCountSlots - 2, done_mode, s);
+      ctx->launches++;
+      if (ev)
+        CUDA_TRY(ctx, cudaEventRecord(ev[++n_ev], s));
+      continue;
+    }
     if (st.first) {
       const uint32_t want = (tiles + kBlock / 32 - 1) / (kBlock / 32);
       const uint32_t cap = (uint32_t)sc.grid_first[stats];
@@ -339,8 +379,14 @@ enqueue_part(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp, 
     } else {
       grid = (uint32_t)sc.grid_next[stats];
     }
+    // every pixel finishes exactly once per frame; in a stage that is not the last, finished pixels
+    // are parked and the last stage runs their epilogue (kernels.cuh)
+    int done_mode = 0;
+    if (ctx->defer && n_steps > 1)
+      done_mode = k + 1 < n_steps ? kDoneDefer : kDoneDrain;
     launch_path(st.first, stats, grid, fp, sc.d, cm.tex, L.q[k & 1], hits, L.counts + k, L.q[(k + 1) & 1],
-                L.counts + k + 1, fo, ctx->ctr, work, st.bounce0, st.n_iters, sc.stack_cap, s);
+                L.counts + k + 1, fo, ctx->ctr, work, st.bounce0, st.n_iters, sc.stack_cap, L.done,
+                L.counts + kCountSlots - 2, done_mode, s);
     ctx->launches++;
     if (ev)
       CUDA_TRY(ctx, cudaEventRecord(ev[++n_ev], s));
@@ -363,7 +409,7 @@ enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp_
   if (rc)
     return rc;
   const FrameOut fo{ accum, out, rad };
-  Lane A{ { ctx->queue[0], ctx->queue[1] }, ctx->hits, ctx->counts };
+  Lane A{ { ctx->queue[0], ctx->queue[1] }, ctx->hits, ctx->hits2, ctx->done, ctx->counts };
   fp.part_row0 = 0;
   fp.part_rows = fp.band_rows;
   int parts = ctx->dual && !stats && !ev && fp.is_static && n >= (1u << 18) ? ctx->dual + 1 : 1;
@@ -383,6 +429,8 @@ enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp_
     for (RayQueue& q : L.q)
       q.o += off, q.d += off, q.thr += off, q.acc += off;
     L.hits += off;
+    L.hits2 += off;
+    L.done += off;
     L.counts += (size_t)kCountSlots * i;
     FrameParams f = fp;
     f.part_row0 = row0;
@@ -459,6 +507,10 @@ ptc_create(int device, ptc_context** out)
     cudaStreamCreateWithFlags(&ctx->side_stream[i], cudaStreamNonBlocking);
     cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming);
   }
+  if (const char* e = getenv("PTC_WAVE"))
+    ctx->wave_small = atoi(e) != 0;
+  if (const char* e = getenv("PTC_DEFER"))
+    ctx->defer = atoi(e) != 0;
   if (const char* e = getenv("PTC_DUAL")) {
     ctx->dual = atoi(e);
     ctx->dual = ctx->dual < 0 ? 0 : (ctx->dual > 3 ? 3 : ctx->dual);
@@ -614,6 +666,8 @@ ptc_upload_scene(ptc_context* ctx, const ptc_scene_desc* desc, int32_t* scene_id
     s.grid_next[st] = ctx->n_sms * path_kernel_blocks_per_sm(false, st != 0, false, s.stack_cap);
     s.grid_shade[st] = ctx->n_sms * path_kernel_blocks_per_sm(false, st != 0, true, s.stack_cap);
     s.grid_extend[st] = ctx->n_sms * extend_kernel_blocks_per_sm(st != 0, s.stack_cap);
+    s.grid_wave_first[st] = ctx->n_sms * wave_kernel_blocks_per_sm(true, st != 0, s.stack_cap);
+    s.grid_wave_next[st] = ctx->n_sms * wave_kernel_blocks_per_sm(false, st != 0, s.stack_cap);
   }
   if (!s.grid_first[0] || !s.grid_next[0] || !s.grid_extend[0] || !s.grid_first[1] || !s.grid_extend[1])
     return fail(ctx, PTC_ERR_INVALID, "traversal stack does not fit in shared memory");
@@ -1076,7 +1130,7 @@ ptc_set_wavefront(ptc_context* ctx, uint32_t first_iters, uint32_t next_iters, i
   if (!ctx)
     return PTC_ERR_INVALID;
   if (split_extend >= 0)
-    ctx->split_extend = split_extend ? 1 : 0;
+    ctx->split_extend = split_extend > 2 ? 2 : split_extend;
   if (refill)
     ctx->refill = refill > 32 ? 32 : refill;
   if (first_iters == 0xFFFFFFFFu) {
@@ -1105,13 +1159,16 @@ ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeat
     return fail(ctx, PTC_ERR_INVALID, "accum is required");
   cudaStream_t s = (cudaStream_t)args->stream;
   Step steps[kMaxBounces + 2];
-  bool split = false;
-  const int n_steps = frame_schedule(ctx, fp, scene_bvh_bytes(ctx, args->scene_id), steps, &split);
-  // the launches of one frame: kind 0 = first stage, 1 = fused later stage, 2 = extend, 3 = shade
+  bool split = false, wave = false;
+  const int n_steps = frame_schedule(ctx, fp, scene_bvh_bytes(ctx, args->scene_id), steps, &split, &wave);
+  // the launches of one frame: kind 0 = first stage, 1 = fused later stage, 2 = extend, 3 = shade,
+  // 4 / 5 = shifted form: generate + intersect / shade + intersect
   struct L { uint32_t kind, bounce0, iters; };
   std::vector<L> launches;
   for (int k = 0; k < n_steps; ++k) {
-    if (steps[k].first)
+    if (wave)
+      launches.push_back({ steps[k].first ? 4u : 5u, (uint32_t)steps[k].bounce0, 1u });
+    else if (steps[k].first)
       launches.push_back({ 0u, 0u, (uint32_t)steps[k].n_iters });
     else if (split) {
       launches.push_back({ 2u, (uint32_t)steps[k].bounce0, 1u });
@@ -1143,7 +1200,7 @@ ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeat
   for (int k = 1; k < n_steps; ++k)
     out->queue_rays += counts[k];
   out->queue_bytes_per_ray = 4 * sizeof(float4);
-  out->hit_bytes_per_ray = split ? (uint32_t)sizeof(uint4) : 0u;
+  out->hit_bytes_per_ray = split || wave ? (uint32_t)sizeof(uint4) : 0u;
   // timed passes
   for (uint32_t r = 0; r < repeats; ++r) {
     rc = enqueue_frame(ctx, args, fp, (float*)args->accum, (uint32_t*)args->out_rgba, nullptr, s, false,

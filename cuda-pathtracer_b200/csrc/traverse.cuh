@@ -74,8 +74,32 @@ reference_tid(uint32_t x, uint32_t y, uint32_t width)
   return ((x >> 4) + (y >> 4) * gx) * 256u + (y & 15u) * 16u + (x & 15u);
 }
 
+// The part of generateRay (intersection.cuh:75-90) that depends on the camera only: screen
+// distance and the screen basis.  The stage kernel evaluates it once per CTA into shared memory
+// (same instructions, so the same bits) instead of once per pixel: a tanf, an IEEE division and
+// two normalisations, about 130 of the 2 100 instructions of a primary path.
+struct CamBasis
+{
+  float screen_dist;
+  float3 cu, cv;
+};
+
+__device__ __forceinline__ CamBasis
+camera_basis(const FrameParams& fp)
+{
+  CamBasis B;
+  const int half_w = (int)(fp.width / 2);
+  const float3 cdir = mk3(fp.cam.dir[0], fp.cam.dir[1], fp.cam.dir[2]);
+  B.screen_dist = half_w / tanf(fp.cam.fov_x * 0.5f);
+  float3 cu = normalize(cross(cdir, mk3(0.0f, -1.0f, 0.0f)));
+  B.cv = normalize(cross(cu, cdir));
+  B.cu = cu * -1.0f;
+  return B;
+}
+
 __device__ __forceinline__ void
-primary_ray(const FrameParams& fp, uint32_t x, uint32_t y, Rng& rng, float3& origin, float3& dir)
+primary_ray(const FrameParams& fp, const CamBasis& B, uint32_t x, uint32_t y, Rng& rng, float3& origin,
+            float3& dir)
 {
   rng_init(rng, fp.hash_seed + reference_tid(x, y, fp.width));
 
@@ -83,10 +107,8 @@ primary_ray(const FrameParams& fp, uint32_t x, uint32_t y, Rng& rng, float3& ori
   const int half_w = (int)(fp.width / 2), half_h = (int)(fp.height / 2);
   const float3 cpos = mk3(fp.cam.position[0], fp.cam.position[1], fp.cam.position[2]);
   const float3 cdir = mk3(fp.cam.dir[0], fp.cam.dir[1], fp.cam.dir[2]);
-  float screen_dist = half_w / tanf(fp.cam.fov_x * 0.5f);
-  float3 cu = normalize(cross(cdir, mk3(0.0f, -1.0f, 0.0f)));
-  float3 cv = normalize(cross(cu, cdir));
-  cu = cu * -1.0f;
+  const float screen_dist = B.screen_dist;
+  const float3 cu = B.cu, cv = B.cv;
   float3 screen_pos =
     cpos + (cdir * screen_dist) + (cu * (float)((int)x - half_w)) + (cv * (float)((int)y - half_h));
   dir = normalize(screen_pos - cpos);
@@ -99,6 +121,12 @@ primary_ray(const FrameParams& fp, uint32_t x, uint32_t y, Rng& rng, float3& ori
   float3 ap = (cosf(random_angle) * cu + sinf(random_angle) * cv) * random_radius;
   dir = normalize(focal_point - ap);
   origin = origin + ap;
+}
+
+__device__ __forceinline__ void
+primary_ray(const FrameParams& fp, uint32_t x, uint32_t y, Rng& rng, float3& origin, float3& dir)
+{
+  primary_ray(fp, camera_basis(fp), x, y, rng, origin, dir);
 }
 
 // Moeller-Trumbore exactly as intersection.cuh:102-135 evaluates it on the device
@@ -158,6 +186,22 @@ __device__ __forceinline__ float
 half_hi(uint32_t w)
 {
   return __high2float(*reinterpret_cast<const __half2*>(&w));
+}
+
+// Packed fp32 pair helpers for fma.rn.f32x2 (sm_100 FFMA2).
+__device__ __forceinline__ uint64_t
+pack2(float lo, float hi)
+{
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void
+fma2(float& r0, float& r1, float q0, float q1, uint64_t a, uint64_t b)
+{
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pack2(q0, q1)), "l"(a), "l"(b));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(r0), "=f"(r1) : "l"(r));
 }
 
 // bit s of an 8-bit mask -> bit 3s (the triangle space of a node gives every slot 3 bits)
@@ -272,7 +316,13 @@ trav_init_any(const DScene& sc, Trav& T, const float3 o, const float3 d)
 // (t, face id) and boxes are only culled when strictly farther than the best hit), so the
 // loop is shaped for SIMT convergence: a leaf's remaining triangles are deferred on the
 // stack instead of being looped over while the other lanes of the warp idle.
-template <bool STATS, typename Stack>
+//
+// F2: the slab tests of two children share one packed fp32 FMA (fma.rn.f32x2 -> FFMA2, new on
+// sm_100): each half is the same round-to-nearest fma as the scalar form, so the hit masks do not
+// change, and the node test issues 24 FFMA2 instead of 48 FFMA.  Measured on B200: -2.5 % frame time
+// on the 10 M-triangle scene (k_extend, 80 registers, no spills); +0.3 % in the fused path kernels,
+// whose 64-register cap turns the register pairs into extra spills -- so only k_extend asks for it.
+template <bool STATS, typename Stack, bool F2 = false>
 __device__ __forceinline__ bool
 trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& n_tris)
 {
@@ -350,7 +400,33 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
     const float bz = (__uint_as_float(n0.z) - T.o.z) * T.idir.z;
 
     uint32_t hit8 = 0;
-#define PTC_CHILD(k, W, H)                                                                       \
+    if (F2) {
+    // two children per FMA (see above); the kernels are bound by instruction issue, not by the
+    // FMA pipe (ncu: issue 65-73 %, FMA pipe 26-28 %)
+    const uint64_t ax2 = pack2(ax, ax), ay2 = pack2(ay, ay), az2 = pack2(az, az);
+    const uint64_t bx2 = pack2(bx, bx), by2 = pack2(by, by), bz2 = pack2(bz, bz);
+#define PTC_PAIR(k, W)                                                                           \
+  {                                                                                              \
+    float tnx0, tnx1, tfx0, tfx1, tny0, tny1, tfy0, tfy1, tnz0, tnz1, tfz0, tfz1;                \
+    fma2(tnx0, tnx1, half_lo(NX.W), half_hi(NX.W), ax2, bx2);                                    \
+    fma2(tfx0, tfx1, half_lo(FX.W), half_hi(FX.W), ax2, bx2);                                    \
+    fma2(tny0, tny1, half_lo(NY.W), half_hi(NY.W), ay2, by2);                                    \
+    fma2(tfy0, tfy1, half_lo(FY.W), half_hi(FY.W), ay2, by2);                                    \
+    fma2(tnz0, tnz1, half_lo(NZ.W), half_hi(NZ.W), az2, bz2);                                    \
+    fma2(tfz0, tfz1, half_lo(FZ.W), half_hi(FZ.W), az2, bz2);                                    \
+    const float tmin0 = fmaxf(fmaxf(tnx0, tny0), fmaxf(tnz0, 0.0f));                             \
+    const float tmax0 = fminf(fminf(tfx0, tfy0), fminf(tfz0, T.best_t));                         \
+    const float tmin1 = fmaxf(fmaxf(tnx1, tny1), fmaxf(tnz1, 0.0f));                             \
+    const float tmax1 = fminf(fminf(tfx1, tfy1), fminf(tfz1, T.best_t));                         \
+    if (tmin0 <= tmax0)                                                                          \
+      hit8 |= 1u << (k);                                                                         \
+    if (tmin1 <= tmax1)                                                                          \
+      hit8 |= 2u << (k);                                                                         \
+  }
+    PTC_PAIR(0, x) PTC_PAIR(2, y) PTC_PAIR(4, z) PTC_PAIR(6, w)
+#undef PTC_PAIR
+    } else {
+#define PTC_CHILD(k, W, H)                                                                     \
   {                                                                                              \
     const float tnx = fmaf(H(NX.W), ax, bx), tfx = fmaf(H(FX.W), ax, bx);                        \
     const float tny = fmaf(H(NY.W), ay, by), tfy = fmaf(H(FY.W), ay, by);                        \
@@ -363,6 +439,7 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
     PTC_CHILD(0, x, half_lo) PTC_CHILD(1, x, half_hi) PTC_CHILD(2, y, half_lo) PTC_CHILD(3, y, half_hi)
     PTC_CHILD(4, z, half_lo) PTC_CHILD(5, z, half_hi) PTC_CHILD(6, w, half_lo) PTC_CHILD(7, w, half_hi)
 #undef PTC_CHILD
+    }
 
     // internal children: bit s -> 24 + (s ^ oct_inv), i.e. far-to-near from the top bit down
     const uint32_t imask = n0.w >> 24;
