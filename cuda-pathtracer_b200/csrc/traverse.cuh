@@ -309,7 +309,11 @@ trav_init_any(const DScene& sc, Trav& T, const float3 o, const float3 d)
   T.incl = T.best_id != 0xFFFFFFFFu;
 }
 
-// One traversal iteration: AT MOST one triangle test and one 8-wide node test.  Returns
+#ifndef PTC_TRI_PER_ITER
+#define PTC_TRI_PER_ITER 2
+#endif
+
+// One traversal iteration: AT MOST PTC_TRI_PER_ITER triangle tests and one 8-wide node test.  Returns
 // true when the ray has nothing left to visit.
 //
 // Traversal order never changes the answer (the winner is the lexicographic minimum of
@@ -341,6 +345,8 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
   // (Holding triangle tests back until N lanes of the warp have one pending was measured for
   // N = 8..24: 4-7 % slower on both ends of the scene-size range -- the later a hit shrinks
   // best_t, the more boxes are entered.)
+#pragma unroll
+  for (int rep = 0; rep < PTC_TRI_PER_ITER; ++rep)
   if (T.tmask) {
     const uint32_t bit = __ffs(T.tmask) - 1u;
     T.tmask &= T.tmask - 1u;
@@ -366,6 +372,9 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
   }
 
   // -- at most one node test ------------------------------------------------------------
+  // (A warp vote that holds the node test back while fewer than N = 4 / 8 / 12 lanes want one and
+  // others still have triangles to test was measured: 3-5 % slower -- the held lanes sit on the
+  // warp's critical path more often than not.)
   if ((T.ng.y & 0xFF000000u) && T.tsp < kTriBacklog) {
     const uint32_t bit = 31u - __clz(T.ng.y);
     T.ng.y &= ~(1u << bit);

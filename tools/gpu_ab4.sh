@@ -1,0 +1,12 @@
+# A/B: node tests held back by warp vote, two triangle tests per iteration
+V=/root/repo/cuda-pathtracer_b200/_variants
+PTC_LIBRARY=$V/hold8.so python -m pytest tests -m gpu -q -x --timeout 900 -k "not oracle_bvh and not scene_info" 2>&1 | tail -2
+PTC_LIBRARY=$V/tri2.so python -m pytest tests -m gpu -q -x --timeout 900 -k "not oracle_bvh and not scene_info" 2>&1 | tail -2
+for v in default hold4 hold8 hold12 tri2 default; do
+  lib=$V/$v.so; [ $v = default ] && lib=""
+  echo "== $v"
+  PTC_LIBRARY=$lib python tools/frame_probe.py indoor_tex 64 2>&1 | grep ms/frame
+  PTC_LIBRARY=$lib python tools/frame_probe.py indoor_tex 16 3840 2160 8 2>&1 | grep ms/frame
+  PTC_LIBRARY=$lib python tools/frame_probe.py color_sample_plain 16 3840 2160 3 2>&1 | grep ms/frame
+  PTC_LIBRARY=$lib python tools/frame_probe.py synth2236 32 1920 1080 4 2>&1 | grep ms/frame
+done
