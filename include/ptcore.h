@@ -296,7 +296,9 @@ int ptc_launch_count(const ptc_context* ctx, uint64_t* out);
  * stage (generate + extend + shade) and each later stage run in registers before handing the
  * surviving rays to the next stage through the compacted queue (0 keeps the current value).
  * split_extend: 1 = every later stage is an extend kernel with per-lane refill followed by
- * a shade kernel (one iteration per stage), 0 = fused extend+shade, < 0 keeps.
+ * a shade kernel (one iteration per stage), 0 = fused extend+shade, 2 = shifted stages (stage k
+ * shades iteration k-1 and intersects iteration k, so only rays that hit are queued; one
+ * iteration per stage, first_iters / next_iters ignored), < 0 keeps.
  * refill: idle lanes per warp that trigger a refill in the extend kernel (0 keeps; default 12).
  * Default: 1 iteration per stage; later stages fused when nodes + triangles fit 64 KB (L1),
  * split otherwise;
@@ -314,7 +316,8 @@ typedef struct ptc_profile
   uint32_t n_launches;        /* kernel launches per frame                            */
   float launch_ms[130];       /* mean duration of each launch over the repeats        */
   uint32_t launch_kind[130];  /* 0 first stage (generate+extend+shade), 1 fused later
-                                 stage, 2 extend (refilling traversal), 3 shade        */
+                                 stage, 2 extend (refilling traversal), 3 shade,
+                                 4 / 5 shifted form: generate+intersect / shade+intersect */
   uint32_t launch_bounce0[130];/* first radiance-loop iteration each launch handles    */
   uint32_t launch_iters[130];
   float frame_ms;             /* mean duration of the whole frame (all launches)      */

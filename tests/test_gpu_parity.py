@@ -521,7 +521,8 @@ def test_wavefront_granularity_invariance(core):
     results = []
     try:
         for first, nxt, split, refill in [(1, 1, 0, 8), (2, 1, 0, 8), (1, 3, 0, 8), (6, 1, 0, 8), (3, 2, 0, 8),
-                                          (1, 1, 1, 8), (1, 1, 1, 1), (1, 1, 1, 32), (2, 1, 1, 16)]:
+                                          (1, 1, 1, 8), (1, 1, 1, 1), (1, 1, 1, 32), (2, 1, 1, 16),
+                                          (1, 1, 2, 8)]:   # 2 = shifted stages (k_wave)
             core.set_wavefront(first, nxt, split, refill)
             acc, out, rad = dev_buffers(w, h)
             core.reset_counters()
@@ -537,6 +538,52 @@ def test_wavefront_granularity_invariance(core):
     for r in results[1:]:
         assert (bits(r[0]) == bits(a0[0])).all() and (r[1] == a0[1]).all() and (bits(r[2]) == bits(a0[2])).all()
         assert r[3:] == a0[3:]
+
+
+def test_shifted_schedule_and_deferred_epilogue_invariance(core):
+    """1080p (two half-frame pipelines): the shifted schedule (k_wave: only rays that hit are queued,
+    shaded by the next stage) and the epilogue placement (in place / parked for the last stage,
+    PTC_DEFER) change no bit of accumulator, RGBA8 or counters."""
+    import torch
+    P = pkg()
+    L = loaded(core, "indoor_tex")
+    w, h, b = 1920, 1080, 4
+
+    def frames(c, sid, cid):
+        acc, out, rad = dev_buffers(w, h)
+        c.reset_counters()
+        for k in (1, 2):
+            c.render(sid, cid, L.sc, w, h, acc, out, rad, bounces=b, frame_nb=k)
+        torch.cuda.synchronize()
+        n = c.counters()
+        return acc.cpu().numpy(), out.cpu().numpy(), rad.cpu().numpy(), n.segments, n.traced
+
+    base = frames(core, L.sid, L.cid)
+    try:
+        core.set_wavefront(1, 1, 2, 8)
+        shifted = frames(core, L.sid, L.cid)
+    finally:
+        core.set_wavefront_auto()
+    old = os.environ.get("PTC_DEFER")
+    os.environ["PTC_DEFER"] = "0"
+    try:
+        c2 = P.Core(0)
+    finally:
+        if old is None:
+            del os.environ["PTC_DEFER"]
+        else:
+            os.environ["PTC_DEFER"] = old
+    try:
+        sid2 = c2.upload_scene(L.sc)
+        cid2 = c2.set_cubemap(cube_of(L.sc)[0])
+        in_place = frames(c2, sid2, cid2)
+        c2.set_wavefront(1, 1, 2, 8)
+        in_place_shifted = frames(c2, sid2, cid2)
+    finally:
+        c2.close()
+    for r in (shifted, in_place, in_place_shifted):
+        assert (bits(r[0]) == bits(base[0])).all() and (r[1] == base[1]).all() and (bits(r[2]) == bits(base[2])).all()
+        assert r[3:] == base[3:]
 
 
 def test_interleaved_strips_equal_full_frame(core):
