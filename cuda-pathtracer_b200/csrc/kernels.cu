@@ -50,7 +50,15 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
   LocalStack stack;
 #else
   extern __shared__ uint2 s_stack[]; // stack_cap entries x kBlock threads (none when HITS)
+#ifdef PTC_TABLES
+  __shared__ uint32_t s_spread[HITS ? 1 : kSpreadWords];
+  __shared__ uint8_t s_perm[HITS ? 4 : kPermBytes];
+  if (!HITS)
+    trav_tables_init(s_perm, s_spread);
+  SharedStack stack{ s_stack + threadIdx.x, stack_cap, s_perm, s_spread };
+#else
   SharedStack stack{ s_stack + threadIdx.x, stack_cap };
+#endif
 #endif
   __shared__ uint32_t s_rays[16];
   __shared__ float s_cam[8]; // camera basis of the frame, evaluated once per CTA (FIRST)
@@ -281,7 +289,14 @@ k_wave(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
        float4* __restrict__ done_q, uint32_t* __restrict__ done_ctl, const int done_mode)
 {
   extern __shared__ uint2 s_stack[]; // stack_cap entries x kBlock threads
+#ifdef PTC_TABLES
+  __shared__ uint32_t s_spread[kSpreadWords];
+  __shared__ uint8_t s_perm[kPermBytes];
+  trav_tables_init(s_perm, s_spread);
+  SharedStack stack{ s_stack + threadIdx.x, stack_cap, s_perm, s_spread };
+#else
   SharedStack stack{ s_stack + threadIdx.x, stack_cap };
+#endif
   __shared__ uint32_t s_nrays;
   __shared__ float s_cam[8];
   if (threadIdx.x == 0)
@@ -470,7 +485,15 @@ k_extend(const DScene sc, const RayQueue qin, const uint32_t* __restrict__ qin_c
   LocalStack stack;
 #else
   extern __shared__ uint2 s_stack[]; // stack_cap entries x kBlock threads
+#ifdef PTC_TABLES
+  __shared__ uint32_t s_spread[kSpreadWords];
+  __shared__ uint8_t s_perm[kPermBytes];
+  trav_tables_init(s_perm, s_spread);
+  __syncthreads();
+  SharedStack stack{ s_stack + threadIdx.x, stack_cap, s_perm, s_spread };
+#else
   SharedStack stack{ s_stack + threadIdx.x, stack_cap };
+#endif
 #endif
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t n = *qin_count;
@@ -633,7 +656,7 @@ max_optin_smem()
   int dev = 0, v = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-  return v - 128; // the static s_rays[16] + s_cam[8] of k_path share the budget
+  return v - 128 - kPermBytes - 4 * kSpreadWords; // static shared memory of the stage kernels: counters, camera basis, tables
 }
 
 template <bool FIRST, bool STATS, bool HITS>

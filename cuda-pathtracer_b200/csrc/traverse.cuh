@@ -214,6 +214,28 @@ spread3(uint32_t x)
   return x;
 }
 
+// bit s of an 8-bit mask -> bit s ^ c (children are visited in ray-octant order)
+__device__ __forceinline__ uint32_t
+xor_permute8(uint32_t m, uint32_t c)
+{
+  if (c & 1u)
+    m = ((m & 0x55u) << 1) | ((m >> 1) & 0x55u);
+  if (c & 2u)
+    m = ((m & 0x33u) << 2) | ((m >> 2) & 0x33u);
+  if (c & 4u)
+    m = ((m & 0x0Fu) << 4) | (m >> 4);
+  return m;
+}
+
+#ifndef PTC_NO_TABLES
+#define PTC_TABLES 1
+#endif
+// Two small tables the stage kernels keep in shared memory (filled once per CTA, trav_tables_init):
+// the octant permutation of a hit mask (8 x 256 bytes) and the slot mask -> triangle-bit mask
+// spreading (256 words).  One LDS each instead of 12 and 8 ALU instructions per node test: the
+// kernels are bound by instruction issue with the ALU pipe as the busiest one.
+constexpr int kPermBytes = 8 * 256, kSpreadWords = 256;
+
 // Per-ray traversal stack.  Two homes with one interface:
 //  * SharedStack -- the stage kernels: entry e of thread t lives at smem[(e * kBlock + t) * 8],
 //    so whatever depth each lane is at, a warp's push/pop is one conflict-free shared-memory
@@ -224,6 +246,8 @@ spread3(uint32_t x)
 struct LocalStack
 {
   uint2 a[kStackSize];
+  __device__ __forceinline__ uint32_t permute(uint32_t m, uint32_t oct_inv) const { return xor_permute8(m, oct_inv); }
+  __device__ __forceinline__ uint32_t spread7(uint32_t m) const { return spread3(m) * 7u; }
   __device__ __forceinline__ uint2 get(int i) const { return a[i]; }
   __device__ __forceinline__ void put(int i, uint2 v) { a[i] = v; }
   __device__ __forceinline__ int top() const { return kStackSize; }
@@ -233,10 +257,29 @@ struct SharedStack
 {
   uint2* base; // smem + threadIdx.x
   int cap;
+#ifdef PTC_TABLES
+  const uint8_t* perm;    // [oct_inv][mask]
+  const uint32_t* spread; // [mask] -> spread3(mask) * 7
+  __device__ __forceinline__ uint32_t permute(uint32_t m, uint32_t oct_inv) const { return perm[(oct_inv << 8) | m]; }
+  __device__ __forceinline__ uint32_t spread7(uint32_t m) const { return spread[m]; }
+#else
+  __device__ __forceinline__ uint32_t permute(uint32_t m, uint32_t oct_inv) const { return xor_permute8(m, oct_inv); }
+  __device__ __forceinline__ uint32_t spread7(uint32_t m) const { return spread3(m) * 7u; }
+#endif
   __device__ __forceinline__ uint2 get(int i) const { return base[i * kBlock]; }
   __device__ __forceinline__ void put(int i, uint2 v) { base[i * kBlock] = v; }
   __device__ __forceinline__ int top() const { return cap; }
 };
+
+// Fills the two tables (all threads of the CTA; the caller synchronises afterwards).
+__device__ __forceinline__ void
+trav_tables_init(uint8_t* perm, uint32_t* spread)
+{
+  for (uint32_t i = threadIdx.x; i < (uint32_t)kPermBytes; i += blockDim.x)
+    perm[i] = (uint8_t)xor_permute8(i & 0xFFu, i >> 8);
+  for (uint32_t i = threadIdx.x; i < (uint32_t)kSpreadWords; i += blockDim.x)
+    spread[i] = spread3(i) * 7u;
+}
 
 // 32-byte read-only load (sm_100: LDG.E.256): one L1 tag request where two 16-byte loads make two.
 __device__ __forceinline__ void
@@ -336,7 +379,7 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
     const uint2 e = stack.get(stack.top() - T.tsp); // (tri_base, valid24 | leaf-slot hit mask << 24)
     --T.tsp;
     T.tg = make_uint2(e.x, e.y & 0x00FFFFFFu);
-    T.tmask = (spread3(e.y >> 24) * 7u) & T.tg.y;
+    T.tmask = stack.spread7(e.y >> 24) & T.tg.y;
   }
   if (!(T.ng.y & 0xFF000000u) && T.sp)
     T.ng = stack.get(--T.sp);
@@ -452,13 +495,7 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
 
     // internal children: bit s -> 24 + (s ^ oct_inv), i.e. far-to-near from the top bit down
     const uint32_t imask = n0.w >> 24;
-    uint32_t ih = hit8 & imask;
-    if (T.oct_inv & 1u)
-      ih = ((ih & 0x55u) << 1) | ((ih >> 1) & 0x55u);
-    if (T.oct_inv & 2u)
-      ih = ((ih & 0x33u) << 2) | ((ih >> 2) & 0x33u);
-    if (T.oct_inv & 4u)
-      ih = ((ih & 0x0Fu) << 4) | (ih >> 4);
+    const uint32_t ih = stack.permute(hit8 & imask, T.oct_inv);
     T.ng = make_uint2(n1.x, (ih << 24) | imask);
     // (Asking L2 for every hit internal child here -- prefetch.global.L2, DRAM runs at 10 % of its
     // bandwidth on the 10 M-triangle scene -- was measured: +2 % frame time; the extra issue slots
@@ -466,7 +503,7 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
 
     // leaf slots that were hit -> their triangles (3 bits per slot, masked by the existing ones)
     const uint32_t lh = hit8 & ~imask;
-    const uint32_t tnew = (spread3(lh) * 7u) & n1.z;
+    const uint32_t tnew = stack.spread7(lh) & n1.z;
     if (tnew) {
       if (T.tmask) {
         stack.put(stack.top() - (++T.tsp), make_uint2(n1.y, n1.z | (lh << 24))); // defer, unstarted
