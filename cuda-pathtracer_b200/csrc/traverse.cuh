@@ -435,12 +435,11 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
     ldg256(sc.nodes + vec0, n0, n1);
 #endif
     // near / far plane sets picked by ray octant through the load address, not by selects
-    // (measured: deriving the far index as near ^ c instead of the subtraction is slower)
-    // (indices summed in 32 bits before they meet the pointer: `nodes + vec0 + 7u - vnx` made the
-    // compiler subtract in 64 bits, four instructions per far plane set instead of three)
-    const uint4 NX = __ldg(sc.nodes + (vec0 + T.vnx)), FX = __ldg(sc.nodes + (vec0 + (7u - T.vnx)));
-    const uint4 NY = __ldg(sc.nodes + (vec0 + T.vny)), FY = __ldg(sc.nodes + (vec0 + (9u - T.vny)));
-    const uint4 NZ = __ldg(sc.nodes + (vec0 + T.vnz)), FZ = __ldg(sc.nodes + (vec0 + (11u - T.vnz)));
+    // (measured: deriving the far index as near ^ c instead of the subtraction is slower; so is
+    // summing the indices in 32 bits first, +1.3 %, although it is two instructions shorter per set)
+    const uint4 NX = __ldg(sc.nodes + vec0 + T.vnx), FX = __ldg(sc.nodes + vec0 + 7u - T.vnx);
+    const uint4 NY = __ldg(sc.nodes + vec0 + T.vny), FY = __ldg(sc.nodes + vec0 + 9u - T.vny);
+    const uint4 NZ = __ldg(sc.nodes + vec0 + T.vnz), FZ = __ldg(sc.nodes + vec0 + 11u - T.vnz);
     if (STATS)
       n_nodes++;
 
