@@ -19,10 +19,18 @@ value     device-resident: accumulator and RGBA8 stay in HBM, CUDA events per fr
           launching stream, L2 flushed (512 MB memset) between timed frames.
 e2e       the same frames through ptc_render_host: camera/arguments host->device and the
           RGBA8 frame device->pinned host every step, inside the timed region.
-roofline  for the dominant kernel (traversal): bytes of BVH nodes + triangle records the
-          traced rays fetch (counted by the kernel's own visit counters) over
-          the kernel's CUDA-event time, against MEASURED_PEAKS.json's HBM figure -- with the
-          FP32 issue bound printed beside it, since a 27 KB scene is not bandwidth-bound.
+roofline  for the frame's stage kernels: three lower bounds on their time -- bytes (BVH bytes at
+          the MEASURED bandwidth of the cache tier the BVH lives in + every other byte at the HBM
+          peak of MEASURED_PEAKS.json), intersection flops at the FP32 peak, and warp instructions
+          at the issue rate (4 schedulers x SMs x the SM clock sampled during the run) -- `bound`
+          names the largest, `frac` = that bound / the kernels' CUDA-event time.  Instruction
+          counts and DRAM traffic come from the committed ncu capture of the same workload
+          (profiles/r2_counters.json), and say so.
+sustained >= 5 s of back-to-back frames (no flush) with the SM clock sampled during them.
+workloads --workload headline (default; BASELINE.json configs[1]) | cfg0 | cfg1b4 | cfg2 | cfg3:
+          configs[0] 640x360 b=4, configs[1] at 4 iterations, configs[2] = 3840x2160, 16 frames,
+          8 iterations, STRONG scaling over the ranks with the gathered accumulator compared bit
+          for bit with a 1-GPU render, configs[3] = the 10 M-triangle synthetic mesh.
 """
 from __future__ import annotations
 
@@ -203,7 +211,8 @@ def run_reference_arm(args):
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "frames_per_s": frames_full / r["seconds"],
-            "config": config_dict(args, w, h, sc, "host cores; each step = a strided sample of 16x16 blocks"),
+            "config": config_dict(args, w, h, sc),
+            "sampling": "host cores; each step = a strided sample of 16x16 blocks of the frame",
             "cpu_baseline": {"value": r["mrays"], "unit": "Mrays/s", "cores": r["cores"], "kind": r["kind"],
                              "sample": r["sample"]},
             "e2e": {"value": r["mrays"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -212,13 +221,47 @@ def run_reference_arm(args):
     return 0
 
 
-def config_dict(args, w, h, sc, l2):
-    return {"workload": f"{args.scene} {w}x{h} 1spp/frame bounces={args.bounces} temporal accumulation "
-                        f"(BASELINE.json configs[1]; cubemap = reference's constant fallback)",
+WORKLOADS = {
+    # name: (scene, width, height, bounces, scaling)
+    "headline": ("indoor_tex", 0, 0, 3, "weak"),       # configs[1]; N > 1: N x the pixels (WEAK_DIMS)
+    "cfg0": ("indoor_tex", 640, 360, 4, "strong"),
+    "cfg1b4": ("indoor_tex", 1920, 1080, 4, "strong"),
+    "cfg2": ("indoor_tex", 3840, 2160, 8, "strong"),   # 16 frames, gather after the last, bit-identity check
+    "cfg3": ("synth2236", 1920, 1080, 4, "strong"),
+}
+
+
+def baseline_config_name(scene, w, h, bounces):
+    """Which entry of BASELINE.json `configs` these arguments are (None: none of them)."""
+    if scene.startswith("indoor"):
+        if (w, h, bounces) == (640, 360, 4):
+            return "configs[0] (README indoor scene 640x360, 1 spp, 4 bounces)"
+        if (w, h) == (1920, 1080):
+            return ("configs[1] (indoor scene 1920x1080, 1 spp/frame, temporal accumulation"
+                    + ("" if bounces == 3 else f"; {bounces} iterations instead of the reference's constant 3") + ")")
+        if (w, h, bounces) == (3840, 2160, 8):
+            return "configs[2] (indoor scene 3840x2160, 8 bounces, image tiles across the GPUs)"
+        if h * 16 == w * 9:
+            return "configs[1] weak-scaled (the same 16:9 view at N x 1080p pixels)"
+    if scene == "synth2236" and (w, h) == (1920, 1080):
+        return "configs[3] (synthetic 10 M-triangle mesh, 1080p, glossy / refractive materials)"
+    return None
+
+
+def config_dict(args, w, h, sc):
+    """Identical for both arms (the driver compares it)."""
+    name = baseline_config_name(args.scene, w, h, args.bounces)
+    return {"workload": f"{args.scene} {w}x{h} 1spp/frame bounces={args.bounces} temporal accumulation; "
+                        + (f"BASELINE.json {name}" if name else "not a BASELINE.json configuration")
+                        + ("; cubemap = the reference's constant fallback" if args.scene.startswith("indoor") else ""),
             "scene": args.scene, "width": w, "height": h, "bounces": args.bounces, "faces": sc.n_faces,
             "partition": (f"{args.gpus} ranks, round-robin 16-row strips, scene replicated"
                           if args.gpus > 1 and args.partition == "strips" else
-                          f"{args.gpus} contiguous band(s) of whole 16-row strips, scene replicated"), "l2": l2}
+                          f"{args.gpus} contiguous band(s) of whole 16-row strips, scene replicated")}
+
+
+L2_POLICY = ("512 MB memset between timed frames (outside the per-frame event pairs); steady-state figure "
+             "without flush alongside")
 
 
 # ---------------------------------------------------------------------------------------------
@@ -376,8 +419,7 @@ def run_ours(args):
                 "ms_gather_once": ms_gather,
                 "ms_per_frame_rank0": {"min": per_frame[0], "median": per_frame[len(per_frame) // 2],
                                        "max": per_frame[-1]},
-                "config": config_dict(args, w, h, sc, "512 MB memset between timed frames (outside the per-frame "
-                                                     "event pairs); steady-state figure without flush alongside"),
+                "config": config_dict(args, w, h, sc), "l2_policy": L2_POLICY,
                 "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_ms / K,
                         "h2d_bytes_per_step": C.sizeof(P.core.PtcRenderArgs) + 64,

@@ -11,9 +11,9 @@ REPO = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libptcore.so")
 CUDA = os.environ.get("CUDA_HOME", "/usr/local/cuda")
-SOURCES = ["ptcore.cu", "kernels.cu", "bvh_builder.cpp"]
+SOURCES = ["ptcore.cu", "kernels.cu", "group.cu", "bvh_builder.cpp"]
 HEADERS = ["bvh.h", "device_types.cuh", "kernels.cuh", "vecmath.cuh", "traverse.cuh", "shade.cuh",
-           "../../include/ptcore.h"]
+           "ptcore_internal.h", "../../include/ptcore.h"]
 
 
 def up_to_date():
@@ -29,7 +29,7 @@ def build(force=False, verbose=False):
         return OUT
     cmd = [os.path.join(CUDA, "bin", "nvcc"), "-std=c++17", "-O3", "-lineinfo",
            "-gencode", "arch=compute_100a,code=sm_100a",
-           "-Xcompiler", "-fPIC,-O2,-Wall", "-shared",
+           "-Xcompiler", "-fPIC,-O2,-Wall,-pthread", "-shared",
            "-I", os.path.join(REPO, "include"), "-I", CSRC]
     if verbose:
         cmd += ["-Xptxas", "-v"]

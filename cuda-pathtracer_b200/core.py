@@ -33,7 +33,7 @@ class PtcRenderArgs(C.Structure):
                 ("accum", C.c_void_p), ("out_rgba", C.c_void_p),
                 ("radiance_out", C.c_void_p), ("stream", C.c_void_p),
                 ("strip_rows", C.c_uint32), ("strip_stride", C.c_uint32),
-                ("strip_phase", C.c_uint32), ("_pad", C.c_uint32)]
+                ("strip_phase", C.c_uint32), ("flags", C.c_uint32)]
 
 
 class PtcCounters(C.Structure):
@@ -57,7 +57,9 @@ class PtcProfile(C.Structure):
                 ("frame_ms", C.c_float), ("traced", C.c_uint64), ("segments", C.c_uint64),
                 ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
                 ("rays_per_bounce", C.c_uint64 * 16), ("queue_rays", C.c_uint64),
-                ("queue_bytes_per_ray", C.c_uint32), ("hit_bytes_per_ray", C.c_uint32)]
+                ("queue_bytes_per_ray", C.c_uint32), ("hit_bytes_per_ray", C.c_uint32),
+                ("frame_ms_shipped", C.c_float), ("pipelines", C.c_uint32),
+                ("extend_lanes", C.c_uint64 * 8)]
 
 
 class PtcHostBvh(C.Structure):
@@ -75,7 +77,12 @@ EXPORTS = ["ptc_abi_version", "ptc_create", "ptc_destroy", "ptc_last_error", "pt
            "ptc_profile_frame", "ptc_render_host_async", "ptc_wait",
            "ptc_upload_scene_from_device", "ptc_set_cubemap_from_array",
            "ptc_set_cubemap_from_cross", "ptc_cubemap_faces_from_cross",
-           "ptc_write_ppm", "ptc_accum_save", "ptc_accum_load", "ptc_debug_read_bandwidth"]
+           "ptc_write_ppm", "ptc_accum_save", "ptc_accum_load", "ptc_debug_read_bandwidth",
+           "ptc_group_create", "ptc_group_destroy", "ptc_group_last_error", "ptc_group_size",
+           "ptc_group_context", "ptc_group_upload_scene", "ptc_group_set_cubemap", "ptc_group_render",
+           "ptc_group_sync", "ptc_group_image", "ptc_group_read_image", "ptc_group_gather_accum",
+           "ptc_group_reset_accumulation", "ptc_shared_alloc", "ptc_shared_open", "ptc_shared_close",
+           "ptc_shared_free", "ptc_flag_signal", "ptc_flag_wait", "ptc_memcpy_to_host"]
 
 _lib = None
 
@@ -105,8 +112,22 @@ def load_library() -> C.CDLL:
                      "ptc_render_host_async", "ptc_wait", "ptc_set_cubemap_from_cross",
                      "ptc_cubemap_faces_from_cross", "ptc_upload_scene_from_device",
                      "ptc_set_cubemap_from_array", "ptc_write_ppm", "ptc_accum_save", "ptc_accum_load",
-                     "ptc_debug_read_bandwidth"]:
+                     "ptc_debug_read_bandwidth", "ptc_group_create", "ptc_group_upload_scene",
+                     "ptc_group_set_cubemap", "ptc_group_render", "ptc_group_sync", "ptc_group_read_image",
+                     "ptc_group_gather_accum", "ptc_group_reset_accumulation", "ptc_shared_alloc",
+                     "ptc_shared_open", "ptc_shared_close", "ptc_shared_free", "ptc_flag_signal",
+                     "ptc_flag_wait", "ptc_memcpy_to_host"]:
             getattr(lib, name).restype = C.c_int
+        lib.ptc_group_last_error.restype = C.c_char_p
+        lib.ptc_group_last_error.argtypes = [C.c_void_p]
+        lib.ptc_group_destroy.restype = None
+        lib.ptc_group_destroy.argtypes = [C.c_void_p]
+        lib.ptc_group_size.restype = C.c_uint32
+        lib.ptc_group_size.argtypes = [C.c_void_p]
+        lib.ptc_group_context.restype = C.c_void_p
+        lib.ptc_group_context.argtypes = [C.c_void_p, C.c_uint32]
+        lib.ptc_group_image.restype = C.c_void_p
+        lib.ptc_group_image.argtypes = [C.c_void_p]
         lib.ptc_band_rows.restype = C.c_uint32
         _lib = lib
     return _lib
@@ -122,7 +143,7 @@ def _ptr(a):
     return C.c_void_p(int(a))
 
 
-def cubemap_faces_from_cross(cross, rgb_hex: int = 0):
+def cubemap_faces_from_cross(cross, rgb_hex: int = 0xFFFFFFFF):
     """Host-only: the six faces (6, size, size, 4) the reference cuts out of a cube cross
     (texture_utils.cpp:5-52), or its constant-colour fallback.  Returns (faces, used_fallback)."""
     lib = load_library()
@@ -239,7 +260,7 @@ class Core:
                                              C.byref(cid)), "ptc_set_cubemap")
         return cid.value
 
-    def set_cubemap_from_cross(self, cross, rgb_hex: int = 0):
+    def set_cubemap_from_cross(self, cross, rgb_hex: int = 0xFFFFFFFF):
         """uploadCubemap (gpu_processor.cpp:68-161) for a (h, w, nb_chan) float cube cross, or --
         ``cross=None`` -- for the constant-colour path.  Returns (cubemap_id, used_fallback)."""
         cid, fb = C.c_int32(-1), C.c_int32(0)
@@ -272,7 +293,7 @@ class Core:
     # -- render ----------------------------------------------------------------
     def _args(self, scene_id, cubemap_id, camera, width, height, accum, out_rgba=None,
               radiance_out=None, bounces=3, moved=False, post_id=0, frame_nb=0, rows=None,
-              stream=0, strips=None):
+              stream=0, strips=None, out_full=False):
         cam = camera if isinstance(camera, PtcCamera) else camera.camera_struct()
         self._keep = [cam]
         a = PtcRenderArgs()
@@ -287,6 +308,7 @@ class Core:
         a.stream = C.c_void_p(int(stream)) if stream else None
         if strips:  # (strip_rows, strip_stride, strip_phase): interleaved image tiles
             a.strip_rows, a.strip_stride, a.strip_phase = strips
+        a.flags = 1 if out_full else 0  # PTC_OUT_FULL_IMAGE
         return a
 
     def band_rows(self, width, height, rows=None, strips=None) -> int:
@@ -309,8 +331,8 @@ class Core:
 
     def set_wavefront_auto(self):
         """Back to the default schedule (first stage depth chosen per scene size)."""
-        self._check(self.lib.ptc_set_wavefront(self.ctx, C.c_uint32(0xFFFFFFFF), C.c_uint32(1), C.c_int32(1),
-                                               C.c_uint32(8)), "ptc_set_wavefront")
+        self._check(self.lib.ptc_set_wavefront(self.ctx, C.c_uint32(0xFFFFFFFF), C.c_uint32(0), C.c_int32(-1),
+                                               C.c_uint32(0)), "ptc_set_wavefront")
 
     def profile_frame(self, *args, repeats=5, **kw) -> dict:
         """Per-launch CUDA-event times of one frame + traversal statistics (ptc_profile_frame)."""
@@ -328,7 +350,9 @@ class Core:
                 "nodes_visited": pr.nodes_visited, "tris_tested": pr.tris_tested,
                 "rays_per_bounce": [pr.rays_per_bounce[i] for i in range(16)],
                 "queue_rays": pr.queue_rays, "queue_bytes_per_ray": pr.queue_bytes_per_ray,
-                "hit_bytes_per_ray": pr.hit_bytes_per_ray}
+                "hit_bytes_per_ray": pr.hit_bytes_per_ray,
+                "frame_ms_shipped": pr.frame_ms_shipped, "pipelines": pr.pipelines,
+                "extend_lanes": [pr.extend_lanes[i] for i in range(5)]}
 
     def render(self, *args, **kw):
         """Device-pointer render call (accum / out_rgba / radiance_out are device buffers)."""
@@ -389,3 +413,131 @@ class Core:
         self._check(self.lib.ptc_debug_rng(self.ctx, _ptr(s), C.c_uint32(s.size), C.c_uint32(n_draws),
                                            C.c_int(int(reference_impl)), _ptr(out)), "ptc_debug_rng")
         return out
+
+
+class Group:
+    """Several GPUs behind one call (ptc_group_*): one upload, one render per frame, one image on
+    devices[0], the same bits as one GPU.  Single process; `devices` may repeat a device."""
+
+    def __init__(self, devices):
+        self.lib = load_library()
+        self.devices = list(devices)
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        g = C.c_void_p()
+        rc = self.lib.ptc_group_create(arr, C.c_uint32(len(self.devices)), C.byref(g))
+        if rc == PTC_ERR_NO_DEVICE:
+            raise PtcError("ptc_group_create: a device is missing or has no peer access to devices[0] "
+                           "(the core has no CPU fallback)")
+        if rc:
+            raise PtcError(f"ptc_group_create failed: {rc}")
+        self.g = g
+        self._keep = None
+
+    def close(self):
+        if self.g:
+            self.lib.ptc_group_destroy(self.g)
+            self.g = C.c_void_p()
+
+    def _check(self, rc, what):
+        if rc:
+            raise PtcError(f"{what} failed ({rc}): {self.lib.ptc_group_last_error(self.g).decode()}")
+
+    @property
+    def size(self):
+        return int(self.lib.ptc_group_size(self.g))
+
+    def upload_scene(self, scene) -> int:
+        desc = scene.to_desc()
+        sid = C.c_int32(-1)
+        self._check(self.lib.ptc_group_upload_scene(self.g, C.byref(desc), C.byref(sid)), "ptc_group_upload_scene")
+        return sid.value
+
+    def set_cubemap(self, faces) -> int:
+        faces = np.ascontiguousarray(faces, dtype=np.float32)
+        cid = C.c_int32(-1)
+        self._check(self.lib.ptc_group_set_cubemap(self.g, _ptr(faces), C.c_uint32(faces.shape[1]), C.byref(cid)),
+                    "ptc_group_set_cubemap")
+        return cid.value
+
+    def render(self, scene_id, cubemap_id, camera, width, height, out_rgba=None, bounces=3, moved=False,
+               post_id=0, frame_nb=0, stream=0):
+        cam = camera if isinstance(camera, PtcCamera) else camera.camera_struct()
+        self._keep = cam
+        a = PtcRenderArgs()
+        a.scene_id, a.cubemap_id = scene_id, cubemap_id
+        a.camera = C.pointer(cam)
+        a.width, a.height = width, height
+        a.bounces, a.moved, a.post_id, a.frame_nb = bounces, int(bool(moved)), post_id, frame_nb
+        a.out_rgba = _ptr(out_rgba)
+        a.stream = C.c_void_p(int(stream)) if stream else None
+        self._check(self.lib.ptc_group_render(self.g, C.byref(a)), "ptc_group_render")
+
+    def sync(self):
+        self._check(self.lib.ptc_group_sync(self.g), "ptc_group_sync")
+
+    def read_image(self, width, height, stream=0) -> np.ndarray:
+        out = np.zeros((height, width), np.uint32)
+        self._check(self.lib.ptc_group_read_image(self.g, _ptr(out), C.c_void_p(int(stream)) if stream else None),
+                    "ptc_group_read_image")
+        return out
+
+    def gather_accum(self, width, height) -> np.ndarray:
+        out = np.zeros((height, width, 3), np.float32)
+        self._check(self.lib.ptc_group_gather_accum(self.g, _ptr(out)), "ptc_group_gather_accum")
+        return out
+
+    def reset_accumulation(self):
+        self._check(self.lib.ptc_group_reset_accumulation(self.g), "ptc_group_reset_accumulation")
+
+
+class SharedBuffer:
+    """Device memory of one rank that the other ranks of a one-process-per-GPU job map through CUDA
+    IPC (ptc_shared_*): the full image the ranks' kernels store their tiles into, and the flags."""
+
+    def __init__(self, device, nbytes=0, handle=None):
+        self.lib = load_library()
+        self.device = device
+        self.ptr = C.c_void_p()
+        self.owner = handle is None
+        if self.owner:
+            h = (C.c_uint8 * 64)()
+            rc = self.lib.ptc_shared_alloc(C.c_int(device), C.c_uint64(nbytes), C.byref(self.ptr), h)
+            if rc:
+                raise PtcError(f"ptc_shared_alloc failed: {rc}")
+            self.handle = bytes(h)
+        else:
+            h = (C.c_uint8 * 64).from_buffer_copy(handle)
+            rc = self.lib.ptc_shared_open(C.c_int(device), h, C.byref(self.ptr))
+            if rc:
+                raise PtcError(f"ptc_shared_open failed: {rc} (no peer access between the GPUs?)")
+            self.handle = bytes(handle)
+
+    @property
+    def address(self) -> int:
+        return int(self.ptr.value)
+
+    def close(self):
+        if self.ptr:
+            (self.lib.ptc_shared_free if self.owner else self.lib.ptc_shared_close)(C.c_int(self.device), self.ptr)
+            self.ptr = C.c_void_p()
+
+    def to_host(self, out: np.ndarray, offset=0, stream=0, sync=True):
+        rc = self.lib.ptc_memcpy_to_host(C.c_int(self.device), _ptr(out), C.c_void_p(self.address + offset),
+                                         C.c_uint64(out.nbytes), C.c_void_p(int(stream)) if stream else None,
+                                         C.c_int(int(sync)))
+        if rc:
+            raise PtcError(f"ptc_memcpy_to_host failed: {rc}")
+
+
+def flag_signal(device, address, value, stream=0):
+    rc = load_library().ptc_flag_signal(C.c_int(device), C.c_void_p(address), C.c_uint32(value),
+                                        C.c_void_p(int(stream)) if stream else None)
+    if rc:
+        raise PtcError(f"ptc_flag_signal failed: {rc}")
+
+
+def flag_wait(device, address, n, stride_words, value, stream=0):
+    rc = load_library().ptc_flag_wait(C.c_int(device), C.c_void_p(address), C.c_uint32(n), C.c_uint32(stride_words),
+                                      C.c_uint32(value), C.c_void_p(int(stream)) if stream else None)
+    if rc:
+        raise PtcError(f"ptc_flag_wait failed: {rc}")

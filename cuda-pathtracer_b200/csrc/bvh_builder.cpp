@@ -432,6 +432,84 @@ exp_scale(uint8_t e)
   return f;
 }
 
+// Treelet order (serial, deterministic post-pass over the breadth-first emission).  Breadth-first
+// order keeps a node's children contiguous (required: child = child_base + rank) but puts every
+// level of a subtree in a different region of the array, and the triangle records follow the node
+// order; a ray walking down one subtree of a 1.4 GB structure touches one 2 MB page per level for
+// the nodes and another for the triangles.  Here the nodes are re-emitted as treelets: starting at
+// a subtree root, sibling groups are taken breadth-first until the treelet holds `budget` nodes;
+// the groups left on the frontier start their own treelets right behind it, depth-first.  Sibling
+// groups stay contiguous, every node's triangle block moves with it.  PTC_TREELET = nodes per
+// treelet (0 keeps the breadth-first order).
+static void
+reorder_treelets(HostBvh& out)
+{
+  static const uint32_t budget = getenv("PTC_TREELET") ? (uint32_t)atoi(getenv("PTC_TREELET")) : 0u;
+  const uint32_t n = (uint32_t)out.nodes.size();
+  if (!budget || n < 2 * budget)
+    return;
+  std::vector<uint32_t> order; // new position -> old index
+  order.reserve(n);
+  order.push_back(0);
+  std::vector<uint32_t> pending{ 0 }; // old indices whose child group starts a treelet (LIFO)
+  std::vector<uint32_t> frontier, nextf;
+  while (!pending.empty()) {
+    const uint32_t root = pending.back();
+    pending.pop_back();
+    frontier.assign(1, root);
+    uint32_t taken = 0;
+    while (!frontier.empty()) {
+      nextf.clear();
+      size_t q = 0;
+      for (; q < frontier.size(); ++q) {
+        const Node8& nd = out.nodes[frontier[q]];
+        const uint32_t k = (uint32_t)__builtin_popcount(nd.imask);
+        if (!k)
+          continue;
+        if (taken && taken + k > budget)
+          break;
+        for (uint32_t c = 0; c < k; ++c) {
+          order.push_back(nd.child_base + c);
+          nextf.push_back(nd.child_base + c);
+        }
+        taken += k;
+      }
+      // what did not fit: roots of later treelets (reverse, so the first is handled next)
+      for (size_t r = frontier.size(); r > q; --r)
+        pending.push_back(frontier[r - 1]);
+      if (q < frontier.size()) {
+        for (size_t r = nextf.size(); r > 0; --r)
+          pending.push_back(nextf[r - 1]);
+        break;
+      }
+      frontier.swap(nextf);
+    }
+  }
+  std::vector<uint32_t> new_of(n);
+  for (uint32_t i = 0; i < n; ++i)
+    new_of[order[i]] = i;
+  std::vector<Node8> nodes(n);
+  std::vector<TriRecord> tris(out.tris.size());
+  std::vector<uint32_t> ids(out.face_ids.size());
+  uint32_t tri_top = 0;
+  for (uint32_t i = 0; i < n; ++i) {
+    Node8 nd = out.nodes[order[i]];
+    if (nd.imask)
+      nd.child_base = new_of[nd.child_base];
+    const uint32_t nt = (uint32_t)__builtin_popcount(nd.valid24);
+    for (uint32_t t = 0; t < nt; ++t) {
+      tris[tri_top + t] = out.tris[nd.tri_base + t];
+      ids[tri_top + t] = out.face_ids[nd.tri_base + t];
+    }
+    nd.tri_base = tri_top;
+    tri_top += nt;
+    nodes[i] = nd;
+  }
+  out.nodes.swap(nodes);
+  out.tris.swap(tris);
+  out.face_ids.swap(ids);
+}
+
 } // namespace
 
 void
@@ -630,8 +708,8 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
           const int k = P.kid_in_slot[sl];
           if (k < 0) { // empty slot: an inverted box (lo > hi) can never be hit
             for (int a = 0; a < 3; ++a) {
-              n.lo[a][sl] = half_of_byte(255);
-              n.hi[a][sl] = half_of_byte(0);
+              n.lo_q(a, sl) = half_of_byte(255);
+              n.hi_q(a, sl) = half_of_byte(0);
             }
             continue;
           }
@@ -646,8 +724,8 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
               ql -= 1.f;
             while (qh < 255.f && n.origin[a] + qh * sc < c.box.hi[a])
               qh += 1.f;
-            n.lo[a][sl] = half_of_byte((int)std::min(255.f, std::max(0.f, ql)));
-            n.hi[a][sl] = half_of_byte((int)std::min(255.f, std::max(0.f, qh)));
+            n.lo_q(a, sl) = half_of_byte((int)std::min(255.f, std::max(0.f, ql)));
+            n.hi_q(a, sl) = half_of_byte((int)std::min(255.f, std::max(0.f, qh)));
           }
           if (dp.is_leaf(P.kids[k])) {
             n.valid24 |= ((1u << c.count) - 1u) << (3 * sl); // 001, 011, 111
@@ -675,6 +753,7 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
     level.swap(next);
   }
   out.stats.wide_depth = depth;
+  reorder_treelets(out);
   if (timing)
     fprintf(stderr, "build_bvh: %u faces: binary SAH %.2f s, collapse DP %.2f s, emit %.2f s\n", n_faces,
             secs(t0, t1), secs(t1, t2), secs(t2, now()));

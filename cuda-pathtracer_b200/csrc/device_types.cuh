@@ -79,6 +79,10 @@ struct Counters // device mirror of the ray-count part of ptc_counters
   unsigned long long rays_per_bounce[16];
   unsigned long long nodes_visited;
   unsigned long long tris_tested;
+  // statistics build of the extend kernel only (ptc_profile.extend_lanes): warp iterations of the
+  // traversal loop, and summed over them the lanes that held a ray, ran the node test, ran a
+  // first / a second triangle test
+  unsigned long long ext_iters, ext_have, ext_node, ext_tri1, ext_tri2;
 };
 
 struct FrameParams
@@ -115,6 +119,9 @@ struct FrameOut
   float* accum;         // float3 per band pixel, rows bottom-up inside the band (raytrace.cu:252)
   uint32_t* out_rgba;   // RGBA8 per band pixel, row 0 = top; may be null
   float* radiance_out;  // optional un-clamped radiance of this sample, top-down; may be null
+  uint32_t out_full;    // out_rgba is a FULL width x height image (PTC_OUT_FULL_IMAGE): a pixel goes to
+                        // its GLOBAL row -- the image may live on another GPU (peer / IPC mapping), which
+                        // is how image tiles are assembled without a collective
 };
 
 } // namespace ptc

@@ -133,57 +133,46 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
     }
 
     bool done = !valid;
-    if (FIRST && !fp.is_static) {
-      // preview frame (camera moved): one ray, flat colour, raytrace.cu:54-62
-      if (valid) {
-        float t, u, v;
-        uint32_t id;
-        closest_hit<STATS>(sc, stack, P.origin, P.dir, t, id, u, v, my_nodes, my_tris);
-        if (id != 0xFFFFFFFFu) {
-          Surface s;
-          resolve_hit(sc, id, t, u, v, P.dir, P.spec_carry, s);
-          P.acc = s.diffuse_col;
+    // preview frame (camera moved, raytrace.cu:54-62): one ray, flat colour -- runs through the same
+    // loop (frame_schedule gives it one iteration) so that the kernel holds ONE traversal instance
+    const bool preview = FIRST && !fp.is_static;
+    for (int it = 0; it < n_iters; ++it) {
+      const uint32_t active = __ballot_sync(0xFFFFFFFFu, !done);
+      if (!active)
+        break;
+      const int b = bounce0 + it;
+      if (lane == 0)
+        atomicAdd(&s_rays[b < 16 ? b : 15], (uint32_t)__popc(active));
+      if (!done) {
+        float t, u = 0.f, v = 0.f;
+        uint32_t id, segs;
+        const bool last = !preview && b + 1 >= fp.max_bounces; // nothing after this iteration: any-hit query
+        if (HITS) {
+          const uint4 h = __ldcs(hits + i);
+          t = __uint_as_float(h.x), id = h.y, u = __uint_as_float(h.z), v = __uint_as_float(h.w);
+          if (!last)
+            lights_hit(sc, P.origin, P.dir, t, id);
         } else {
-          P.acc = env_lookup(cube, P.dir);
+          trace_ray<STATS>(sc, stack, P.origin, P.dir, last, t, id, u, v, my_nodes, my_tris);
         }
-        my_segs++, my_traced++;
-        done = true;
-      }
-      const uint32_t m = __ballot_sync(0xFFFFFFFFu, valid);
-      if (lane == 0 && m)
-        atomicAdd(&s_rays[0], (uint32_t)__popc(m));
-    } else {
-      for (int it = 0; it < n_iters; ++it) {
-        const uint32_t active = __ballot_sync(0xFFFFFFFFu, !done);
-        if (!active)
-          break;
-        const int b = bounce0 + it;
-        if (lane == 0)
-          atomicAdd(&s_rays[b < 16 ? b : 15], (uint32_t)__popc(active));
-        if (!done) {
-          float t, u, v;
-          uint32_t id, segs;
-          const bool last = b + 1 >= fp.max_bounces; // nothing after this iteration: any-hit query
-          if (HITS) {
-            const uint4 h = __ldcs(hits + i);
-            t = __uint_as_float(h.x), id = h.y, u = __uint_as_float(h.z), v = __uint_as_float(h.w);
-            if (!last)
-              lights_hit(sc, P.origin, P.dir, t, id);
-          } else if (last) {
-            u = v = 0.f;
-            last_hit<STATS>(sc, stack, P.origin, P.dir, t, id, my_nodes, my_tris);
+        if (preview) {
+          if (id != 0xFFFFFFFFu) {
+            Surface s;
+            resolve_hit(sc, id, t, u, v, P.dir, P.spec_carry, s);
+            P.acc = s.diffuse_col;
           } else {
-            closest_hit<STATS>(sc, stack, P.origin, P.dir, t, id, u, v, my_nodes, my_tris);
+            P.acc = env_lookup(cube, P.dir);
           }
-          if (last && id < sc.n_faces) {
-            done = true; // a triangle in front on the last iteration adds no radiance
-            segs = 1;
-          } else {
-            done = shade_step(fp, sc, cube, P, rng, t, id, u, v, b, segs);
-          }
-          my_segs += segs;
-          my_traced++;
+          done = true;
+          segs = 1;
+        } else if (last && id < sc.n_faces) {
+          done = true; // a triangle in front on the last iteration adds no radiance
+          segs = 1;
+        } else {
+          done = shade_step(fp, sc, cube, P, rng, t, id, u, v, b, segs);
         }
+        my_segs += segs;
+        my_traced++;
       }
     }
 
@@ -379,10 +368,7 @@ k_wave(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
     uint32_t id = 0xFFFFFFFFu;
     if (!done) {
       my_traced++;
-      if (last)
-        last_hit<STATS>(sc, stack, P.origin, P.dir, t, id, my_nodes, my_tris);
-      else
-        closest_hit<STATS>(sc, stack, P.origin, P.dir, t, id, u, v, my_nodes, my_tris);
+      trace_ray<STATS>(sc, stack, P.origin, P.dir, last, t, id, u, v, my_nodes, my_tris);
       if (last && id < sc.n_faces) {
         done = true; // a triangle in front on the last iteration adds no radiance
         my_segs++;
@@ -475,6 +461,9 @@ k_wave(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
 #ifndef PTC_EXTEND_BLOCKS
 #define PTC_EXTEND_BLOCKS 3
 #endif
+#ifndef PTC_TRI_BATCH
+#define PTC_TRI_BATCH 0
+#endif
 template <bool STATS>
 __global__ void __launch_bounds__(kBlock, PTC_EXTEND_BLOCKS)
 k_extend(const DScene sc, const RayQueue qin, const uint32_t* __restrict__ qin_count,
@@ -500,6 +489,7 @@ k_extend(const DScene sc, const RayQueue qin, const uint32_t* __restrict__ qin_c
   Trav T;
   bool have = false, exhausted = false;
   uint32_t slot = 0, my_nodes = 0, my_tris = 0;
+  unsigned long long st_iters = 0, st_have = 0, st_node = 0, st_tri1 = 0, st_tri2 = 0;
 
   for (;;) {
     const uint32_t idle = __ballot_sync(0xFFFFFFFFu, !have);
@@ -527,10 +517,18 @@ k_extend(const DScene sc, const RayQueue qin, const uint32_t* __restrict__ qin_c
       if (!__any_sync(0xFFFFFFFFu, have))
         break;
     }
-    if (have && trav_step<STATS, decltype(stack), true>(sc, T, stack, my_nodes, my_tris)) {
+    const uint32_t n_before = my_nodes, t_before = my_tris;
+    const bool had = have;
+    if (have && trav_step<STATS, decltype(stack), true, PTC_PREFETCH_NODE, PTC_TRI_BATCH != 0>(sc, T, stack, my_nodes, my_tris)) {
       __stcs(hits + slot, make_uint4(__float_as_uint(T.best_t), T.best_id, __float_as_uint(T.best_u),
                                      __float_as_uint(T.best_v)));
       have = false;
+    }
+    if (STATS) { // where the lanes of a warp iteration go (lane 0 keeps the sums)
+      const uint32_t mh = __ballot_sync(0xFFFFFFFFu, had), mn = __ballot_sync(0xFFFFFFFFu, my_nodes != n_before);
+      const uint32_t m1 = __ballot_sync(0xFFFFFFFFu, my_tris != t_before);
+      const uint32_t m2 = __ballot_sync(0xFFFFFFFFu, my_tris - t_before > 1u);
+      st_iters++, st_have += __popc(mh), st_node += __popc(mn), st_tri1 += __popc(m1), st_tri2 += __popc(m2);
     }
   }
   if (STATS) {
@@ -538,6 +536,13 @@ k_extend(const DScene sc, const RayQueue qin, const uint32_t* __restrict__ qin_c
     if (lane == 0 && (wn | wt)) {
       atomicAdd(&ctr->nodes_visited, (unsigned long long)wn);
       atomicAdd(&ctr->tris_tested, (unsigned long long)wt);
+    }
+    if (lane == 0 && st_iters) {
+      atomicAdd(&ctr->ext_iters, st_iters);
+      atomicAdd(&ctr->ext_have, st_have);
+      atomicAdd(&ctr->ext_node, st_node);
+      atomicAdd(&ctr->ext_tri1, st_tri1);
+      atomicAdd(&ctr->ext_tri2, st_tri2);
     }
   }
 }

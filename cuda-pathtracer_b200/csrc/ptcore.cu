@@ -16,6 +16,7 @@
 #include "bvh.h"
 #include "kernels.cuh"
 #include "ptcore.h"
+#include "ptcore_internal.h"
 
 using namespace ptc;
 
@@ -56,7 +57,7 @@ struct ptc_context
   uint32_t first_iters = 0, next_iters = 1; // first_iters 0 = per scene (frame_schedule) // wavefront granularity (ptc_set_wavefront)
   int32_t split_extend = -1;   // form of the stages: 0 fused, 1 refilling extend kernel + shade kernel, 2 shifted (k_wave), -1 = per scene
   int wave_small = 0;          // automatic choice for L1-resident scenes: 1 shifted, 0 fused; PTC_WAVE overrides (experiments)
-  uint32_t refill = 12;        // idle lanes of a warp that trigger a refill in k_extend
+  uint32_t refill = 12;        // idle lanes of a warp that trigger a refill in k_extend (kDefaultRefill)
   uint4* hits = nullptr;       // closest triangle hit per queue slot (split stages; shifted stages: even queue)
   uint4* hits2 = nullptr;      // shifted stages: hit records of the odd queue
   float4* done = nullptr;      // (radiance, pixel) of paths that finished before the last stage
@@ -73,6 +74,18 @@ struct ptc_context
   uint32_t* h_out_dev = nullptr;
   float* h_rad_dev = nullptr;
   size_t h_px = 0;
+  // whose samples the staged device accumulator holds: host buffer, scene and band geometry of the
+  // last host-buffer call.  A call for anything else re-seeds it from the caller's buffer.
+  struct StagingOwner
+  {
+    const void* accum = nullptr;
+    int32_t scene_id = -1;
+    uint32_t geom[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    bool operator==(const StagingOwner& o) const
+    {
+      return accum == o.accum && scene_id == o.scene_id && !memcmp(geom, o.geom, sizeof(geom));
+    }
+  } h_owner;
   // pipelined host call: second device frame + copy stream so the device->host copy of
   // frame k overlaps the rendering of frame k+1
   uint32_t* h_out_dev2 = nullptr;
@@ -85,6 +98,7 @@ struct ptc_context
 namespace {
 
 constexpr int kMaxBounces = 64;
+constexpr uint32_t kDefaultRefill = 12;
 // queue counters, then 2 work counters per step; the last two slots: parked-pixel count and the
 // work counter of their drain (kernels.cuh, kDoneDefer / kDoneDrain)
 constexpr int kCountSlots = 3 * (kMaxBounces + 2);
@@ -119,6 +133,40 @@ struct DeviceGuard
   {
     if (prev >= 0)
       cudaSetDevice(prev);
+  }
+};
+
+// Temporary device buffer of the parity / measurement entry points: freed on every return path.
+struct DevBuf
+{
+  void* p = nullptr;
+  ~DevBuf() { cudaFree(p); }
+  cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 16); }
+  template <typename T>
+  T* as() const
+  {
+    return (T*)p;
+  }
+};
+
+struct EventList
+{
+  std::vector<cudaEvent_t> ev;
+  ~EventList()
+  {
+    for (cudaEvent_t e : ev)
+      if (e)
+        cudaEventDestroy(e);
+  }
+  cudaError_t create(size_t n)
+  {
+    ev.assign(n, nullptr);
+    for (cudaEvent_t& e : ev) {
+      cudaError_t rc = cudaEventCreate(&e);
+      if (rc != cudaSuccess)
+        return rc;
+    }
+    return cudaSuccess;
   }
 };
 
@@ -289,7 +337,8 @@ frame_schedule(const ptc_context* ctx, const FrameParams& fp, size_t bvh_bytes, 
   const bool small = bvh_bytes <= (64u << 10);
   const bool split = ctx->split_extend >= 0 ? ctx->split_extend == 1 : !small;
   // shifted form (k_wave, kernels.cu): stage k intersects iteration k and shades iteration k-1, so
-  // that only rays that hit are queued and shaded -- the L1-resident scenes' default
+  // that only rays that hit are queued and shaded.  Selectable (split_extend = 2, or PTC_WAVE=1 for
+  // the L1-resident scenes), NOT a default: it measured 0.2-4 % behind the fused form
   const bool wave = fp.is_static && (ctx->split_extend >= 0 ? ctx->split_extend == 2 : small && ctx->wave_small);
   if (split_out)
     *split_out = split;
@@ -395,6 +444,16 @@ enqueue_part(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp, 
   return 0;
 }
 
+// Pipelines a frame of this size is rendered as by ptc_render (see enqueue_frame).
+uint32_t
+frame_pipelines(const ptc_context* ctx, const FrameParams& fp)
+{
+  const uint32_t n = fp.band_rows * fp.width;
+  uint32_t parts = ctx->dual && fp.is_static && n >= (1u << 18) ? (uint32_t)ctx->dual + 1u : 1u;
+  const uint32_t strips = (fp.band_rows + 15u) / 16u;
+  return parts > strips ? strips : parts;
+}
+
 // Enqueues one frame; accum/out/rad are device pointers.  Profiling calls (stats / ev) run
 // the frame as one pipeline; otherwise a frame of at least 256 K pixels runs as two halves
 // (whole 16-row strips) on the caller's stream and an internal one, joined before returning
@@ -408,14 +467,12 @@ enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp_
   int rc = ensure_capacity(ctx, n);
   if (rc)
     return rc;
-  const FrameOut fo{ accum, out, rad };
+  const FrameOut fo{ accum, out, rad, (a->flags & PTC_OUT_FULL_IMAGE) ? 1u : 0u };
   Lane A{ { ctx->queue[0], ctx->queue[1] }, ctx->hits, ctx->hits2, ctx->done, ctx->counts };
   fp.part_row0 = 0;
   fp.part_rows = fp.band_rows;
-  int parts = ctx->dual && !stats && !ev && fp.is_static && n >= (1u << 18) ? ctx->dual + 1 : 1;
   const uint32_t strips = (fp.band_rows + 15u) / 16u;
-  if ((uint32_t)parts > strips)
-    parts = (int)strips;
+  const int parts = stats || ev ? 1 : (int)frame_pipelines(ctx, fp);
   if (parts <= 1)
     return enqueue_part(ctx, a, fp, fo, s, A, stats, ev);
 
@@ -450,10 +507,20 @@ enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp_
 }
 
 // Device-side staging of the host-buffer calls (accumulator, two RGBA8 frames, radiance).
+// `fresh` is set when the staged accumulator does not hold the samples of THIS caller buffer /
+// scene / band (first call, new size, or a different owner with the same pixel count -- e.g. rows
+// 0-540 then 540-1080): the caller's accumulator must then be uploaded first.
 int
-ensure_staging(ptc_context* ctx, size_t n, bool& fresh)
+ensure_staging(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp, size_t n, bool& fresh)
 {
-  fresh = false;
+  ptc_context::StagingOwner who;
+  who.accum = a->accum;
+  who.scene_id = a->scene_id;
+  const uint32_t g[8] = { fp.width, fp.height, fp.row_begin, fp.band_rows, fp.strip_rows, fp.strip_stride,
+                          fp.strip_phase, 0u };
+  memcpy(who.geom, g, sizeof(g));
+  fresh = !(who == ctx->h_owner);
+  ctx->h_owner = who;
   if (n == ctx->h_px)
     return 0;
   cudaFree(ctx->h_accum_dev);
@@ -573,33 +640,83 @@ ptc_upload_scene(ptc_context* ctx, const ptc_scene_desc* desc, int32_t* scene_id
 {
   if (!ctx || !desc || !scene_id)
     return PTC_ERR_INVALID;
-  DeviceGuard g(ctx->device);
+  PreparedScene ps;
+  std::string err;
+  int rc = prepare_scene(desc, ps, err);
+  if (rc)
+    return fail(ctx, rc, err);
+  return upload_prepared(ctx, desc, ps, scene_id);
+}
+
+} // extern "C"
+
+namespace ptc {
+
+int
+context_device(const ptc_context* ctx)
+{
+  return ctx->device;
+}
+
+int
+prepare_scene(const ptc_scene_desc* desc, PreparedScene& ps, std::string& err)
+{
   uint32_t n_faces = 0;
   for (uint32_t m = 0; m < desc->n_meshes; ++m)
     n_faces += desc->mesh_face_counts[m];
   for (uint32_t f = 0; f < n_faces; ++f)
-    if (desc->faces[f].material_id >= desc->n_materials)
-      return fail(ctx, PTC_ERR_INVALID, "face references a material outside the table");
+    if (desc->faces[f].material_id >= desc->n_materials) {
+      err = "face references a material outside the table";
+      return PTC_ERR_INVALID;
+    }
   for (uint32_t i = 0; i < desc->n_materials; ++i) {
     const ptc_material& m = desc->materials[i];
     if (m.diffuse_spec_map < 0 || (uint32_t)m.diffuse_spec_map >= desc->n_textures ||
-        m.normal_map >= (int32_t)desc->n_textures)
-      return fail(ctx, PTC_ERR_INVALID, "material references a texture outside the table");
-    if (desc->textures[m.diffuse_spec_map].nb_chan != 4)
-      return fail(ctx, PTC_ERR_INVALID, "diffuse/specular texture must have 4 channels");
-    if (m.normal_map >= 0 && desc->textures[m.normal_map].nb_chan != 3)
-      return fail(ctx, PTC_ERR_INVALID, "normal map must have 3 channels");
+        m.normal_map >= (int32_t)desc->n_textures) {
+      err = "material references a texture outside the table";
+      return PTC_ERR_INVALID;
+    }
+    if (desc->textures[m.diffuse_spec_map].nb_chan != 4) {
+      err = "diffuse/specular texture must have 4 channels";
+      return PTC_ERR_INVALID;
+    }
+    if (m.normal_map >= 0 && desc->textures[m.normal_map].nb_chan != 3) {
+      err = "normal map must have 3 channels";
+      return PTC_ERR_INVALID;
+    }
   }
+  ps.n_faces = n_faces;
+  build_bvh(desc, ps.bvh);
+  if ((int)ps.bvh.stats.wide_depth + 1 > kStackSize - kTriBacklog) {
+    err = "BVH too deep for the traversal stack";
+    return PTC_ERR_INVALID;
+  }
+  build_shade_records(desc, ps.shade);
+  return PTC_OK;
+}
 
-  HostBvh bvh;
-  build_bvh(desc, bvh);
-  if ((int)bvh.stats.wide_depth + 1 > kStackSize - kTriBacklog)
-    return fail(ctx, PTC_ERR_INVALID, "BVH too deep for the traversal stack");
-  std::vector<ShadeRecord> shade;
-  build_shade_records(desc, shade);
+int
+upload_prepared(ptc_context* ctx, const ptc_scene_desc* desc, const PreparedScene& ps, int32_t* scene_id)
+{
+  DeviceGuard g(ctx->device);
+  const HostBvh& bvh = ps.bvh;
+  const std::vector<ShadeRecord>& shade = ps.shade;
+  const uint32_t n_faces = ps.n_faces;
 
-  ctx->scenes.emplace_back();
-  SceneDev& s = ctx->scenes.back();
+  // built into a local record and published only when everything succeeded: a failed upload
+  // leaves no half-initialised scene behind a valid scene id (and frees what it allocated)
+  SceneDev s;
+  struct Rollback
+  {
+    SceneDev& s;
+    bool armed = true;
+    ~Rollback()
+    {
+      if (armed)
+        for (void* p : s.allocs)
+          cudaFree(p);
+    }
+  } rollback{ s };
   int rc;
   const Node8* d_nodes;
   const TriRecord* d_tris;
@@ -682,9 +799,15 @@ ptc_upload_scene(ptc_context* ctx, const ptc_scene_desc* desc, int32_t* scene_id
   s.info.shade_bytes = sizeof(ShadeRecord);
   s.info.texture_bytes = total;
   s.info.smem_resident = 0;
+  rollback.armed = false;
+  ctx->scenes.push_back(std::move(s));
   *scene_id = (int32_t)ctx->scenes.size() - 1;
   return PTC_OK;
 }
+
+} // namespace ptc
+
+extern "C" {
 
 int
 ptc_scene_info_get(const ptc_context* ctx, int32_t scene_id, ptc_scene_info* out)
@@ -742,7 +865,9 @@ ptc_cubemap_faces_from_cross(const float* cross, uint32_t w, uint32_t h, uint32_
     *used_fallback = (cross && !usable) ? 1 : 0;
   if (!usable) {
     // createUnitTexture (gpu_processor.cpp:38-58): six 1x1 faces of one colour, alpha 0
-    const uint32_t color = (cross || !rgb_hex) ? 0x131b23u : rgb_hex;
+    // a cross that fails the checks, or no colour given: the reference's default 0x131b23
+    // (gpu_processor.cpp:75,99-105,128-132); "0x000000" in a scene file is black (:88-93)
+    const uint32_t color = (cross || rgb_hex == PTC_CUBEMAP_DEFAULT_COLOR) ? 0x131b23u : (rgb_hex & 0xFFFFFFu);
     if (capacity < 24)
       return PTC_ERR_INVALID;
     for (int f = 0; f < 6; ++f) {
@@ -985,7 +1110,7 @@ ptc_render_host(ptc_context* ctx, const ptc_render_args* args, int upload_accum,
   const size_t n = (size_t)fp.band_rows * fp.width;
   cudaStream_t s = (cudaStream_t)args->stream;
   bool fresh = false;
-  rc = ensure_staging(ctx, n, fresh);
+  rc = ensure_staging(ctx, args, fp, n, fresh);
   if (rc)
     return rc;
   if (fresh)
@@ -1028,7 +1153,7 @@ ptc_render_host_async(ptc_context* ctx, const ptc_render_args* args, int upload_
     }
   }
   bool fresh = false;
-  rc = ensure_staging(ctx, n, fresh);
+  rc = ensure_staging(ctx, args, fp, n, fresh);
   if (rc)
     return rc;
   if (fresh || upload_accum)
@@ -1137,6 +1262,7 @@ ptc_set_wavefront(ptc_context* ctx, uint32_t first_iters, uint32_t next_iters, i
     ctx->first_iters = 0; // automatic (per scene size) ...
     ctx->split_extend = -1; // ... for the whole schedule
     ctx->next_iters = 1;
+    ctx->refill = kDefaultRefill; // ... including the measured refill threshold
   } else if (first_iters)
     ctx->first_iters = first_iters;
   if (next_iters)
@@ -1155,8 +1281,6 @@ ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeat
   int rc = fill_frame(ctx, args, fp, false);
   if (rc)
     return rc;
-  if (!args->accum)
-    return fail(ctx, PTC_ERR_INVALID, "accum is required");
   cudaStream_t s = (cudaStream_t)args->stream;
   Step steps[kMaxBounces + 2];
   bool split = false, wave = false;
@@ -1177,34 +1301,50 @@ ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeat
       launches.push_back({ 1u, (uint32_t)steps[k].bounce0, (uint32_t)steps[k].n_iters });
   }
   const int n_l = (int)launches.size();
-  std::vector<cudaEvent_t> ev((size_t)(n_l + 1) * repeats);
-  for (cudaEvent_t& e : ev)
-    CUDA_TRY(ctx, cudaEventCreate(&e));
+  EventList evl, evf;
+  CUDA_TRY(ctx, evl.create((size_t)(n_l + 1) * repeats));
+  CUDA_TRY(ctx, evf.create(2));
+  std::vector<cudaEvent_t>& ev = evl.ev;
+  // every pass renders into SCRATCH buffers: the caller's accumulator and image are not touched
+  // (repeating one sample number into a live accumulator would bias it)
+  const size_t n_px = (size_t)fp.band_rows * fp.width;
+  DevBuf b_acc, b_out;
+  CUDA_TRY(ctx, b_acc.alloc(n_px * 12));
+  CUDA_TRY(ctx, b_out.alloc(n_px * 4));
+  CUDA_TRY(ctx, cudaMemsetAsync(b_acc.p, 0, n_px * 12, s));
+  float* accum = b_acc.as<float>();
+  uint32_t* out_rgba = b_out.as<uint32_t>();
   // statistics pass (untimed): ray counts and BVH node / triangle visits of this frame
   Counters before, after;
   CUDA_TRY(ctx, cudaStreamSynchronize(s));
   CUDA_TRY(ctx, cudaMemcpy(&before, ctx->ctr, sizeof(before), cudaMemcpyDeviceToHost));
-  rc = enqueue_frame(ctx, args, fp, (float*)args->accum, (uint32_t*)args->out_rgba, nullptr, s, true);
+  rc = enqueue_frame(ctx, args, fp, accum, out_rgba, nullptr, s, true);
   if (rc)
     return rc;
   CUDA_TRY(ctx, cudaStreamSynchronize(s));
   CUDA_TRY(ctx, cudaMemcpy(&after, ctx->ctr, sizeof(after), cudaMemcpyDeviceToHost));
   std::vector<uint32_t> counts(kMaxBounces + 2);
   CUDA_TRY(ctx, cudaMemcpy(counts.data(), ctx->counts, counts.size() * 4, cudaMemcpyDeviceToHost));
+  // the statistics pass must not show up in the caller's ray counters
+  CUDA_TRY(ctx, cudaMemcpy(ctx->ctr, &before, sizeof(before), cudaMemcpyHostToDevice));
   out->traced = after.traced - before.traced;
   out->segments = after.segments - before.segments;
   out->nodes_visited = after.nodes_visited - before.nodes_visited;
   out->tris_tested = after.tris_tested - before.tris_tested;
   for (int i = 0; i < 16; ++i)
     out->rays_per_bounce[i] = after.rays_per_bounce[i] - before.rays_per_bounce[i];
+  out->extend_lanes[0] = after.ext_iters - before.ext_iters;
+  out->extend_lanes[1] = after.ext_have - before.ext_have;
+  out->extend_lanes[2] = after.ext_node - before.ext_node;
+  out->extend_lanes[3] = after.ext_tri1 - before.ext_tri1;
+  out->extend_lanes[4] = after.ext_tri2 - before.ext_tri2;
   for (int k = 1; k < n_steps; ++k)
     out->queue_rays += counts[k];
   out->queue_bytes_per_ray = 4 * sizeof(float4);
   out->hit_bytes_per_ray = split || wave ? (uint32_t)sizeof(uint4) : 0u;
-  // timed passes
+  // timed passes, one pipeline, an event after every launch
   for (uint32_t r = 0; r < repeats; ++r) {
-    rc = enqueue_frame(ctx, args, fp, (float*)args->accum, (uint32_t*)args->out_rgba, nullptr, s, false,
-                       ev.data() + (size_t)r * (n_l + 1));
+    rc = enqueue_frame(ctx, args, fp, accum, out_rgba, nullptr, s, false, ev.data() + (size_t)r * (n_l + 1));
     if (rc)
       return rc;
   }
@@ -1229,8 +1369,19 @@ ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeat
     total += ms;
   }
   out->frame_ms = total / repeats;
-  for (cudaEvent_t& e : ev)
-    cudaEventDestroy(e);
+  // the frame as ptc_render ships it (half-frame pipelines on two streams), `repeats` frames back to back
+  CUDA_TRY(ctx, cudaEventRecord(evf.ev[0], s));
+  for (uint32_t r = 0; r < repeats; ++r) {
+    rc = enqueue_frame(ctx, args, fp, accum, out_rgba, nullptr, s);
+    if (rc)
+      return rc;
+  }
+  CUDA_TRY(ctx, cudaEventRecord(evf.ev[1], s));
+  CUDA_TRY(ctx, cudaStreamSynchronize(s));
+  float shipped = 0.f;
+  cudaEventElapsedTime(&shipped, evf.ev[0], evf.ev[1]);
+  out->frame_ms_shipped = shipped / repeats;
+  out->pipelines = frame_pipelines(ctx, fp);
   return PTC_OK;
 }
 
@@ -1256,21 +1407,16 @@ ptc_trace_primary(ptc_context* ctx, int32_t scene_id, const ptc_camera* camera, 
   fp.max_bounces = 1;
   fp.is_static = 1;
   const uint32_t n = width * height;
-  int32_t* d_ids = nullptr;
-  float* d_t = nullptr;
-  CUDA_TRY(ctx, cudaMalloc(&d_ids, (size_t)n * 4));
-  CUDA_TRY(ctx, cudaMalloc(&d_t, (size_t)n * 4));
-  launch_primary_hits(fp, ctx->scenes[scene_id].d, d_ids, d_t, 0);
+  DevBuf b_ids, b_t;
+  CUDA_TRY(ctx, b_ids.alloc((size_t)n * 4));
+  CUDA_TRY(ctx, b_t.alloc((size_t)n * 4));
+  launch_primary_hits(fp, ctx->scenes[scene_id].d, b_ids.as<int32_t>(), b_t.as<float>(), 0);
   ctx->launches++;
-  cudaError_t e = cudaDeviceSynchronize();
-  if (e == cudaSuccess && hit_ids)
-    e = cudaMemcpy(hit_ids, d_ids, (size_t)n * 4, cudaMemcpyDeviceToHost);
-  if (e == cudaSuccess && t)
-    e = cudaMemcpy(t, d_t, (size_t)n * 4, cudaMemcpyDeviceToHost);
-  cudaFree(d_ids);
-  cudaFree(d_t);
-  if (e != cudaSuccess)
-    return fail(ctx, (int)e, cudaGetErrorString(e));
+  CUDA_TRY(ctx, cudaDeviceSynchronize());
+  if (hit_ids)
+    CUDA_TRY(ctx, cudaMemcpy(hit_ids, b_ids.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  if (t)
+    CUDA_TRY(ctx, cudaMemcpy(t, b_t.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
   return PTC_OK;
 }
 
@@ -1283,27 +1429,21 @@ ptc_intersect_rays(ptc_context* ctx, int32_t scene_id, const float* origins, con
   if (!n)
     return PTC_OK;
   DeviceGuard g(ctx->device);
-  float *d_o = nullptr, *d_d = nullptr, *d_t = nullptr;
-  int32_t* d_i = nullptr;
-  CUDA_TRY(ctx, cudaMalloc(&d_o, n * 12));
-  CUDA_TRY(ctx, cudaMalloc(&d_d, n * 12));
-  CUDA_TRY(ctx, cudaMalloc(&d_i, n * 4));
-  CUDA_TRY(ctx, cudaMalloc(&d_t, n * 4));
-  cudaError_t e = cudaMemcpy(d_o, origins, n * 12, cudaMemcpyHostToDevice);
-  if (e == cudaSuccess)
-    e = cudaMemcpy(d_d, dirs, n * 12, cudaMemcpyHostToDevice);
-  if (e == cudaSuccess) {
-    launch_intersect_rays(ctx->scenes[scene_id].d, d_o, d_d, n, d_i, d_t, ctx->ctr, 0);
-    ctx->launches++;
-    e = cudaDeviceSynchronize();
-  }
-  if (e == cudaSuccess && hit_ids)
-    e = cudaMemcpy(hit_ids, d_i, n * 4, cudaMemcpyDeviceToHost);
-  if (e == cudaSuccess && t)
-    e = cudaMemcpy(t, d_t, n * 4, cudaMemcpyDeviceToHost);
-  cudaFree(d_o), cudaFree(d_d), cudaFree(d_i), cudaFree(d_t);
-  if (e != cudaSuccess)
-    return fail(ctx, (int)e, cudaGetErrorString(e));
+  DevBuf b_o, b_d, b_i, b_t;
+  CUDA_TRY(ctx, b_o.alloc(n * 12));
+  CUDA_TRY(ctx, b_d.alloc(n * 12));
+  CUDA_TRY(ctx, b_i.alloc(n * 4));
+  CUDA_TRY(ctx, b_t.alloc(n * 4));
+  CUDA_TRY(ctx, cudaMemcpy(b_o.p, origins, n * 12, cudaMemcpyHostToDevice));
+  CUDA_TRY(ctx, cudaMemcpy(b_d.p, dirs, n * 12, cudaMemcpyHostToDevice));
+  launch_intersect_rays(ctx->scenes[scene_id].d, b_o.as<float>(), b_d.as<float>(), n, b_i.as<int32_t>(),
+                        b_t.as<float>(), ctx->ctr, 0);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaDeviceSynchronize());
+  if (hit_ids)
+    CUDA_TRY(ctx, cudaMemcpy(hit_ids, b_i.p, n * 4, cudaMemcpyDeviceToHost));
+  if (t)
+    CUDA_TRY(ctx, cudaMemcpy(t, b_t.p, n * 4, cudaMemcpyDeviceToHost));
   return PTC_OK;
 }
 
@@ -1355,23 +1495,16 @@ ptc_debug_rng(ptc_context* ctx, const uint32_t* seeds, uint32_t n_seeds, uint32_
   if (!ctx || !seeds || !out || !n_seeds || !n_draws)
     return PTC_ERR_INVALID;
   DeviceGuard g(ctx->device);
-  uint32_t* d_s = nullptr;
-  float* d_o = nullptr;
-  CUDA_TRY(ctx, cudaMalloc(&d_s, (size_t)n_seeds * 4));
-  CUDA_TRY(ctx, cudaMalloc(&d_o, (size_t)n_seeds * n_draws * 4));
-  cudaError_t e = cudaMemcpy(d_s, seeds, (size_t)n_seeds * 4, cudaMemcpyHostToDevice);
-  if (e == cudaSuccess) {
-    if (reference_impl)
-      launch_debug_curand(d_s, n_seeds, n_draws, d_o, 0);
-    else
-      launch_debug_rng(d_s, n_seeds, n_draws, d_o, 0);
-    e = cudaDeviceSynchronize();
-  }
-  if (e == cudaSuccess)
-    e = cudaMemcpy(out, d_o, (size_t)n_seeds * n_draws * 4, cudaMemcpyDeviceToHost);
-  cudaFree(d_s), cudaFree(d_o);
-  if (e != cudaSuccess)
-    return fail(ctx, (int)e, cudaGetErrorString(e));
+  DevBuf b_s, b_o;
+  CUDA_TRY(ctx, b_s.alloc((size_t)n_seeds * 4));
+  CUDA_TRY(ctx, b_o.alloc((size_t)n_seeds * n_draws * 4));
+  CUDA_TRY(ctx, cudaMemcpy(b_s.p, seeds, (size_t)n_seeds * 4, cudaMemcpyHostToDevice));
+  if (reference_impl)
+    launch_debug_curand(b_s.as<uint32_t>(), n_seeds, n_draws, b_o.as<float>(), 0);
+  else
+    launch_debug_rng(b_s.as<uint32_t>(), n_seeds, n_draws, b_o.as<float>(), 0);
+  CUDA_TRY(ctx, cudaDeviceSynchronize());
+  CUDA_TRY(ctx, cudaMemcpy(out, b_o.p, (size_t)n_seeds * n_draws * 4, cudaMemcpyDeviceToHost));
   return PTC_OK;
 }
 

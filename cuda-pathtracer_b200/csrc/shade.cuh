@@ -279,7 +279,8 @@ epilogue(const FrameParams& fp, const FrameOut& fo, uint32_t x, uint32_t lrow, f
   rad = post_process(rad, fp.post_id);
   const uint32_t R = (uint32_t)(rad.x * 255) & 0xFFu, G = (uint32_t)(rad.y * 255) & 0xFFu,
                  B = (uint32_t)(rad.z * 255) & 0xFFu;
-  __stcs(fo.out_rgba + p, R | (G << 8) | (B << 16)); // a = 0, raytrace.cu:232
+  const size_t po = fo.out_full ? (size_t)global_row(fp, lrow) * fp.width + x : p;
+  __stcs(fo.out_rgba + po, R | (G << 8) | (B << 16)); // a = 0, raytrace.cu:232
 }
 
 } // namespace ptc

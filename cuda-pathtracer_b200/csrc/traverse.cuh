@@ -13,6 +13,12 @@
 
 namespace ptc {
 
+// node layout: 0 = lo[3][8], hi[3][8] (six 16-byte plane loads addressed by ray octant),
+// 1 = [axis][lo | hi][8] (three 32-byte loads + register selects); must match bvh_builder.cpp
+#ifndef PTC_NODE_LAYOUT
+#define PTC_NODE_LAYOUT 1
+#endif
+
 // ---------------------------------------------------------------------------
 // cuRAND XORWOW, restated (curand_kernel.h:772-799 init with subsequence = offset = 0,
 // :863-874 step, curand_uniform.h:69-72).  State is 6 words, carried per path.
@@ -295,7 +301,9 @@ struct Trav
 {
   float3 o, d, idir;
   uint32_t oct, oct_inv;
+#if PTC_NODE_LAYOUT == 0
   uint32_t vnx, vny, vnz; // uint4 index (inside a node) of the near plane set per axis
+#endif
   uint2 ng; // node group: first child index, 8 hit bits (31..24) | imask (7..0)
   uint2 tg; // triangle group: tri_base, valid24 of its node
   uint32_t tmask; // triangles of tg still to test (bits of the node's 24-bit triangle space)
@@ -323,9 +331,11 @@ trav_init(Trav& T, const float3 o, const float3 d)
                1.0f / (fabsf(d.z) > eps ? d.z : copysignf(eps, d.z)));
   T.oct = (d.x < 0.f ? 1u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 4u : 0u);
   T.oct_inv = 7u - T.oct;
+#if PTC_NODE_LAYOUT == 0
   T.vnx = d.x < 0.f ? 5u : 2u; // lo planes at 2,3,4 / hi planes at 5,6,7 (bvh.h)
   T.vny = d.y < 0.f ? 6u : 3u;
   T.vnz = d.z < 0.f ? 7u : 4u;
+#endif
   T.sp = 0;
   T.tsp = 0;
   T.ng = make_uint2(0u, 0x80000000u); // root as a one-entry node group
@@ -369,7 +379,17 @@ trav_init_any(const DScene& sc, Trav& T, const float3 o, const float3 d)
 // change, and the node test issues 24 FFMA2 instead of 48 FFMA.  Measured on B200: -2.5 % frame time
 // on the 10 M-triangle scene (k_extend, 80 registers, no spills); +0.3 % in the fused path kernels,
 // whose 64-register cap turns the register pairs into extra spills -- so only k_extend asks for it.
-template <bool STATS, typename Stack, bool F2 = false>
+#ifndef PTC_PREFETCH_NODE
+#define PTC_PREFETCH_NODE 0
+#endif
+// the same two switches for the traversal inside the fused path kernels (64-register cap)
+#ifndef PTC_PATH_PF
+#define PTC_PATH_PF 0
+#endif
+#ifndef PTC_PATH_TB
+#define PTC_PATH_TB 0
+#endif
+template <bool STATS, typename Stack, bool F2 = false, int PF = 0, bool TB = false>
 __device__ __forceinline__ bool
 trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& n_tris)
 {
@@ -384,41 +404,17 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
   if (!(T.ng.y & 0xFF000000u) && T.sp)
     T.ng = stack.get(--T.sp);
 
-  // -- at most one triangle test ------------------------------------------------------
-  // (Holding triangle tests back until N lanes of the warp have one pending was measured for
-  // N = 8..24: 4-7 % slower on both ends of the scene-size range -- the later a hit shrinks
-  // best_t, the more boxes are entered.)
-#pragma unroll
-  for (int rep = 0; rep < PTC_TRI_PER_ITER; ++rep)
-  if (T.tmask) {
-    const uint32_t bit = __ffs(T.tmask) - 1u;
-    T.tmask &= T.tmask - 1u;
-    const uint32_t rec = T.tg.x + __popc(T.tg.y & ((1u << bit) - 1u));
-    const float4* tp = sc.tris + (size_t)rec * kTriVec;
-    const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
-    if (STATS)
-      n_tris++;
-    float t, u, v;
-    if (tri_test(t0, t1, t2, T.o, T.d, t, u, v)) {
-      const uint32_t fid = __float_as_uint(t2.y);
-      if (t > 0.f && (t < T.best_t || (t == T.best_t && (T.any ? T.incl : fid < T.best_id)))) {
-        T.best_t = t;
-        T.best_id = fid;
-        T.best_u = u;
-        T.best_v = v;
-        if (T.any) { // occluded: nothing else about this ray matters
-          T.ng.y = 0u, T.tmask = 0u;
-          T.sp = T.tsp = 0;
-        }
-      }
-    }
-  }
-
-  // -- at most one node test ------------------------------------------------------------
-  // (A warp vote that holds the node test back while fewer than N = 4 / 8 / 12 lanes want one and
-  // others still have triangles to test was measured: 3-5 % slower -- the held lanes sit on the
-  // warp's critical path more often than not.)
-  if ((T.ng.y & 0xFF000000u) && T.tsp < kTriBacklog) {
+  // -- which node this iteration tests ------------------------------------------------------
+  // A warp whose lanes hold both kinds of work waits for the triangle records, computes, and only
+  // then asks for the nodes: dependent memory round trips per iteration although every address is
+  // known here.  PF != 0 (the extend kernel) selects the node BEFORE the triangle tests and
+  // requests its line from L1 (CCTL.E.PF1): 1 = the lanes that also hold triangles, 2 = every lane
+  // with a node, 3 = the node header itself is loaded here.  PF == 0 selects it after them (the
+  // early selection alone costs the fused path kernels 2 %).
+  bool do_node = (T.ng.y & 0xFF000000u) && T.tsp < kTriBacklog;
+  uint32_t vec0 = 0;
+  uint4 n0 = make_uint4(0, 0, 0, 0), n1 = n0;
+  auto select_node = [&]() {
     const uint32_t bit = 31u - __clz(T.ng.y);
     T.ng.y &= ~(1u << bit);
     const uint32_t imask_parent = T.ng.y & 0xFFu;
@@ -426,20 +422,112 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
       stack.put(T.sp++, T.ng);
     const uint32_t slot = (bit - 24u) ^ T.oct_inv;
     const uint32_t rel = __popc(imask_parent & ~(0xFFFFFFFFu << slot));
-    const uint32_t vec0 = (T.ng.x + rel) * kNodeVec;
+    vec0 = (T.ng.x + rel) * kNodeVec;
+  };
+  if (PF != 0 && do_node) {
+    select_node();
+    if (PF == 3)
+      ldg256(sc.nodes + vec0, n0, n1);
+    else if (PF == 2 || (PF == 1 && T.tmask))
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(sc.nodes + vec0));
+  }
 
-    uint4 n0, n1;
-#ifdef PTC_NO_LDG256
-    n0 = __ldg(sc.nodes + vec0), n1 = __ldg(sc.nodes + vec0 + 1);
-#else
-    ldg256(sc.nodes + vec0, n0, n1);
-#endif
+  // -- at most PTC_TRI_PER_ITER triangle tests --------------------------------------------------
+  // (Holding triangle tests back until N lanes of the warp have one pending was measured for
+  // N = 8..24: 4-7 % slower on both ends of the scene-size range -- the later a hit shrinks
+  // best_t, the more boxes are entered.)
+  // TB: the records of BOTH tests are requested before the first is evaluated.  The source-level
+  // profile of the extend kernel on the 10 M-triangle scene showed three exposed memory waits per
+  // iteration -- first use of triangle record 1 (17 % of all stall samples), of record 2 (13 %),
+  // of the node header (15 %) -- because the second record's address was only formed after the
+  // first test.  Same tests, same order, same bits.
+  bool hit_any = false;
+  auto accept = [&](const float4& t2, float t, float u, float v) {
+    const uint32_t fid = __float_as_uint(t2.y);
+    if (t > 0.f && (t < T.best_t || (t == T.best_t && (T.any ? T.incl : fid < T.best_id)))) {
+      T.best_t = t;
+      T.best_id = fid;
+      T.best_u = u;
+      T.best_v = v;
+      if (T.any) { // occluded: nothing else about this ray matters
+        T.ng.y = 0u, T.tmask = 0u;
+        T.sp = T.tsp = 0;
+        hit_any = true;
+      }
+    }
+  };
+  if (TB && PTC_TRI_PER_ITER == 2) {
+    if (T.tmask) {
+      const uint32_t bit0 = __ffs(T.tmask) - 1u;
+      T.tmask &= T.tmask - 1u;
+      const bool two = T.tmask != 0u;
+      const uint32_t bit1 = two ? __ffs(T.tmask) - 1u : bit0;
+      T.tmask &= T.tmask - 1u;
+      const float4* tp0 = sc.tris + (size_t)(T.tg.x + __popc(T.tg.y & ((1u << bit0) - 1u))) * kTriVec;
+      const float4* tp1 = sc.tris + (size_t)(T.tg.x + __popc(T.tg.y & ((1u << bit1) - 1u))) * kTriVec;
+      const float4 a0 = __ldg(tp0), a1 = __ldg(tp0 + 1), a2 = __ldg(tp0 + 2);
+      float4 b0 = a0, b1 = a1, b2 = a2;
+      if (two)
+        b0 = __ldg(tp1), b1 = __ldg(tp1 + 1), b2 = __ldg(tp1 + 2);
+      if (STATS)
+        n_tris += two ? 2u : 1u;
+      float t, u, v;
+      if (tri_test(a0, a1, a2, T.o, T.d, t, u, v))
+        accept(a2, t, u, v);
+      if (two && !hit_any && tri_test(b0, b1, b2, T.o, T.d, t, u, v))
+        accept(b2, t, u, v);
+    }
+  } else {
+#pragma unroll
+    for (int rep = 0; rep < PTC_TRI_PER_ITER; ++rep)
+      if (T.tmask) {
+        const uint32_t bit = __ffs(T.tmask) - 1u;
+        T.tmask &= T.tmask - 1u;
+        const uint32_t rec = T.tg.x + __popc(T.tg.y & ((1u << bit) - 1u));
+        const float4* tp = sc.tris + (size_t)rec * kTriVec;
+        const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+        if (STATS)
+          n_tris++;
+        float t, u, v;
+        if (tri_test(t0, t1, t2, T.o, T.d, t, u, v))
+          accept(t2, t, u, v);
+      }
+  }
+
+  // -- at most one node test ------------------------------------------------------------
+  // (A warp vote that holds the node test back while fewer than N = 4 / 8 / 12 lanes want one and
+  // others still have triangles to test was measured: 3-5 % slower -- the held lanes sit on the
+  // warp's critical path more often than not.)
+  if (do_node && !hit_any) {
+    if (PF == 0)
+      select_node();
+    if (PF != 3)
+      ldg256(sc.nodes + vec0, n0, n1);
+#if PTC_NODE_LAYOUT == 0
     // near / far plane sets picked by ray octant through the load address, not by selects
     // (measured: deriving the far index as near ^ c instead of the subtraction is slower; so is
     // summing the indices in 32 bits first, +1.3 %, although it is two instructions shorter per set)
     const uint4 NX = __ldg(sc.nodes + vec0 + T.vnx), FX = __ldg(sc.nodes + vec0 + 7u - T.vnx);
     const uint4 NY = __ldg(sc.nodes + vec0 + T.vny), FY = __ldg(sc.nodes + vec0 + 9u - T.vny);
     const uint4 NZ = __ldg(sc.nodes + vec0 + T.vnz), FZ = __ldg(sc.nodes + vec0 + 11u - T.vnz);
+#else
+    // One 32-byte load per axis (lower and upper planes of the axis are adjacent, bvh.h): the node
+    // is FOUR load instructions instead of seven.  Every lane of a warp reads a different node, so
+    // each load instruction costs one L1 wavefront per lane, and the L1 data pipe -- not DRAM, not
+    // occupancy (2, 3 and 4 CTAs per SM measured the same) -- is what the traversal kernels
+    // saturate first (ncu: l1tex__data_pipe_lsu_wavefronts 62-73 % of peak on the L2-resident
+    // 180 k-triangle scene).  The near / far set is then a register select on the ray's octant.
+    uint4 X0, X1, Y0, Y1, Z0, Z1;
+    ldg256(sc.nodes + vec0 + 2, X0, X1);
+    ldg256(sc.nodes + vec0 + 4, Y0, Y1);
+    ldg256(sc.nodes + vec0 + 6, Z0, Z1);
+    const bool ngx = T.oct & 1u, ngy = T.oct & 2u, ngz = T.oct & 4u;
+#define PTC_SEL4(c, A, B) make_uint4((c) ? (A).x : (B).x, (c) ? (A).y : (B).y, (c) ? (A).z : (B).z, (c) ? (A).w : (B).w)
+    const uint4 NX = PTC_SEL4(ngx, X1, X0), FX = PTC_SEL4(ngx, X0, X1);
+    const uint4 NY = PTC_SEL4(ngy, Y1, Y0), FY = PTC_SEL4(ngy, Y0, Y1);
+    const uint4 NZ = PTC_SEL4(ngz, Z1, Z0), FZ = PTC_SEL4(ngz, Z0, Z1);
+#undef PTC_SEL4
+#endif
     if (STATS)
       n_nodes++;
 
@@ -546,34 +634,49 @@ lights_hit(const DScene& sc, const float3 o, const float3 d, float& best_t, uint
   }
 }
 
-// What the last radiance-loop iteration needs to know (see trav_init_any): id = light id,
-// miss, or SOME face id when a triangle is in front.
+// One radiance-loop iteration's intersection query, ONE instance of the traversal loop for both
+// forms (the stage kernels used to inline a closest-hit and an any-hit copy of it, and a third for
+// the preview frame: ~450 instructions each in kernels whose first stage showed 19 % of its stall
+// samples waiting for instructions):
+//   last == false  closest hit with the reference's acceptance rules -- triangles front-facing
+//                  only, 0 < t < best, lowest face index wins equal t (intersection.cuh:110,
+//                  183-184) -- then the sphere lights (:199-212)
+//   last == true   what the LAST iteration needs to know (trav_init_any): id = light id, miss, or
+//                  SOME face id when a triangle is in front; u, v are not meaningful
+template <bool STATS, typename Stack>
+__device__ __forceinline__ void
+trace_ray(const DScene& sc, Stack& stack, const float3 o, const float3 d, const bool last, float& best_t,
+          uint32_t& best_id, float& best_u, float& best_v, uint32_t& n_nodes, uint32_t& n_tris)
+{
+  Trav T;
+  trav_init(T, o, d);
+  if (last) {
+    lights_hit(sc, o, d, T.best_t, T.best_id);
+    T.any = true;
+    T.incl = T.best_id != 0xFFFFFFFFu;
+  }
+  while (!trav_step<STATS, Stack, false, PTC_PATH_PF, PTC_PATH_TB != 0>(sc, T, stack, n_nodes, n_tris)) {
+  }
+  best_t = T.best_t, best_id = T.best_id, best_u = T.best_u, best_v = T.best_v;
+  if (!last)
+    lights_hit(sc, o, d, best_t, best_id);
+}
+
 template <bool STATS, typename Stack>
 __device__ __forceinline__ void
 last_hit(const DScene& sc, Stack& stack, const float3 o, const float3 d, float& best_t, uint32_t& best_id,
          uint32_t& n_nodes, uint32_t& n_tris)
 {
-  Trav T;
-  trav_init_any(sc, T, o, d);
-  while (!trav_step<STATS>(sc, T, stack, n_nodes, n_tris)) {
-  }
-  best_t = T.best_t, best_id = T.best_id;
+  float u, v;
+  trace_ray<STATS>(sc, stack, o, d, true, best_t, best_id, u, v, n_nodes, n_tris);
 }
 
-// Closest hit with the reference's acceptance rules: triangles front-facing only,
-// 0 < t < best, lowest face index wins equal t (intersection.cuh:110,183-184); then the
-// sphere lights.
 template <bool STATS, typename Stack>
 __device__ __forceinline__ void
 closest_hit(const DScene& sc, Stack& stack, const float3 o, const float3 d, float& best_t, uint32_t& best_id,
             float& best_u, float& best_v, uint32_t& n_nodes, uint32_t& n_tris)
 {
-  Trav T;
-  trav_init(T, o, d);
-  while (!trav_step<STATS>(sc, T, stack, n_nodes, n_tris)) {
-  }
-  best_t = T.best_t, best_id = T.best_id, best_u = T.best_u, best_v = T.best_v;
-  lights_hit(sc, o, d, best_t, best_id);
+  trace_ray<STATS>(sc, stack, o, d, false, best_t, best_id, best_u, best_v, n_nodes, n_tris);
 }
 
 } // namespace ptc

@@ -29,8 +29,12 @@ extern "C" {
 #endif
 
 /* 3: device-tree upload, cube-cross cubemaps, PPM / accumulator files, read-bandwidth probe;
- * the structs of version 2 are unchanged. */
-#define PTC_ABI_VERSION 3
+ * the structs of version 2 are unchanged.
+ * 4: rgb_hex of the cube-cross calls: PTC_CUBEMAP_DEFAULT_COLOR selects the default colour, 0 is
+ *    black; ptc_profile_frame no longer touches the caller's buffers and reports more;
+ *    ptc_render_args._pad became `flags` (PTC_OUT_FULL_IMAGE); ptc_group_* (several GPUs behind
+ *    one call), ptc_shared_* / ptc_flag_* (the same across processes). */
+#define PTC_ABI_VERSION 4
 
 typedef enum ptc_status
 {
@@ -148,8 +152,13 @@ typedef struct ptc_render_args
   uint32_t strip_rows;   /* 0 -> 16, the reference's block height (raytrace.cu:315) */
   uint32_t strip_stride;
   uint32_t strip_phase;
-  uint32_t _pad;
+  uint32_t flags;        /* PTC_OUT_FULL_IMAGE: out_rgba points at a FULL width x height image and every
+                            pixel of the band is stored at its global row.  The image may be memory of
+                            ANOTHER GPU (peer access or a CUDA IPC mapping, ptc_ipc_*): the tiles of
+                            several GPUs then assemble one image with plain stores from the kernel's
+                            epilogue, no collective (device-pointer calls only)                   */
 } ptc_render_args;
+#define PTC_OUT_FULL_IMAGE 1u
 
 typedef struct ptc_counters
 {
@@ -199,8 +208,10 @@ int ptc_set_cubemap(ptc_context* ctx, const float* faces, uint32_t size, int32_t
  * -y = (1,2), +z = (1,1), -z = (3,1); cells of size = w/4; alpha 0) and uploaded.  Like the
  * reference, a cross with w/4 != h/3 or a non-power-of-two size is not an error: the constant
  * colour 0x131b23 (size 1) is used instead and *used_fallback (optional) is set.
- * `cross` == NULL selects that constant-colour path with `rgb_hex` (0 -> 0x131b23), which is
- * what a scene without cubemap or with a "0xRRGGBB" cubemap line gets (gpu_processor.cpp:88-93). */
+ * `cross` == NULL selects that constant-colour path with `rgb_hex` = 0xRRGGBB (0 is black, as
+ * strtol of a "0x000000" cubemap line gives, gpu_processor.cpp:88-93) or
+ * PTC_CUBEMAP_DEFAULT_COLOR for the reference's default 0x131b23 (a scene without cubemap). */
+#define PTC_CUBEMAP_DEFAULT_COLOR 0xFFFFFFFFu
 int ptc_set_cubemap_from_cross(ptc_context* ctx, const float* cross, uint32_t w, uint32_t h,
                                uint32_t nb_chan, uint32_t rgb_hex, int32_t* cubemap_id,
                                int32_t* used_fallback);
@@ -309,8 +320,10 @@ int ptc_set_wavefront(ptc_context* ctx, uint32_t first_iters, uint32_t next_iter
                       int32_t split_extend, uint32_t refill);
 
 /* Measurement: renders the frame described by `args` `repeats` times with CUDA events
- * around every kernel launch on args->stream (device pointers as for ptc_render), plus one
- * untimed pass with traversal statistics.  The accumulator receives repeats + 1 samples. */
+ * around every kernel launch on args->stream (as ONE pipeline, so that every launch can be
+ * timed alone), once more with traversal statistics (untimed), and `repeats` times as ptc_render
+ * ships it (frame_ms_shipped).  All passes render into scratch buffers owned by the call:
+ * args->accum / out_rgba / radiance_out are ignored and the caller's ray counters unchanged. */
 typedef struct ptc_profile
 {
   uint32_t n_launches;        /* kernel launches per frame                            */
@@ -327,9 +340,62 @@ typedef struct ptc_profile
   uint64_t queue_rays;        /* rays written to (and read back from) a queue          */
   uint32_t queue_bytes_per_ray; /* bytes per queue slot (written once + read once)     */
   uint32_t hit_bytes_per_ray; /* hit record between extend and shade (0 when fused)    */
+  float frame_ms_shipped;     /* mean duration of the frame as ptc_render enqueues it  */
+  uint32_t pipelines;         /* half-frame pipelines ptc_render uses for this frame   */
+  uint64_t extend_lanes[8];   /* extend kernel, statistics pass: [0] warp iterations of the
+                                 traversal loop, and summed over them the lanes that [1] held a
+                                 ray, [2] ran a node test, [3] a triangle test, [4] a second one */
 } ptc_profile;
 int ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeats,
                       ptc_profile* out);
+
+/* -- several GPUs behind one call (single process) ------------------------------------------
+ * The reference drives one GPU from one host thread (gpu_info.cpp:26-28,38-43;
+ * GPUProcessor::render, gpu_processor.cpp:365-386).  A group keeps that call shape -- one upload,
+ * one render call per frame, one image -- over N devices: the scene is prepared once and
+ * replicated, the image is split into round-robin 16-row strips (strip s -> devices[s mod N]),
+ * every device accumulates its strips in an accumulator the group owns, and the RGBA8 pixels are
+ * stored by each device's kernels straight into the full image on devices[0] through the peer
+ * mapping (PTC_OUT_FULL_IMAGE) -- no gather pass, no collective.  The N-device image and
+ * accumulator are bit-identical to one device's.  `devices` may name the same device more than
+ * once (several contexts on one GPU; how the path is tested on a one-GPU box).
+ * ptc_group_render: args as for ptc_render except accum, radiance_out, rows and strips must be 0;
+ *   out_rgba = device pointer ON devices[0] of the full width x height image, or NULL for an image
+ *   the group owns (ptc_group_image / ptc_group_read_image); asynchronous: in the order of
+ *   args->stream (a stream of devices[0]) the frame is complete when the call's work is.
+ * ptc_group_gather_accum: the full float3 accumulator, rows bottom-up as one device keeps it
+ *   (raytrace.cu:252), assembled in HOST memory; synchronises. */
+typedef struct ptc_group ptc_group;
+int ptc_group_create(const int* devices, uint32_t n, ptc_group** out);
+void ptc_group_destroy(ptc_group* g);
+const char* ptc_group_last_error(const ptc_group* g);
+uint32_t ptc_group_size(const ptc_group* g);
+ptc_context* ptc_group_context(ptc_group* g, uint32_t i);
+int ptc_group_upload_scene(ptc_group* g, const ptc_scene_desc* desc, int32_t* scene_id);
+int ptc_group_set_cubemap(ptc_group* g, const float* faces, uint32_t size, int32_t* cubemap_id);
+int ptc_group_render(ptc_group* g, const ptc_render_args* args);
+int ptc_group_sync(ptc_group* g);
+const void* ptc_group_image(const ptc_group* g);
+int ptc_group_read_image(ptc_group* g, void* host_rgba, void* stream);
+int ptc_group_gather_accum(ptc_group* g, float* host_accum);
+int ptc_group_reset_accumulation(ptc_group* g);
+
+/* -- the same direct-store assembly for one PROCESS per GPU (bench.py under torchrun) ----------
+ * ptc_shared_alloc: device memory on `device` plus its CUDA IPC handle (64 bytes) to send to the
+ *   other ranks; ptc_shared_open maps it there (pass the mapped pointer as out_rgba with
+ *   PTC_OUT_FULL_IMAGE); ptc_shared_close / ptc_shared_free undo them.
+ * ptc_flag_signal: after everything enqueued on `stream` so far, store `value` to the (possibly
+ *   peer-mapped) 32-bit flag with system-scope release semantics ("my strips of frame k are in").
+ * ptc_flag_wait: `stream` waits (a one-block kernel that spins) until flags[i * stride_words]
+ *   has reached `value` for every i < n (n <= 256).
+ * ptc_memcpy_to_host: device -> host copy on `stream` (sync != 0: waits for it). */
+int ptc_shared_alloc(int device, uint64_t bytes, void** ptr, uint8_t handle[64]);
+int ptc_shared_open(int device, const uint8_t handle[64], void** ptr);
+int ptc_shared_close(int device, void* ptr);
+int ptc_shared_free(int device, void* ptr);
+int ptc_flag_signal(int device, void* flag, uint32_t value, void* stream);
+int ptc_flag_wait(int device, const void* flags, uint32_t n, uint32_t stride_words, uint32_t value, void* stream);
+int ptc_memcpy_to_host(int device, void* host, const void* dev, uint64_t bytes, void* stream, int sync);
 
 /* -- parity / debugging entry points (used by tests, not by a renderer) -------- */
 

@@ -27,6 +27,7 @@ struct RefGpu
   cudaTextureObject_t cube_tex = 0;
   uint32_t n_faces = 0, n_lights = 0;
   scene::SceneData h_sd;
+  std::vector<scene::Mesh> h_meshes; // host copy of the device Mesh table (device Face pointers)
 };
 
 #define CK(x)                                                                                  \
@@ -89,6 +90,83 @@ ref_hits_kernel(const scene::SceneData* sd, uint32_t n_faces, const float3* orig
     ts[k] = dist;
 }
 
+// The same answer for meshes too large for one thread per ray (10 M faces): a block of 256 rays
+// walks ONE chunk of one mesh's faces, 64 at a time through shared memory, with the reference's
+// own intersectTriangle; the winner of intersect()'s in-order scan (accept t < dist && t > 0,
+// intersection.cuh:183-184) is the minimum t with the LOWEST face index among equal t, i.e. the
+// minimum of the 64-bit key (bits(t) << 32 | global face index) -- positive floats order like
+// their bit patterns -- so chunks combine with atomicMin in any order.
+constexpr int kBfRays = 256, kBfTile = 64;
+
+__global__ void __launch_bounds__(kBfRays)
+ref_hits_tiled_kernel(const scene::Face* faces, uint32_t n_mesh_faces, uint32_t first_global_id,
+                      uint32_t faces_per_chunk, const float3* origins, const float3* dirs, uint64_t n,
+                      unsigned long long* keys)
+{
+  __shared__ uint4 s_faces[kBfTile * 7]; // 64 x scene::Face (112 B)
+  static_assert(sizeof(scene::Face) == 112, "Face layout");
+  const uint64_t k = blockIdx.x * (uint64_t)kBfRays + threadIdx.x;
+  const bool live = k < n;
+  scene::Ray r;
+  if (live) {
+    r.origin = origins[k];
+    r.dir = dirs[k];
+  }
+  const uint32_t f0 = blockIdx.y * faces_per_chunk;
+  const uint32_t f1 = f0 + faces_per_chunk < n_mesh_faces ? f0 + faces_per_chunk : n_mesh_faces;
+  unsigned long long best = ~0ull;
+  float3 nrm;
+  float2 uv;
+  for (uint32_t base = f0; base < f1; base += kBfTile) {
+    const uint32_t cnt = f1 - base < (uint32_t)kBfTile ? f1 - base : (uint32_t)kBfTile;
+    __syncthreads();
+    const uint4* src = reinterpret_cast<const uint4*>(faces + base);
+    for (uint32_t i = threadIdx.x; i < cnt * 7u; i += kBfRays)
+      s_faces[i] = src[i];
+    __syncthreads();
+    if (!live)
+      continue;
+    const scene::Face* sf = reinterpret_cast<const scene::Face*>(s_faces);
+    for (uint32_t i = 0; i < cnt; ++i) {
+      float t;
+      if (intersectTriangle(sf[i], nrm, uv, r, t) && t < 100000.0f && t > 0.0) {
+        const unsigned long long key =
+          ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)(first_global_id + base + i);
+        best = key < best ? key : best;
+      }
+    }
+  }
+  if (live && best != ~0ull)
+    atomicMin(keys + k, best);
+}
+
+__global__ void
+ref_hits_finish_kernel(const scene::SceneData* sd, uint32_t n_faces, const float3* origins, const float3* dirs,
+                       uint64_t n, const unsigned long long* keys, int32_t* ids, float* ts)
+{
+  uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+  if (k >= n)
+    return;
+  scene::Ray r;
+  r.origin = origins[k];
+  r.dir = dirs[k];
+  float dist = 100000.0f, inter_dist = 100000.0f;
+  int32_t id = -1;
+  if (keys[k] != ~0ull) {
+    dist = __uint_as_float((unsigned)(keys[k] >> 32));
+    id = (int32_t)(keys[k] & 0xFFFFFFFFull);
+  }
+  for (unsigned l = 0; l < sd->lights.size; ++l) // intersection.cuh:199-212
+    if (intersectSphere(r, sd->lights.data[l], inter_dist) && inter_dist < dist && inter_dist >= 0.0) {
+      dist = inter_dist;
+      id = (int32_t)(n_faces + l);
+    }
+  if (ids)
+    ids[k] = id;
+  if (ts)
+    ts[k] = dist;
+}
+
 // Primary rays exactly as `kernel` generates them (raytrace.cu:218-240).
 __global__ void
 ref_primary_kernel(unsigned width, unsigned height, scene::Camera cam, unsigned hash_seed,
@@ -142,6 +220,7 @@ ref_gpu_create(const ptc_scene_desc* d, const float* cube_faces, unsigned cube_s
   }
   g->n_faces = (uint32_t)off;
   g->n_lights = d->n_lights;
+  g->h_meshes = meshes;
   scene::SceneData& sd = g->h_sd;
   sd.meshes.size = d->n_meshes;
   sd.materials.size = d->n_materials;
@@ -349,6 +428,53 @@ ref_gpu_intersect(void* h, const float* origins, const float* dirs, uint64_t n, 
   if (ts)
     CK(cudaMemcpy(ts, d_t, n * 4, cudaMemcpyDeviceToHost));
   cudaFree(d_o), cudaFree(d_d), cudaFree(d_i), cudaFree(d_t);
+  return 0;
+}
+
+// Same contract as ref_gpu_intersect through the tiled brute-force kernels above (any mesh size).
+int
+ref_gpu_intersect_tiled(void* h, const float* origins, const float* dirs, uint64_t n, int32_t* ids,
+                        float* ts)
+{
+  RefGpu* g = (RefGpu*)h;
+  if (!n)
+    return 0;
+  float3 *d_o, *d_d;
+  int32_t* d_i;
+  float* d_t;
+  unsigned long long* d_k;
+  CK(cudaMalloc(&d_o, n * 12));
+  CK(cudaMalloc(&d_d, n * 12));
+  CK(cudaMalloc(&d_i, n * 4));
+  CK(cudaMalloc(&d_t, n * 4));
+  CK(cudaMalloc(&d_k, n * 8));
+  CK(cudaMemcpy(d_o, origins, n * 12, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d_d, dirs, n * 12, cudaMemcpyHostToDevice));
+  CK(cudaMemset(d_k, 0xFF, n * 8));
+  const unsigned ray_blocks = (unsigned)((n + kBfRays - 1) / kBfRays);
+  uint32_t first = 0;
+  for (const scene::Mesh& m : g->h_meshes) {
+    const uint32_t nf = m.faces.size;
+    if (nf) {
+      // enough chunks to fill the machine whatever the ray count; chunk = whole tiles
+      uint32_t chunks = (2048u + ray_blocks - 1) / ray_blocks;
+      const uint32_t tiles = (nf + kBfTile - 1) / kBfTile;
+      chunks = chunks > tiles ? tiles : chunks;
+      const uint32_t per = ((tiles + chunks - 1) / chunks) * kBfTile;
+      chunks = (nf + per - 1) / per;
+      ref_hits_tiled_kernel<<<dim3(ray_blocks, chunks), kBfRays>>>(m.faces.data, nf, first, per, d_o, d_d, n, d_k);
+    }
+    first += nf;
+  }
+  scene::SceneData* d_sd;
+  CK(cudaMemcpy(&d_sd, g->scenes.scenes, sizeof(d_sd), cudaMemcpyDeviceToHost));
+  ref_hits_finish_kernel<<<(unsigned)((n + 127) / 128), 128>>>(d_sd, g->n_faces, d_o, d_d, n, d_k, d_i, d_t);
+  CK(cudaDeviceSynchronize());
+  if (ids)
+    CK(cudaMemcpy(ids, d_i, n * 4, cudaMemcpyDeviceToHost));
+  if (ts)
+    CK(cudaMemcpy(ts, d_t, n * 4, cudaMemcpyDeviceToHost));
+  cudaFree(d_o), cudaFree(d_d), cudaFree(d_i), cudaFree(d_t), cudaFree(d_k);
   return 0;
 }
 

@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     for s in syms:
         assert hasattr(lib, s), f"{s} declared in include/ptcore.h but not exported"
     assert sorted(P.core.EXPORTS) == syms
-    assert lib.ptc_abi_version() == 3
+    assert lib.ptc_abi_version() == 4
 
 
 def test_record_layouts_match_reference_contract():
@@ -120,14 +120,14 @@ def test_ptscene_parser_rejects_bad_input():
 # -- host BVH builder --------------------------------------------------------------------------
 NODE = np.dtype([("origin", "<f4", 3), ("e", "u1", 3), ("imask", "u1"), ("child_base", "<u4"),
                  ("tri_base", "<u4"), ("valid24", "<u4"), ("occupied", "<u4"),
-                 ("qlo", "<f2", (3, 8)), ("qhi", "<f2", (3, 8))])
+                 ("planes", "<f2", (3, 2, 8))])   # [axis][lower | upper][slot], csrc/bvh.h
 TRI = np.dtype([("v0", "<f4", 3), ("e1", "<f4", 3), ("e2", "<f4", 3), ("face_id", "<u4"), ("_pad", "<u4", 2)])
 
 
 def decode_child_box(n, i):
     scale = np.array([np.array([int(e) << 23], np.uint32).view(np.float32)[0] for e in n["e"]], np.float64)
-    lo = n["origin"].astype(np.float64) + n["qlo"][:, i].astype(np.float64) * scale
-    hi = n["origin"].astype(np.float64) + n["qhi"][:, i].astype(np.float64) * scale
+    lo = n["origin"].astype(np.float64) + n["planes"][:, 0, i].astype(np.float64) * scale
+    hi = n["origin"].astype(np.float64) + n["planes"][:, 1, i].astype(np.float64) * scale
     return lo, hi
 
 
@@ -164,10 +164,10 @@ def test_bvh_structure(name):
             cnt = bin((int(n["valid24"]) >> (3 * i)) & 7).count("1")
             if not ((int(n["occupied"]) >> i) & 1):
                 assert not inner and cnt == 0
-                assert (n["qlo"][:, i] > n["qhi"][:, i]).all()   # inverted box: never hit
+                assert (n["planes"][:, 0, i] > n["planes"][:, 1, i]).all()   # inverted box: never hit
                 continue
             lo, hi = decode_child_box(n, i)
-            assert (n["qlo"][:, i] == np.round(n["qlo"][:, i])).all() and n["qhi"][:, i].max() <= 255
+            assert (n["planes"][:, 0, i] == np.round(n["planes"][:, 0, i])).all() and n["planes"][:, 1, i].max() <= 255
             if inner:
                 assert cnt == 0
                 rel = bin(int(n["imask"]) & ((1 << i) - 1)).count("1")
@@ -361,6 +361,9 @@ def test_cube_cross_faces_match_reference_extraction():
     assert faces.shape == (6, 1, 1, 4) and not fb and (faces[..., :3] == default).all() and (faces[..., 3] == 0).all()
     faces, fb = P.core.cubemap_faces_from_cross(None, 0xFF8000)
     assert (faces[0, 0, 0] == np.array([1.0, 128 / 255.0, 0.0, 0.0], np.float32)).all()
+    # "0x000000" is black in the reference (strtol, gpu_processor.cpp:88-93), not "no colour"
+    faces, fb = P.core.cubemap_faces_from_cross(None, 0)
+    assert not fb and (faces == 0).all()
     # not 4:3, and not a power of two: the reference falls back to the default colour, no error
     for shape in ((10, 16, 3), (9, 12, 3), (36, 48, 3)):
         faces, fb = P.core.cubemap_faces_from_cross(np.ones(shape, np.float32))
