@@ -952,3 +952,98 @@ def test_two_half_pipelines_equal_single_pipeline(core, monkeypatch):
         assert core.launch_count() - n0 == 2 * (single.launch_count() - m0)
     finally:
         single.close()
+
+
+# -- several GPUs behind one call (ptc_group_*) ---------------------------------------------------
+def _group_devices():
+    import torch
+    n = torch.cuda.device_count()
+    return list(range(n)) if n > 1 else [0, 0, 0]   # one GPU: three contexts on it (same code path)
+
+
+def test_group_render_equals_one_gpu(core):
+    """ptc_group_render over all visible GPUs (a one-GPU box: three contexts on that GPU): strips
+    per member, RGBA8 stored by the kernels straight into the full image on devices[0], per-member
+    accumulators.  Image and gathered accumulator == the 1-GPU frame, bit for bit, at 1080p
+    (67.5 strips) and at an odd size; the group's own frame counter follows the reference's."""
+    import ctypes as C
+    import torch
+    L = loaded(core, "indoor_tex")
+    devs = _group_devices()
+    g = P.Group(devs)
+    try:
+        assert g.size == len(devs)
+        sid = g.upload_scene(L.sc)
+        cid = g.set_cubemap(cube_of(L.sc)[0])
+        for (w, h, b) in [(1920, 1080, 3), (333, 77, 4)]:
+            acc, out, _ = dev_buffers(w, h)
+            g.reset_accumulation()
+            for k in (1, 2, 3):
+                core.render(L.sid, L.cid, L.sc, w, h, acc, out, None, bounces=b, frame_nb=k)
+                g.render(sid, cid, L.sc, w, h, bounces=b)       # frame_nb 0: the group's counter
+            torch.cuda.synchronize()
+            g.sync()
+            img = g.read_image(w, h)
+            assert (img == out.cpu().numpy().view(np.uint32)).all(), (w, h)
+            ga = g.gather_accum(w, h)
+            assert (bits(ga) == bits(acc.cpu().numpy())).all(), (w, h)
+        # caller-owned image on devices[0], explicit sample number, post-processing
+        w, h = 640, 360
+        acc, out, _ = dev_buffers(w, h)
+        mine = torch.zeros(h, w, dtype=torch.int32, device="cuda:0")
+        g.reset_accumulation()
+        core.render(L.sid, L.cid, L.sc, w, h, acc, out, None, bounces=3, frame_nb=7, post_id=2)
+        g.render(sid, cid, L.sc, w, h, out_rgba=mine, bounces=3, frame_nb=7, post_id=2)
+        g.sync()
+        torch.cuda.synchronize()
+        assert torch.equal(mine, out)
+        # the group owns the split: a caller-given band is refused
+        a = P.core.PtcRenderArgs()
+        cam = L.sc.camera_struct()
+        a.scene_id, a.cubemap_id, a.width, a.height = sid, cid, w, h
+        a.camera = C.pointer(cam)
+        a.row_begin, a.row_end = 0, 16
+        with pytest.raises(P.PtcError, match="group owns"):
+            g._check(g.lib.ptc_group_render(g.g, C.byref(a)), "ptc_group_render")
+    finally:
+        g.close()
+
+
+def test_full_image_store_and_flags(core):
+    """PTC_OUT_FULL_IMAGE + ptc_shared_* + ptc_flag_*: the pieces bench.py uses to assemble the image
+    of a one-process-per-GPU job without a collective.  Two contexts render alternate strips into
+    one shared full-size image (an IPC handle can only be opened from ANOTHER process, so the
+    owner's pointer is used here); a flag kernel per producer, a waiting kernel on the consumer
+    stream enqueued first, then the copy to the host: == the single-context frame."""
+    import torch
+    L = loaded(core, "indoor_tex")
+    w, h, b = 1280, 720, 3
+    acc, out, _ = dev_buffers(w, h)
+    core.render(L.sid, L.cid, L.sc, w, h, acc, out, None, bounces=b, frame_nb=2)
+    torch.cuda.synchronize()
+    shared = P.SharedBuffer(0, w * h * 4 + 1024)
+    other = P.Core(0)
+    try:
+        assert len(shared.handle) == 64
+        L2 = Loaded(other, L.sc)
+        flags = shared.address + w * h * 4
+        streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+        consumer = torch.cuda.Stream()
+        P.core.flag_wait(0, flags, 2, 1, 5, stream=consumer.cuda_stream)   # enqueued FIRST: really waits
+        host = np.zeros((h, w), np.uint32)
+        keep = []
+        for rank, (c, l) in enumerate([(core, L), (other, L2)]):
+            strips = (16, 2, rank)
+            bh = c.band_rows(w, h, strips=strips)
+            accb = torch.zeros(bh, w, 3, device="cuda")
+            keep.append(accb)
+            torch.cuda.synchronize()
+            c.render(l.sid, l.cid, L.sc, w, h, accb, shared.address, None, bounces=b, frame_nb=2, strips=strips,
+                     out_full=True, stream=streams[rank].cuda_stream)
+            P.core.flag_signal(0, flags + 4 * rank, 5, stream=streams[rank].cuda_stream)
+        shared.to_host(host, stream=consumer.cuda_stream, sync=True)
+        assert (host == out.cpu().numpy().view(np.uint32)).all()
+    finally:
+        torch.cuda.synchronize()
+        other.close()
+        shared.close()
