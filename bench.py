@@ -202,14 +202,15 @@ def run_reference_arm(args):
         return 0
     P = pkg()
     sc = load_scene(P, args.scene)
-    w, h = (args.width, args.height) if args.width else WEAK_DIMS.get(args.gpus, WEAK_DIMS[1])
+    w, h = (args.width, args.height) if args.width else (WEAK_DIMS.get(args.gpus, WEAK_DIMS[1])
+                                                        if args.scaling == "weak" else WEAK_DIMS[1])
     total = max(1, args.steps + args.warmup)
     r = cpu_sample(P, sc, w, h, args.bounces, args.steps, args.warmup, min(2.0, 150.0 / total))
     ms = r["seconds"] / args.steps * 1e3
     frames_full = r["pixels"] / float(w * h)
     line = {"impl": "reference", "metric": "Mrays/s @1080p 1spp, README indoor scene", "value": r["mrays"], "unit": "Mrays/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "frames_per_s": frames_full / r["seconds"],
             "config": config_dict(args, w, h, sc),
             "sampling": "host cores; each step = a strided sample of 16x16 blocks of the frame",
@@ -282,29 +283,49 @@ def run_ours(args):
     P = pkg()
     sc = load_scene(P, args.scene)
     n = max(world, 1)
-    w, h = (args.width, args.height) if args.width else WEAK_DIMS.get(n, (1920 * n, 1080))
+    weak = args.scaling == "weak"
+    w, h = (args.width, args.height) if args.width else (WEAK_DIMS.get(n, (1920 * n, 1080)) if weak else WEAK_DIMS[1])
     core = P.Core(local)
     sid = core.upload_scene(sc)
     cid = core.set_cubemap(sc.cubemap)
     # N > 1: round-robin 16-row strips (strip s -> rank s % N) so every rank sees the same mix
     # of cheap (sky / far wall) and expensive rows; --partition bands gives contiguous bands
     interleaved = world > 1 and args.partition == "strips"
-    gather = P.tiles.BandGather(h, w, world, rank, interleaved=interleaved)
-    strips = gather.strips
-    r0, r1 = (0, 0) if interleaved else gather.band
+    geom = P.tiles.BandGather(h, w, world, rank, interleaved=interleaved)
+    strips = geom.strips
+    r0, r1 = (0, 0) if interleaved else geom.band
     rows_kw = {"strips": strips} if interleaved else {"rows": (r0, r1)}
-    bh = gather.n_rows
+    bh = geom.n_rows
     dev = torch.device("cuda", local)
     accum = torch.zeros(max(bh, 1), w, 3, device=dev)
     out = torch.zeros(max(bh, 1), w, dtype=torch.int32, device=dev)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream()
+    cs = stream.cuda_stream
     K, W = args.steps, args.warmup
+    # N > 1, --gather store (default): every frame of every rank is stored by its kernels straight
+    # into the full image on rank 0 (tiles.StoreAssembly; no collective), and rank 0's stream holds
+    # the frame complete when all ranks' flags are in -- the image is assembled EVERY frame, inside
+    # the per-frame timing.  --gather nccl: round 1's one all_gather_into_tensor after the last frame.
+    store = P.tiles.StoreAssembly(P.core, local, h, w, world, rank) if world > 1 and args.gather == "store" else None
+    seq = [0]  # frames issued through the assembly so far (flag values must only grow)
 
-    def frame(k):
-        if bh:
-            core.render(sid, cid, sc, w, h, accum, out, None, bounces=args.bounces, frame_nb=k,
-                        stream=stream.cuda_stream, **rows_kw)
+    def frame(k, host=None):
+        if store is not None:
+            seq[0] += 1
+            f = seq[0]
+            store.before_frame(f, cs)
+            if bh:
+                core.render(sid, cid, sc, w, h, accum, store.image(f), None, bounces=args.bounces, frame_nb=k,
+                            stream=cs, out_full=True, **rows_kw)
+            store.after_frame(f, cs)
+            if rank == 0:
+                store.wait_complete(f, cs)
+                if host is not None:        # e2e: the assembled image goes to pinned host memory
+                    store.to_host(f, host, cs)
+                store.consumed(f, cs)
+        elif bh:
+            core.render(sid, cid, sc, w, h, accum, out, None, bounces=args.bounces, frame_nb=k, stream=cs, **rows_kw)
 
     def barrier():
         if world > 1:
@@ -314,9 +335,10 @@ def run_ours(args):
     # ---- device-resident value -----------------------------------------------------------
     for k in range(1, W + 1):
         frame(k)
-    if world > 1:
-        gather.gather(out.view(torch.uint8).view(bh, w, 4))  # warm NCCL
+    if world > 1 and store is None:
+        geom.gather(out.view(torch.uint8).view(bh, w, 4))  # warm NCCL
     barrier()
+    accum.zero_()   # the timed frames are samples 1..K of a fresh accumulation (config 2: compared bit for bit)
     core.reset_counters()
     launches_before = core.launch_count()
     sampler = ClockSampler(local) if rank == 0 else None
@@ -327,10 +349,11 @@ def run_ours(args):
     for k in range(K):
         flush.zero_()                       # L2 flush between timed frames (outside the event pair)
         ev[k][0].record(stream)
-        frame(W + 1 + k)
+        frame(1 + k)
         ev[k][1].record(stream)
     g0.record(stream)
-    full = gather.gather(out.view(torch.uint8).view(bh, w, 4)) if bh else None
+    if world > 1 and store is None and bh:
+        geom.gather(out.view(torch.uint8).view(bh, w, 4))
     g1.record(stream)
     barrier()
     t_wall1 = time.time()
@@ -351,56 +374,104 @@ def run_ours(args):
     segments, traced, launches = float(stats[1]), float(stats[2]), int(stats[3])
     value = segments / (ms_total * 1e-3) / 1e6
     if os.environ.get("PTC_BENCH_DEBUG"):
-        print(f"[rank {rank}] frames {ms_frames:.3f} ms  gather {g0.elapsed_time(g1):.3f} ms  rows {bh}",
-              file=sys.stderr, flush=True)
+        print(f"[rank {rank}] frames {ms_frames:.3f} ms  gather {ms_gather:.3f} ms  rows {bh}", file=sys.stderr, flush=True)
 
-    # ---- steady state without the flush (informational) -----------------------------------
-    barrier()
-    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    s0.record(stream)
-    for k in range(K):
-        frame(W + 1 + k)
-    s1.record(stream)
-    barrier()
-    ms_steady = s0.elapsed_time(s1) / K
+    # ---- N-GPU result == 1-GPU result, bit for bit (config 2's acceptance test) -------------
+    # The band accumulators (samples 1..K) are gathered on every rank (torch.distributed, outside
+    # any timing), rank 0 renders the same K samples of the WHOLE frame on its own GPU and compares
+    # the float3 accumulator bit for bit; with --gather store also the assembled RGBA8 image.
+    identity = None
+    if args.verify:
+        full_td = geom.gather(torch.flip(accum, dims=[0])[:bh].contiguous()) if bh or world > 1 else accum
+        if rank == 0:
+            acc1 = torch.zeros(h, w, 3, device=dev)
+            out1 = torch.zeros(h, w, dtype=torch.int32, device=dev)
+            ref_core = core
+            for k in range(1, K + 1):
+                ref_core.render(sid, cid, sc, w, h, acc1, out1, None, bounces=args.bounces, frame_nb=k, stream=cs)
+            torch.cuda.synchronize()
+            same_acc = bool(torch.equal(torch.flip(full_td, dims=[0]).view(torch.int32), acc1.view(torch.int32)))
+            identity = {"accumulator_bit_identical_to_1gpu": same_acc, "samples": K, "pixels": w * h}
+            if store is not None:
+                img = np.zeros((h, w), np.uint32)
+                store.to_host(seq[0], img, cs, sync=True)
+                identity["image_bit_identical_to_1gpu"] = bool((img == out1.cpu().numpy().view(np.uint32)).all())
+            del acc1, out1
+        barrier()
 
-    # ---- end to end through the host-buffer call ------------------------------------------
-    # ptc_render_host_async: arguments + camera host->device and the RGBA8 frame device->pinned
-    # host EVERY step; the copy of frame k overlaps the rendering of frame k+1 (two host
-    # buffers), everything has landed on the host when the timed region ends.
-    h_accum = torch.zeros(max(bh, 1), w, 3).pin_memory()
-    h_out = [torch.zeros(max(bh, 1), w, dtype=torch.int32).pin_memory() for _ in range(2)]
-    e2e_ms = 0.0
-    if bh:
-        for k in range(1, W + 1):
-            core.render_host_async(sid, cid, sc, w, h, h_accum.numpy(), h_out[k & 1].numpy(), None,
-                                   bounces=args.bounces, frame_nb=k, upload_accum=(k == 1),
-                                   stream=stream.cuda_stream, **rows_kw)
-        core.wait()
+    # ---- sustained: >= 5 s of back-to-back frames, no flush, clocks sampled ---------------------
     barrier()
-    t0 = time.perf_counter()
-    for k in range(K):
+    n_sus = max(K, int(np.ceil(args.sustain_s * 1e3 / max(ms_total / K, 1e-3)))) if args.sustain_s > 0 else 0
+    sustained = None
+    if n_sus:
+        sus_sampler = ClockSampler(local) if rank == 0 else None
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        tw0 = time.time()
+        s0.record(stream)
+        for k in range(n_sus):
+            frame(K + 1 + k)
+        s1.record(stream)
+        barrier()
+        tw1 = time.time()
+        t = torch.tensor([s0.elapsed_time(s1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        sus_clocks = sus_sampler.stop(tw0, tw1) if sus_sampler else None
+        sustained = {"frames": n_sus, "seconds": float(t[0]) * 1e-3, "ms_per_step": float(t[0]) / n_sus,
+                     "value": segments / K * n_sus / (float(t[0]) * 1e-3) / 1e6, "unit": "Mrays/s",
+                     "clocks": sus_clocks, "l2": "no flush between frames"}
+    ms_steady = sustained["ms_per_step"] if sustained else None
+
+    # ---- end to end through host buffers ----------------------------------------------------
+    # N = 1: ptc_render_host_async -- arguments + camera host->device and the RGBA8 frame
+    # device->pinned host EVERY step; the copy of frame k overlaps the rendering of frame k+1 (two
+    # host buffers).  N > 1 (--gather store): every step ends with the ASSEMBLED full image in
+    # rank 0's pinned host memory (the consumer the reference's window is, gpu_processor.cpp:365-386).
+    e2e_d2h = int(bh) * w * 4
+    barrier()
+    if store is not None:
+        h_img = [torch.zeros(h, w, dtype=torch.int32).pin_memory() for _ in range(2)] if rank == 0 else None
+        for k in range(W):
+            frame(k + 1, h_img[k & 1].numpy() if rank == 0 else None)
+        barrier()
+        t0 = time.perf_counter()
+        for k in range(K):
+            frame(W + 1 + k, h_img[k & 1].numpy() if rank == 0 else None)
+        torch.cuda.synchronize()
+        e2e_d2h = w * h * 4 if rank == 0 else 0
+    else:
+        h_accum = torch.zeros(max(bh, 1), w, 3).pin_memory()
+        h_out = [torch.zeros(max(bh, 1), w, dtype=torch.int32).pin_memory() for _ in range(2)]
         if bh:
-            core.render_host_async(sid, cid, sc, w, h, h_accum.numpy(), h_out[k & 1].numpy(), None,
-                                   bounces=args.bounces, frame_nb=W + 1 + k,
-                                   stream=stream.cuda_stream, **rows_kw)
-    if bh:
-        core.wait()
-    e2e_own_ms = (time.perf_counter() - t0) * 1e3
+            for k in range(1, W + 1):
+                core.render_host_async(sid, cid, sc, w, h, h_accum.numpy(), h_out[k & 1].numpy(), None,
+                                       bounces=args.bounces, frame_nb=k, upload_accum=(k == 1), stream=cs, **rows_kw)
+            core.wait()
+        barrier()
+        t0 = time.perf_counter()
+        for k in range(K):
+            if bh:
+                core.render_host_async(sid, cid, sc, w, h, h_accum.numpy(), h_out[k & 1].numpy(), None,
+                                       bounces=args.bounces, frame_nb=W + 1 + k, stream=cs, **rows_kw)
+        if bh:
+            core.wait()
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3  # host clock: the call chain ends with frames on the host
-    if os.environ.get("PTC_BENCH_DEBUG"):
-        print(f"[rank {rank}] e2e {e2e_ms:.3f} ms (own {e2e_own_ms:.3f}) for {K} steps", file=sys.stderr, flush=True)
-    t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+    t = torch.tensor([e2e_ms, float(e2e_d2h)], dtype=torch.float64, device=dev)
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_ms = float(t[0])
+        mx = t.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        e2e_ms = float(mx[0])
+    e2e_d2h_total = int(t[1])
     e2e_value = segments / (e2e_ms * 1e-3) / 1e6
 
-    # ---- roofline of the dominant kernel (rank 0, N = 1 only needs it) ---------------------
+    # ---- roofline of the stage kernels, baselines (rank 0) ----------------------------------
     roof = cpu_base = gpu_base = None
     if rank == 0:
-        roof = roofline(P, core, sid, cid, sc, w, h, rows_kw, args, accum, out, stream)
+        sm_mhz = (clocks or {}).get("sm_mhz")
+        roof = roofline(P, core, sid, cid, sc, w, h, rows_kw, args, accum, out, stream, sm_mhz=sm_mhz)
         if world == 1 and not args.no_cpu_baseline:
             try:
                 r = cpu_sample(P, sc, w, h, args.bounces, 3, 1, 4.0, prefer_reference=False)
@@ -408,45 +479,74 @@ def run_ours(args):
                             "sample": r["sample"]}
             except Exception as e:  # the checker is optional for the product, mandatory for the report
                 cpu_base = {"value": None, "unit": "Mrays/s", "cores": 0, "kind": "port", "sample": f"failed: {e}"}
-            gpu_base = reference_kernel_on_gpu(sc, w, h, args.bounces, K, W)
+            if sc.n_faces <= 100_000:
+                gpu_base = reference_kernel_on_gpu(sc, w, h, args.bounces, K, W)
+            else:
+                gpu_base = {"unavailable": f"brute force over {sc.n_faces} faces per ray: not runnable at this size"}
 
     if rank == 0:
         line = {"metric": "Mrays/s @1080p 1spp, README indoor scene", "value": value, "unit": "Mrays/s", "n_gpus": world,
                 "steps": K, "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "frames_per_s": K / (ms_total * 1e-3), "segments_per_step": segments / K,
                 "traced_per_step": traced / K, "ms_per_step_steady_no_flush": ms_steady,
                 "ms_gather_once": ms_gather,
+                "gather": ("none (1 GPU)" if world == 1 else
+                           "every frame: kernels store RGBA8 into the full image on rank 0 over NVLink (CUDA IPC), "
+                           "rank 0's stream waits for all ranks' flags inside the per-frame timing; no collective"
+                           if store is not None else "one NCCL all_gather_into_tensor after the last timed frame"),
                 "ms_per_frame_rank0": {"min": per_frame[0], "median": per_frame[len(per_frame) // 2],
                                        "max": per_frame[-1]},
                 "config": config_dict(args, w, h, sc), "l2_policy": L2_POLICY,
-                "clocks": clocks,
+                "clocks": clocks, "sustained": sustained, "bit_identity": identity,
                 "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_ms / K,
-                        "h2d_bytes_per_step": C.sizeof(P.core.PtcRenderArgs) + 64,
-                        "d2h_bytes_per_step": int(bh) * w * 4},
+                        "h2d_bytes_per_step": (C.sizeof(P.core.PtcRenderArgs) + 64) * world,
+                        "d2h_bytes_per_step": e2e_d2h_total,
+                        "what": ("assembled full image -> rank 0 pinned host memory every step" if store is not None
+                                 else "every rank's RGBA8 band -> its pinned host memory every step")},
                 "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu_base,
                 "reference_kernel_same_gpu": gpu_base}
         print(json.dumps(line))
+    barrier()
+    if store is not None:
+        store.close()
     core.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
-def roofline(P, core, sid, cid, sc, w, h, rows_kw, args, accum, out, stream):
-    """The dominant kernel is k_path (extend + shade of one wavefront step; every launch of a
-    frame is an instance of it).  achieved = algorithmic bytes of a frame's k_path launches /
-    their CUDA-event time (ptc_profile_frame: events around every launch on the launching
-    stream).  Algorithmic bytes (DESIGN.md "Roofline"): BVH nodes visited x 128 B + triangle
-    records tested x 48 B (counted by the kernel's own statistics pass) + per traced ray 96 B
-    of shading record and diffuse texel + 2 x 64 B per ray handed through a queue + 28 B per
-    pixel of accumulator read/write and RGBA8."""
+def ncu_counters(args, w, h):
+    """Per-frame counters of this workload's stage kernels from the committed ncu capture
+    (profiles/r2_counters.json, written by tools/ncu_counters.py from `ncu --csv` of tools/probe.py):
+    warp instructions executed and DRAM bytes.  NOT measured in this run -- the entry says which
+    capture it came from; None when the workload has no capture."""
+    try:
+        table = json.load(open(os.path.join(REPO, "profiles", "r2_counters.json")))
+        return table.get(f"{args.scene} {w}x{h} b={args.bounces}")
+    except Exception:
+        return None
+
+
+def roofline(P, core, sid, cid, sc, w, h, rows_kw, args, accum, out, stream, sm_mhz=None):
+    """Three lower bounds on the time of a frame's stage kernels (k_path / k_extend; every launch of
+    a frame is one of them), all per frame:
+      bytes  BVH bytes (nodes visited x 128 B + triangle records tested x 48 B, counted by the
+             kernels' statistics pass, which tests pin to oracle O2's counts) at the MEASURED read
+             bandwidth of the cache tier the BVH lives in + every other algorithmic byte (96 B of
+             shading record and texel per traced ray, 2 x 64 B per queued ray, 28 B per pixel) at
+             the HBM peak of MEASURED_PEAKS.json
+      fp32   nodes x 160 + triangles x 37 flops at SMs x 128 lanes x 2 x the SM clock
+      issue  warp instructions (committed ncu capture) at SMs x 4 schedulers x the SM clock
+    `bound` = the largest, `frac` = that bound / the kernels' CUDA-event time (events around every
+    launch, one pipeline).  The algorithmic-bytes-over-HBM-peak figure of round 1 is kept under
+    `algorithmic_gbs_vs_hbm` -- it is not a roofline fraction for a cache-resident scene."""
     hbm, how = measured_peaks()
     try:
         prof = core.profile_frame(sid, cid, sc, w, h, accum, out, None, bounces=args.bounces, frame_nb=5,
                                   stream=stream.cuda_stream, repeats=8, **rows_kw)
     except Exception as e:
-        return {"bound": "hbm", "achieved": None, "peak": hbm, "unit": "GB/s", "frac": None, "traffic": None,
+        return {"bound": None, "achieved": None, "peak": None, "unit": None, "frac": None, "traffic": None,
                 "note": f"profile_frame failed: {e}"}
     info = core.scene_info(sid)
     px = core.band_rows(w, h, **rows_kw) * w
@@ -457,57 +557,62 @@ def roofline(P, core, sid, cid, sc, w, h, rows_kw, args, accum, out, stream):
     b_fb = px * 28
     nbytes = b_bvh + b_shade + b_queue + b_fb
     k_ms = sum(prof["launch_ms"])
-    ach = nbytes / (k_ms * 1e-3) / 1e9
-    flops = prof["nodes_visited"] * 160.0 + prof["tris_tested"] * 37.0
-    fp32_peak = 148 * 128 * 2 * 1965e6 / 1e12
     n = max(1, len(prof["launch_ms"]))
-    # Which memory tier the BVH bytes actually come from, and that tier's MEASURED read bandwidth
-    # on this box (ptc_debug_read_bandwidth: the traversal's 16-byte read-only loads over a working
-    # set of that size).  t_roof = bvh bytes / tier bandwidth + every other byte / HBM bandwidth.
+    clock_hz = (sm_mhz or 1965.0) * 1e6
+    n_sms = 148
+    flops = prof["nodes_visited"] * 160.0 + prof["tris_tested"] * 37.0
+    fp32_peak = n_sms * 128 * 2 * clock_hz
+    issue_peak = n_sms * 4 * clock_hz
     bvh_resident = info.bvh_nodes * info.bvh_node_bytes + info.n_faces * info.tri_bytes
     tier = "l1" if bvh_resident <= (64 << 10) else ("l2" if bvh_resident <= (64 << 20) else "hbm")
-    tiers = None
-    try:
-        tiers = {"l1_gbs": core.read_bandwidth(32 << 10, 48 << 30), "l2_gbs": core.read_bandwidth(32 << 20, 24 << 30),
-                 "hbm_read_gbs": core.read_bandwidth(4 << 30, 16 << 30)}
-        tier_bw = {"l1": tiers["l1_gbs"], "l2": tiers["l2_gbs"], "hbm": tiers["hbm_read_gbs"]}[tier]
-        t_roof_ms = (b_bvh / tier_bw + (nbytes - b_bvh) / hbm) / 1e9 * 1e3
-        tiers.update({"bvh_resident_bytes": bvh_resident, "bvh_tier": tier, "t_roof_ms": t_roof_ms,
-                      "frac_of_tier_roofline": t_roof_ms / k_ms,
-                      "how": "16-byte read-only loads from all SMs over a zeroed working set of 32 KB / 32 MB / 4 GB"})
-    except Exception as e:
-        tiers = {"error": str(e)}
-    traffic = dram_traffic_per_launch(args, w, h, n)
-    return {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": traffic,
-            "cache_tiers": tiers,
-            "peak_source": how, "kernel": "ptc::k_path + ptc::k_extend (the wavefront stages of one frame)",
+    tiers = {"l1_gbs": core.read_bandwidth(32 << 10, 48 << 30), "l2_gbs": core.read_bandwidth(32 << 20, 24 << 30),
+             "hbm_read_gbs": core.read_bandwidth(4 << 30, 16 << 30), "bvh_resident_bytes": bvh_resident,
+             "bvh_tier": tier,
+             "how": "16-byte read-only loads from all SMs over a zeroed working set of 32 KB / 32 MB / 4 GB"}
+    tier_bw = {"l1": tiers["l1_gbs"], "l2": tiers["l2_gbs"], "hbm": min(tiers["hbm_read_gbs"], hbm)}[tier]
+    t_bytes = (b_bvh / tier_bw + (nbytes - b_bvh) / hbm) / 1e9 * 1e3
+    t_fp32 = flops / fp32_peak * 1e3
+    ctr = ncu_counters(args, w, h)
+    t_issue = ctr["warp_instructions_per_frame"] / issue_peak * 1e3 if ctr else None
+    bounds = {"bytes": t_bytes, "fp32": t_fp32}
+    if t_issue is not None:
+        bounds["issue"] = t_issue
+    bound = max(bounds, key=bounds.get)
+    if bound == "issue":
+        ach, peak, unit = ctr["warp_instructions_per_frame"] / (k_ms * 1e-3) / 1e9, issue_peak / 1e9, "Gwarp-inst/s"
+    elif bound == "fp32":
+        ach, peak, unit = flops / (k_ms * 1e-3) / 1e12, fp32_peak / 1e12, "TFLOP/s"
+    else:
+        ach, peak, unit = nbytes / (k_ms * 1e-3) / 1e9, nbytes / (t_bytes * 1e-3) / 1e9, "GB/s"
+    traffic = ctr["dram_bytes_per_frame"] / n if ctr else None
+    return {"bound": {"bytes": tier if tier != "hbm" else "hbm", "fp32": "fp32", "issue": "issue"}[bound],
+            "achieved": ach, "peak": peak, "unit": unit, "frac": bounds[bound] / k_ms, "traffic": traffic,
+            "traffic_source": (ctr["source"] + " (committed capture, not measured in this run)") if ctr else None,
+            "traffic_over_algorithmic": (ctr["dram_bytes_per_frame"] / nbytes) if ctr else None,
+            "bounds_ms": bounds, "bounds_frac": {k: v / k_ms for k, v in bounds.items()},
+            "sm_clock_mhz_used": clock_hz / 1e6,
+            "peak_note": "bytes: effective peak = algorithmic bytes / (BVH bytes at the measured bandwidth of their "
+                         "cache tier + the rest at the HBM peak); hbm peak " + how,
+            "cache_tiers": tiers, "hbm_peak_gbs": hbm,
+            "algorithmic_gbs_vs_hbm": {"achieved": nbytes / (k_ms * 1e-3) / 1e9, "peak": hbm,
+                                       "ratio": nbytes / (k_ms * 1e-3) / 1e9 / hbm,
+                                       "note": "NOT a roofline fraction when the BVH is cache-resident"},
+            "kernel": "ptc::k_path + ptc::k_extend (the wavefront stages of one frame)",
             "launches_per_frame": n, "kernel_ms_per_launch": k_ms / n, "kernel_ms_per_frame": k_ms,
-            "frame_ms": prof["frame_ms"], "kernel_share_of_frame": k_ms / prof["frame_ms"],
+            "frame_ms_one_pipeline": prof["frame_ms"], "frame_ms_as_shipped": prof["frame_ms_shipped"],
+            "pipelines_as_shipped": prof["pipelines"],
+            "frac_vs_shipped_frame": bounds[bound] / prof["frame_ms_shipped"] if prof["frame_ms_shipped"] else None,
+            "kernel_share_of_frame": k_ms / prof["frame_ms"],
             "launch_ms": prof["launch_ms"], "launch_kind": prof["launch_kind"],
             "algorithmic_bytes_per_launch": nbytes / n,
             "algorithmic_bytes_per_frame": {"bvh": b_bvh, "shade": b_shade, "queue": b_queue, "framebuffer": b_fb},
+            "intersection_flops_per_frame": flops,
+            "warp_instructions_per_frame": ctr["warp_instructions_per_frame"] if ctr else None,
             "nodes_per_ray": prof["nodes_visited"] / max(1, prof["traced"]),
             "tris_per_ray": prof["tris_tested"] / max(1, prof["traced"]),
-            "rays_per_bounce": prof["rays_per_bounce"][:args.bounces],
-            "fp32_bound": {"intersection_flops_per_frame": flops,
-                           "achieved_tflops": flops / (k_ms * 1e-3) / 1e12,
-                           "peak_tflops_at_max_clock": fp32_peak,
-                           "frac": flops / (k_ms * 1e-3) / 1e12 / fp32_peak},
-            "note": "achieved counts ALGORITHMIC bytes; BVH bytes of a cache-resident scene never reach HBM "
-                    "(traffic = measured DRAM bytes), so frac against the HBM peak says how hard the caches "
-                    "are driven; cache_tiers gives the roofline against the tier the BVH lives in"}
-
-
-def dram_traffic_per_launch(args, w, h, n_launches):
-    """dram__bytes_read.sum + dram__bytes_write.sum of the frame's stage kernels from the committed
-    `ncu --set full` capture of this workload (profiles/dram_traffic.json), per launch; None for a
-    workload that has no capture."""
-    try:
-        table = json.load(open(os.path.join(REPO, "profiles", "dram_traffic.json")))
-        ent = table.get(f"{args.scene} {w}x{h} b={args.bounces}")
-        return ent["dram_bytes_per_frame"] / n_launches if ent else None
-    except Exception:
-        return None
+            "extend_lanes_per_warp_iteration": ([x / max(1, prof["extend_lanes"][0]) for x in prof["extend_lanes"][1:]]
+                                                if prof["extend_lanes"][0] else None),
+            "rays_per_bounce": prof["rays_per_bounce"][:args.bounces]}
 
 
 def reference_kernel_on_gpu(sc, w, h, bounces, K, W):
@@ -551,7 +656,25 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--partition", default="strips", choices=["strips", "bands"],
                     help="N > 1: round-robin 16-row strips (default) or contiguous bands")
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS),
+                    help="a BASELINE.json configuration (sets scene / size / bounces / scaling)")
+    ap.add_argument("--scaling", default=None, choices=["weak", "strong"])
+    ap.add_argument("--gather", default="store", choices=["store", "nccl"],
+                    help="N > 1: image assembled every frame by peer stores (default) or one NCCL gather at the end")
+    ap.add_argument("--verify", action="store_true",
+                    help="compare the N-GPU accumulator (and image) bit for bit with a 1-GPU render on rank 0")
+    ap.add_argument("--sustain-s", type=float, default=5.0, help="length of the sustained block (0 = skip)")
     args = ap.parse_args()
+    if args.workload:
+        scene, ww, hh, bb, scaling = WORKLOADS[args.workload]
+        args.scene, args.bounces = scene, bb
+        if ww:
+            args.width, args.height = ww, hh
+        args.scaling = args.scaling or scaling
+        if args.workload == "cfg2":
+            args.verify = True
+    if not args.scaling:
+        args.scaling = "strong" if args.width else "weak"
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         return run_reference_arm(args)

@@ -11,7 +11,7 @@ REPO = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libptcore.so")
 CUDA = os.environ.get("CUDA_HOME", "/usr/local/cuda")
-SOURCES = ["ptcore.cu", "kernels.cu", "group.cu", "bvh_builder.cpp"]
+SOURCES = ["ptcore.cu", "kernels.cu", "group.cu", "bvh_builder.cpp", "flatten.cpp"]
 HEADERS = ["bvh.h", "device_types.cuh", "kernels.cuh", "vecmath.cuh", "traverse.cuh", "shade.cuh",
            "ptcore_internal.h", "../../include/ptcore.h"]
 
@@ -29,7 +29,7 @@ def build(force=False, verbose=False):
         return OUT
     cmd = [os.path.join(CUDA, "bin", "nvcc"), "-std=c++17", "-O3", "-lineinfo",
            "-gencode", "arch=compute_100a,code=sm_100a",
-           "-Xcompiler", "-fPIC,-O2,-Wall,-pthread", "-shared",
+           "-Xcompiler", "-fPIC,-O2,-Wall,-pthread,-ffp-contract=off", "-shared",
            "-I", os.path.join(REPO, "include"), "-I", CSRC]
     if verbose:
         cmd += ["-Xptxas", "-v"]

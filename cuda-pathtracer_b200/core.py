@@ -82,7 +82,8 @@ EXPORTS = ["ptc_abi_version", "ptc_create", "ptc_destroy", "ptc_last_error", "pt
            "ptc_group_context", "ptc_group_upload_scene", "ptc_group_set_cubemap", "ptc_group_render",
            "ptc_group_sync", "ptc_group_image", "ptc_group_read_image", "ptc_group_gather_accum",
            "ptc_group_reset_accumulation", "ptc_shared_alloc", "ptc_shared_open", "ptc_shared_close",
-           "ptc_shared_free", "ptc_flag_signal", "ptc_flag_wait", "ptc_memcpy_to_host"]
+           "ptc_shared_free", "ptc_flag_signal", "ptc_flag_wait", "ptc_memcpy_to_host",
+           "ptc_indexed_face_count", "ptc_flatten_faces", "ptc_upload_scene_indexed"]
 
 _lib = None
 
@@ -118,6 +119,9 @@ def load_library() -> C.CDLL:
                      "ptc_shared_open", "ptc_shared_close", "ptc_shared_free", "ptc_flag_signal",
                      "ptc_flag_wait", "ptc_memcpy_to_host"]:
             getattr(lib, name).restype = C.c_int
+        lib.ptc_indexed_face_count.restype = C.c_uint64
+        lib.ptc_flatten_faces.restype = C.c_int
+        lib.ptc_upload_scene_indexed.restype = C.c_int
         lib.ptc_group_last_error.restype = C.c_char_p
         lib.ptc_group_last_error.argtypes = [C.c_void_p]
         lib.ptc_group_destroy.restype = None
@@ -213,6 +217,19 @@ def host_bvh(scene: ptscene.SceneBlob) -> dict:
                 "face_ids": ids, "sah_cost": float(hb.sah_cost), "max_depth": int(hb.max_depth)}
     finally:
         lib.ptc_host_bvh_free(C.byref(hb))
+
+
+def flatten_faces(mesh: "ptscene.IndexedMesh"):
+    """Host-only: indexed mesh -> (Face records uint8 (F, 112), faces per mesh uint32), ptc_flatten_faces."""
+    lib = load_library()
+    d = mesh.to_desc()
+    n = int(lib.ptc_indexed_face_count(C.byref(d)))
+    faces = np.zeros((n, 112), np.uint8)
+    counts = np.zeros(len(mesh.shapes), np.uint32)
+    rc = lib.ptc_flatten_faces(C.byref(d), _ptr(faces), C.c_uint64(n), _ptr(counts))
+    if rc:
+        raise PtcError(f"ptc_flatten_faces failed ({rc}): an index outside its attribute array?")
+    return faces, counts
 
 
 class Core:
@@ -358,6 +375,13 @@ class Core:
         """Device-pointer render call (accum / out_rgba / radiance_out are device buffers)."""
         a = self._args(*args, **kw)
         self._check(self.lib.ptc_render(self.ctx, C.byref(a)), "ptc_render")
+
+    def upload_scene_indexed(self, mesh, scene) -> int:
+        """ptc_upload_scene_indexed: `mesh` = ptscene.IndexedMesh, materials / lights / textures of `scene`."""
+        d = mesh.to_desc(scene)
+        sid = C.c_int32(-1)
+        self._check(self.lib.ptc_upload_scene_indexed(self.ctx, C.byref(d), C.byref(sid)), "ptc_upload_scene_indexed")
+        return sid.value
 
     def render_host(self, *args, upload_accum=False, download_accum=False, **kw):
         """Host-buffer render call: copies in/out and synchronises."""

@@ -562,6 +562,8 @@ ptc_memcpy_to_host(int device, void* host, const void* dev, uint64_t bytes, void
 // acquire spin on the consumer.
 namespace {
 
+constexpr unsigned long long kFlagWaitNs = 20ull * 1000000000ull; // 20 s
+
 __global__ void
 k_flag_signal(uint32_t* flag, uint32_t value)
 {
@@ -575,11 +577,18 @@ k_flag_wait(const uint32_t* flags, uint32_t n, uint32_t stride_words, uint32_t v
   const uint32_t i = threadIdx.x;
   if (i < n) {
     uint32_t v;
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
     do {
       asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + (size_t)i * stride_words) : "memory");
       if ((int32_t)(v - value) >= 0)
         break;
       __nanosleep(200);
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      // a producer that never signals (a crashed rank, a caller that synchronised the device before
+      // enqueueing it) must not hang the GPU: give up loudly after kFlagWaitNs
+      if (t1 - t0 > kFlagWaitNs)
+        __trap();
     } while (true);
   }
 }

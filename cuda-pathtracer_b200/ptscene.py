@@ -192,3 +192,83 @@ def parse_ptscene(raw: bytes) -> SceneBlob:
     if has:
         cube = np.frombuffer(take(6 * size * size * 16), dtype=np.float32).reshape(6, size, size, 4).copy()
     return SceneBlob(camera, lights, mats, counts, faces, textures, cubemap_path, size, cube)
+
+
+# ---------------------------------------------------------------------------------------------
+# indexed meshes (include/ptcore.h ptc_indexed_desc): the OBJ loader's output BEFORE Face[]
+# ---------------------------------------------------------------------------------------------
+class PtcIndexedMesh(C.Structure):
+    _fields_ = [("indices", C.c_void_p), ("n_indices", C.c_uint64), ("material_ids", C.c_void_p)]
+
+
+class PtcIndexedDesc(C.Structure):
+    _fields_ = [("vertices", C.c_void_p), ("n_vertex_floats", C.c_uint64),
+                ("normals", C.c_void_p), ("n_normal_floats", C.c_uint64),
+                ("texcoords", C.c_void_p), ("n_texcoord_floats", C.c_uint64),
+                ("meshes", C.POINTER(PtcIndexedMesh)), ("n_meshes", C.c_uint32),
+                ("index_stride_ints", C.c_uint32),
+                ("materials", C.c_void_p), ("n_materials", C.c_uint32),
+                ("lights", C.c_void_p), ("n_lights", C.c_uint32),
+                ("textures", C.c_void_p), ("n_textures", C.c_uint32)]
+
+
+class IndexedMesh:
+    """Attribute arrays + per-shape index records and material ids (tinyobj's output)."""
+
+    def __init__(self, vertices, normals, texcoords, shapes, stride=3):
+        self.vertices = np.ascontiguousarray(vertices, np.float32).reshape(-1)
+        self.normals = np.ascontiguousarray(normals, np.float32).reshape(-1)
+        self.texcoords = np.ascontiguousarray(texcoords, np.float32).reshape(-1)
+        self.stride = int(stride)
+        # shapes: list of (indices int32 (n, stride), material_ids int32 (n // 3,))
+        self.shapes = [(np.ascontiguousarray(i, np.int32).reshape(-1, self.stride),
+                        np.ascontiguousarray(m, np.int32).reshape(-1)) for i, m in shapes]
+
+    @property
+    def n_faces(self):
+        return sum(i.shape[0] // 3 for i, _ in self.shapes)
+
+    def to_desc(self, scene=None) -> PtcIndexedDesc:
+        d = PtcIndexedDesc()
+        d.vertices, d.n_vertex_floats = self.vertices.ctypes.data, self.vertices.size
+        d.normals, d.n_normal_floats = self.normals.ctypes.data, self.normals.size
+        d.texcoords, d.n_texcoord_floats = self.texcoords.ctypes.data, self.texcoords.size
+        arr = (PtcIndexedMesh * max(1, len(self.shapes)))()
+        for k, (idx, mids) in enumerate(self.shapes):
+            arr[k].indices, arr[k].n_indices, arr[k].material_ids = idx.ctypes.data, idx.shape[0], mids.ctypes.data
+        d.meshes, d.n_meshes, d.index_stride_ints = arr, len(self.shapes), self.stride
+        self._keep = [arr]
+        if scene is not None:  # materials / lights / textures of a SceneBlob
+            sd = scene.to_desc()
+            self._keep.append((scene, sd))
+            d.materials, d.n_materials = sd.materials, sd.n_materials
+            d.lights, d.n_lights = sd.lights, sd.n_lights
+            d.textures, d.n_textures = sd.textures, sd.n_textures
+        return d
+
+
+def load_ptix(path) -> IndexedMesh:
+    """Reads a .ptix file: the reference loader's tinyobj output (written by the fixture tooling, see
+    tests/golden/make_fixtures.py) -- attribute arrays, index records, per-face material ids."""
+    import struct
+    with open(path, "rb") as f:
+        raw = f.read()
+    assert raw[:4] == b"PTIX" and struct.unpack_from("<I", raw, 4)[0] == 1
+    off = 8
+    arrs = []
+    for _ in range(3):
+        n = struct.unpack_from("<Q", raw, off)[0]
+        arrs.append(np.frombuffer(raw, np.float32, n, off + 8).copy())
+        off += 8 + 4 * n
+    n_shapes, stride = struct.unpack_from("<II", raw, off)
+    off += 8
+    shapes = []
+    for _ in range(n_shapes):
+        ni = struct.unpack_from("<Q", raw, off)[0]
+        idx = np.frombuffer(raw, np.int32, ni * stride, off + 8).copy().reshape(-1, stride)
+        off += 8 + 4 * ni * stride
+        nm = struct.unpack_from("<Q", raw, off)[0]
+        mids = np.frombuffer(raw, np.int32, nm, off + 8).copy()
+        off += 8 + 4 * nm
+        shapes.append((idx, mids))
+    return IndexedMesh(arrs[0], arrs[1], arrs[2], shapes, stride)

@@ -132,3 +132,64 @@ class BandGather:
         if self._identity:
             return out[: self.height]
         return out.index_select(0, self._idx[key])
+
+
+class StoreAssembly:
+    """One process per GPU: the image is assembled on rank 0 by the STORES of every rank's last
+    stage kernel (PTC_OUT_FULL_IMAGE into rank 0's memory, mapped through CUDA IPC over NVLink) --
+    no gather pass, no pad copy, no permutation, no collective on the data path.  torch.distributed
+    only carries the 64-byte IPC handle at set-up.
+
+    Two full-size images alternate (frame k -> image k & 1) so that rank 0 can hand frame k to its
+    consumer while frame k + 1 is being stored.  Flags (one 128-byte line each, in rank 0's memory):
+      ready[r]    = last frame whose strips rank r has stored        (written by rank r)
+      consumed    = last frame rank 0's consumer is done with        (written by rank 0)
+    Rank r renders frame k only after consumed >= k - 2 (the image it is about to overwrite is
+    free); rank 0's stream holds frame k complete after ready[r] >= k for all r.
+    """
+    LINE = 128
+
+    def __init__(self, core_mod, device, height, width, world, rank):
+        import torch.distributed as dist
+        self.m, self.device, self.world, self.rank = core_mod, device, world, rank
+        self.h, self.w = height, width
+        self.image_bytes = ((height * width * 4 + 255) // 256) * 256
+        total = 2 * self.image_bytes + (world + 1) * self.LINE
+        box = [None]
+        if rank == 0:
+            self.buf = core_mod.SharedBuffer(device, total)
+            box[0] = self.buf.handle
+        if world > 1:
+            dist.broadcast_object_list(box, src=0)
+        if rank != 0:
+            self.buf = core_mod.SharedBuffer(device, handle=box[0])
+        self.flags = self.buf.address + 2 * self.image_bytes
+
+    def image(self, frame):
+        return self.buf.address + (frame & 1) * self.image_bytes
+
+    def before_frame(self, frame, stream):
+        """Back-pressure: the image of `frame` was last used by frame - 2."""
+        if self.rank != 0 and frame > 2:
+            self.m.flag_wait(self.device, self.flags + self.world * self.LINE, 1, 1, frame - 2, stream)
+
+    def after_frame(self, frame, stream):
+        """This rank's strips of `frame` are stored (release at system scope, stream order)."""
+        self.m.flag_signal(self.device, self.flags + self.rank * self.LINE, frame, stream)
+
+    def wait_complete(self, frame, stream):
+        """Rank 0: `stream` continues when every rank's strips of `frame` have landed."""
+        assert self.rank == 0
+        self.m.flag_wait(self.device, self.flags, self.world, self.LINE // 4, frame, stream)
+
+    def consumed(self, frame, stream):
+        """Rank 0: everything enqueued on `stream` so far is done with the image of `frame`."""
+        assert self.rank == 0
+        self.m.flag_signal(self.device, self.flags + self.world * self.LINE, frame, stream)
+
+    def to_host(self, frame, out, stream, sync=False):
+        assert self.rank == 0
+        self.buf.to_host(out, offset=(frame & 1) * self.image_bytes, stream=stream, sync=sync)
+
+    def close(self):
+        self.buf.close()

@@ -198,6 +198,41 @@ const char* ptc_last_error(const ptc_context* ctx);
 int ptc_upload_scene(ptc_context* ctx, const ptc_scene_desc* desc, int32_t* scene_id);
 int ptc_scene_info_get(const ptc_context* ctx, int32_t scene_id, ptc_scene_info* out);
 
+/* -- the step BEFORE Face[]: the mesh as the OBJ loader leaves it ------------------------------
+ * Replaces the de-indexing loop of upload_meshes (scene.cpp:202-283): per shape a list of index
+ * records (tinyobj::index_t: vertex, normal, texcoord index first; `index_stride_ints` ints per
+ * record, 0 -> 3) and a material id per face, over shared attribute arrays (tinyobj::attrib_t).
+ * Every triple becomes one scene::Face with the reference's per-face tangent (scene.cpp:250-261,
+ * same expression order, so the same bits); faces of all shapes are flattened in parallel into
+ * ONE array.  An index outside its attribute array (an OBJ without `vn` / `vt`: the reference
+ * reads out of bounds there) is PTC_ERR_INVALID. */
+typedef struct ptc_indexed_mesh
+{
+  const int32_t* indices;      /* n_indices records of index_stride_ints ints                 */
+  uint64_t n_indices;          /* faces = n_indices / 3 (scene.cpp:222)                       */
+  const int32_t* material_ids; /* one per face (tinyobj mesh_t.material_ids)                  */
+} ptc_indexed_mesh;
+
+typedef struct ptc_indexed_desc
+{
+  const float* vertices;  uint64_t n_vertex_floats;   /* attrib_t.vertices,  xyz per vertex  */
+  const float* normals;   uint64_t n_normal_floats;   /* attrib_t.normals,   xyz per normal  */
+  const float* texcoords; uint64_t n_texcoord_floats; /* attrib_t.texcoords, uv per entry    */
+  const ptc_indexed_mesh* meshes;
+  uint32_t n_meshes;
+  uint32_t index_stride_ints;
+  const ptc_material* materials; uint32_t n_materials; /* as in ptc_scene_desc               */
+  const ptc_light* lights;       uint32_t n_lights;
+  const ptc_texture* textures;   uint32_t n_textures;
+} ptc_indexed_desc;
+
+/* host only (no GPU): faces_out[capacity] in mesh order, mesh_face_counts[n_meshes] (optional) */
+uint64_t ptc_indexed_face_count(const ptc_indexed_desc* desc);
+int ptc_flatten_faces(const ptc_indexed_desc* desc, ptc_face* faces_out, uint64_t capacity,
+                      uint32_t* mesh_face_counts);
+/* flatten + ptc_upload_scene */
+int ptc_upload_scene_indexed(ptc_context* ctx, const ptc_indexed_desc* desc, int32_t* scene_id);
+
 /* Replaces uploadCubemap (gpu_processor.cpp:68-161) after face extraction:
  * `faces` = 6 faces (+x,-x,+y,-y,+z,-z) of size*size RGBA floats, host memory. */
 int ptc_set_cubemap(ptc_context* ctx, const float* faces, uint32_t size, int32_t* cubemap_id);
@@ -387,7 +422,9 @@ int ptc_group_reset_accumulation(ptc_group* g);
  * ptc_flag_signal: after everything enqueued on `stream` so far, store `value` to the (possibly
  *   peer-mapped) 32-bit flag with system-scope release semantics ("my strips of frame k are in").
  * ptc_flag_wait: `stream` waits (a one-block kernel that spins) until flags[i * stride_words]
- *   has reached `value` for every i < n (n <= 256).
+ *   has reached `value` for every i < n (n <= 256).  The producers must already be enqueued or
+ *   be enqueued without synchronising the device in between; a wait of more than 20 s traps
+ *   (the stream then reports a launch failure) instead of hanging the GPU.
  * ptc_memcpy_to_host: device -> host copy on `stream` (sync != 0: waits for it). */
 int ptc_shared_alloc(int device, uint64_t bytes, void** ptr, uint8_t handle[64]);
 int ptc_shared_open(int device, const uint8_t handle[64], void** ptr);

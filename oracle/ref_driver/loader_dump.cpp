@@ -137,6 +137,48 @@ main(int argc, char** argv)
     std::cerr << "usage: ref_loader ASSET_FOLDER SCENE_FILE OUT.ptscene\n";
     return 2;
   }
+  // ref_loader --indexed OBJ_PATH MTL_DIR OUT.ptix : what the reference's vendored tinyobjloader
+  // hands to upload_meshes (scene.cpp:202-283) for this OBJ -- the attribute arrays, and per shape
+  // the index triples and per-face material ids -- BEFORE the reference flattens it into Face[].
+  // Pins ptc_flatten_faces: its output for this file must equal the Face[] of the .ptscene dump.
+  if (argc == 5 && std::string(argv[1]) == "--indexed") {
+    tinyobj::attrib_t attrib;
+    std::vector<tinyobj::shape_t> shapes;
+    std::vector<tinyobj::material_t> materials;
+    std::string err;
+    if (!tinyobj::LoadObj(&attrib, &shapes, &materials, &err, argv[2], argv[3])) { // scene.cpp:341
+      std::cerr << "ref_loader: --indexed: " << err << "\n";
+      return 1;
+    }
+    FILE* fo = fopen(argv[4], "wb");
+    if (!fo) {
+      perror("ref_loader: --indexed output");
+      return 1;
+    }
+    Writer w{ fo };
+    w.raw("PTIX", 4);
+    w.u32(1);
+    auto farr = [&](const std::vector<float>& v) {
+      uint64_t n = v.size();
+      w.raw(&n, 8);
+      w.raw(v.data(), n * 4);
+    };
+    farr(attrib.vertices);
+    farr(attrib.normals);
+    farr(attrib.texcoords);
+    w.u32((uint32_t)shapes.size());
+    static_assert(sizeof(tinyobj::index_t) % 4 == 0, "index_t is a record of ints");
+    w.u32((uint32_t)(sizeof(tinyobj::index_t) / 4)); // ints per index record (vertex, normal, texcoord first)
+    for (const tinyobj::shape_t& sh : shapes) {
+      uint64_t ni = sh.mesh.indices.size(), nm = sh.mesh.material_ids.size();
+      w.raw(&ni, 8);
+      w.raw(sh.mesh.indices.data(), ni * sizeof(tinyobj::index_t));
+      w.raw(&nm, 8);
+      w.raw(sh.mesh.material_ids.data(), nm * 4);
+    }
+    fclose(fo);
+    return 0;
+  }
   std::string folder = argv[1], scene_file = argv[2], out = argv[3];
 
   scene::Scene sc(folder + "/" + scene_file); // gpu_processor.cpp:262-263

@@ -55,6 +55,16 @@ def dump_scenes():
             os.remove(out)
 
 
+def dump_indexed():
+    """indoor_indexed.ptix: the reference's own tinyobj output for indoor.obj (attribute arrays,
+    index records, per-face material ids) BEFORE upload_meshes flattens it (scene.cpp:202-283);
+    ptc_flatten_faces on it must reproduce the Face[] of indoor_plain.ptscene bit for bit."""
+    loader = os.path.join(build_ref.OUT, "ref_loader")
+    obj = os.path.join(build_ref.RC, "assets", "obj")
+    subprocess.check_call([loader, "--indexed", os.path.join(obj, "indoor.obj"), obj + "/",
+                           os.path.join(HERE, "indoor_indexed.ptix")], stderr=subprocess.DEVNULL)
+
+
 def rng_kat(ref: RefCpu):
     frames = [1, 2, 3, 64, 1000]
     kat = {"wang_hash": {str(k): int(ref.wang_hash(k)) for k in frames + [0, 0xFFFFFFFF]},
@@ -93,6 +103,7 @@ if __name__ == "__main__":
     if not build_ref.build_all():
         sys.exit("needs /root/reference")
     dump_scenes()
+    dump_indexed()
     ref = RefCpu()
     rng_kat(ref)
     ref_renders(ref)

@@ -1029,15 +1029,16 @@ def test_full_image_store_and_flags(core):
         flags = shared.address + w * h * 4
         streams = [torch.cuda.Stream(), torch.cuda.Stream()]
         consumer = torch.cuda.Stream()
-        P.core.flag_wait(0, flags, 2, 1, 5, stream=consumer.cuda_stream)   # enqueued FIRST: really waits
         host = np.zeros((h, w), np.uint32)
-        keep = []
+        # everything is allocated and idle BEFORE the waiting kernel is enqueued: from here to the
+        # copy nothing may synchronise the device (the wait kernel spins until both flags are set)
+        accs = [torch.zeros(c.band_rows(w, h, strips=(16, 2, r)), w, 3, device="cuda")
+                for r, c in enumerate([core, other])]
+        torch.cuda.synchronize()
+        P.core.flag_wait(0, flags, 2, 1, 5, stream=consumer.cuda_stream)   # enqueued FIRST: really waits
         for rank, (c, l) in enumerate([(core, L), (other, L2)]):
             strips = (16, 2, rank)
-            bh = c.band_rows(w, h, strips=strips)
-            accb = torch.zeros(bh, w, 3, device="cuda")
-            keep.append(accb)
-            torch.cuda.synchronize()
+            accb = accs[rank]
             c.render(l.sid, l.cid, L.sc, w, h, accb, shared.address, None, bounces=b, frame_nb=2, strips=strips,
                      out_full=True, stream=streams[rank].cuda_stream)
             P.core.flag_signal(0, flags + 4 * rank, 5, stream=streams[rank].cuda_stream)

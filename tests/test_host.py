@@ -439,3 +439,83 @@ def test_bench_has_no_cpu_fallback():
     r = _run_bench("--steps", "1", "--warmup", "0")
     assert r.returncode != 0 and "no CPU fallback" in (r.stderr + r.stdout)
     assert not [l for l in r.stdout.splitlines() if l.startswith("{")]
+
+
+# -- indexed mesh -> Face[] (ptc_flatten_faces) -------------------------------------
+def _faces_u8(sc):
+    return np.ascontiguousarray(sc.faces).view(np.uint8).reshape(-1, 112)
+
+
+def test_flatten_faces_matches_reference_loader_fixture():
+    """The reference's own tinyobj output for indoor.obj (tests/golden/indoor_indexed.ptix, frozen by
+    make_fixtures.py) through ptc_flatten_faces == the Face[] the reference's upload_meshes built
+    from the same file (indoor_plain.ptscene): vertices, normals, uvs, material ids and the per-face
+    tangent of scene.cpp:250-261, bit for bit; faces per mesh too."""
+    mesh = P.ptscene.load_ptix(os.path.join(GOLDEN, "indoor_indexed.ptix"))
+    sc = load_scene("indoor_plain")
+    faces, counts = P.core.flatten_faces(mesh)
+    assert faces.shape == (446, 112) and counts.tolist() == np.asarray(sc.mesh_face_counts).tolist()
+    assert (faces == _faces_u8(sc)).all()
+
+
+def test_flatten_faces_live_against_reference_loader(tmp_path):
+    """Every scene the reference ships, live: ref_loader --indexed (tinyobj) -> ptc_flatten_faces
+    against ref_loader's Face[] dump of the same scene.  Needs /root/reference (build container)."""
+    import subprocess
+    loader = os.path.join(REPO, "oracle", "_ref", "ref_loader")
+    assets = "/root/reference/cuda_opengl/assets"
+    if not (os.path.exists(loader) and os.path.isdir(assets)):
+        pytest.skip("oracle/_ref/ref_loader or /root/reference not present")
+    n_checked = 0
+    for scene in ("indoor", "color_sample", "island", "crate_land", "sss_crate"):
+        objs = [l.split()[1] for l in open(os.path.join(assets, scene + ".scene")) if l.startswith("scene ")]
+        ptix, ptsc = str(tmp_path / "m.ptix"), str(tmp_path / "s.ptscene")
+        obj = os.path.join(assets, objs[0])
+        subprocess.check_call([loader, "--indexed", obj, os.path.dirname(obj) + "/", ptix], stderr=subprocess.DEVNULL)
+        subprocess.check_call([loader, assets, scene + ".scene", ptsc], stderr=subprocess.DEVNULL)
+        mesh = P.ptscene.load_ptix(ptix)
+        sc = P.ptscene.load_ptscene(ptsc)
+        faces, counts = P.core.flatten_faces(mesh)
+        assert counts.tolist() == np.asarray(sc.mesh_face_counts).tolist(), scene
+        assert (faces == _faces_u8(sc)).all(), scene
+        n_checked += faces.shape[0]
+    assert n_checked >= 1000   # 446 + 4 smaller scenes
+
+
+def test_flatten_faces_parallel_and_errors(monkeypatch):
+    """200 k faces: the threaded flattening gives the bytes of the single-threaded one; an index
+    outside its attribute array (an OBJ without normals: tinyobj index -1, which the reference
+    dereferences) is refused; the empty mesh is fine."""
+    rng = np.random.default_rng(4)
+    nv, nf = 50_000, 200_000
+    verts = rng.normal(size=(nv, 3)).astype(np.float32)
+    norms = rng.normal(size=(nv, 3)).astype(np.float32)
+    uvs = rng.random((nv, 2)).astype(np.float32)
+    idx = rng.integers(0, nv, (nf * 3, 3)).astype(np.int32)
+    mids = rng.integers(0, 7, nf).astype(np.int32)
+    shapes = [(idx[:90_000 * 3], mids[:90_000]), (idx[:0], mids[:0]), (idx[90_000 * 3:], mids[90_000:])]
+    mesh = P.ptscene.IndexedMesh(verts, norms, uvs, shapes, stride=3)
+    monkeypatch.setenv("PTC_BUILD_THREADS", "1")
+    one, counts = P.core.flatten_faces(mesh)
+    monkeypatch.setenv("PTC_BUILD_THREADS", "7")
+    many, _ = P.core.flatten_faces(mesh)
+    assert counts.tolist() == [90_000, 0, 110_000] and (one == many).all()
+    # against numpy with the reference's expression order (float32 everywhere, no fused multiply-add)
+    f = one.view(np.float32).reshape(-1, 28)
+    v = verts[idx[:, 0]].reshape(nf, 3, 3)
+    uv = uvs[idx[:, 2]].reshape(nf, 3, 2)
+    assert (f[:, 0:9] == v.reshape(nf, 9)).all() and (f[:, 18:24] == uv.reshape(nf, 6)).all()
+    assert (f[:, 9:18] == norms[idx[:, 1]].reshape(nf, 9)).all()
+    e1, e2 = v[:, 1] - v[:, 0], v[:, 2] - v[:, 0]
+    d1, d2 = uv[:, 1] - uv[:, 0], uv[:, 2] - uv[:, 0]
+    with np.errstate(divide="ignore", invalid="ignore"):
+        det = np.float32(1.0) / (d1[:, 0] * d2[:, 1] - d2[:, 0] * d1[:, 1])
+        tan = det[:, None] * (d2[:, 1:2] * e1 - d1[:, 1:2] * e2)
+    assert (f[:, 24:27].view(np.uint32) == tan.astype(np.float32).view(np.uint32)).all()
+    assert (one.view(np.uint32).reshape(-1, 28)[:, 27] == mids.astype(np.uint32)).all()
+    bad = idx.copy()
+    bad[12345, 1] = -1
+    with pytest.raises(P.PtcError, match="index outside"):
+        P.core.flatten_faces(P.ptscene.IndexedMesh(verts, norms, uvs, [(bad, mids)], stride=3))
+    faces, counts = P.core.flatten_faces(P.ptscene.IndexedMesh(verts, norms, uvs, [], stride=3))
+    assert faces.shape == (0, 112) and counts.size == 0
