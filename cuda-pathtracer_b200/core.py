@@ -83,7 +83,9 @@ EXPORTS = ["ptc_abi_version", "ptc_create", "ptc_destroy", "ptc_last_error", "pt
            "ptc_group_sync", "ptc_group_image", "ptc_group_read_image", "ptc_group_gather_accum",
            "ptc_group_reset_accumulation", "ptc_shared_alloc", "ptc_shared_open", "ptc_shared_close",
            "ptc_shared_free", "ptc_flag_signal", "ptc_flag_wait", "ptc_memcpy_to_host",
-           "ptc_indexed_face_count", "ptc_flatten_faces", "ptc_upload_scene_indexed"]
+           "ptc_indexed_face_count", "ptc_flatten_faces", "ptc_upload_scene_indexed",
+           "ptc_texpack_create", "ptc_texpack_destroy", "ptc_texpack_last_error", "ptc_texpack_add_materials",
+           "ptc_texpack_texture_count", "ptc_texpack_textures"]
 
 _lib = None
 
@@ -122,6 +124,15 @@ def load_library() -> C.CDLL:
         lib.ptc_indexed_face_count.restype = C.c_uint64
         lib.ptc_flatten_faces.restype = C.c_int
         lib.ptc_upload_scene_indexed.restype = C.c_int
+        lib.ptc_texpack_create.restype = C.c_int
+        lib.ptc_texpack_add_materials.restype = C.c_int
+        lib.ptc_texpack_textures.restype = C.c_int
+        lib.ptc_texpack_texture_count.restype = C.c_uint32
+        lib.ptc_texpack_texture_count.argtypes = [C.c_void_p]
+        lib.ptc_texpack_last_error.restype = C.c_char_p
+        lib.ptc_texpack_last_error.argtypes = [C.c_void_p]
+        lib.ptc_texpack_destroy.restype = None
+        lib.ptc_texpack_destroy.argtypes = [C.c_void_p]
         lib.ptc_group_last_error.restype = C.c_char_p
         lib.ptc_group_last_error.argtypes = [C.c_void_p]
         lib.ptc_group_destroy.restype = None
@@ -230,6 +241,67 @@ def flatten_faces(mesh: "ptscene.IndexedMesh"):
     if rc:
         raise PtcError(f"ptc_flatten_faces failed ({rc}): an index outside its attribute array?")
     return faces, counts
+
+
+class TexPacker:
+    """ptc_texpack_*: the material / texture table of MaterialLoader::load, ids continuing across
+    scenes.  Host only."""
+
+    def __init__(self):
+        self.lib = load_library()
+        self.p = C.c_void_p()
+        if self.lib.ptc_texpack_create(C.byref(self.p)):
+            raise PtcError("ptc_texpack_create failed")
+        self._keep = []
+
+    def close(self):
+        if self.p:
+            self.lib.ptc_texpack_destroy(self.p)
+            self.p = C.c_void_p()
+
+    def add_materials(self, mtl: "ptscene.MtlSet") -> np.ndarray:
+        """Returns the scene's Material records (structured array, ptscene.MATERIAL_DTYPE)."""
+        imgs = {}
+        for name, a in mtl.images.items():
+            im = ptscene.PtcImage()
+            im.name = name.encode()
+            if a is not None:
+                a = np.ascontiguousarray(a, np.float32)
+                im.h, im.w, im.nb_chan = a.shape
+                im.data = a.ctypes.data
+            self._keep.append(a)
+            imgs[name] = im
+        n = len(mtl.materials)
+        ent = (ptscene.PtcMtlEntry * max(1, n))()
+        for k, m in enumerate(mtl.materials):
+            ent[k].diffuse[:] = [float(x) for x in m["diffuse"]]
+            ent[k].specular[:] = [float(x) for x in m["specular"]]
+            ent[k].ior = m["ior"]
+            for field, name in zip(("diffuse_map", "specular_map", "normal_map"), m["names"]):
+                if name:
+                    if name not in imgs:   # named but not handed over: treated like a failed load
+                        imgs[name] = ptscene.PtcImage()
+                        imgs[name].name = name.encode()
+                    setattr(ent[k], field, C.pointer(imgs[name]))
+        self._keep.append(imgs)
+        out = np.zeros(n, ptscene.MATERIAL_DTYPE)
+        rc = self.lib.ptc_texpack_add_materials(self.p, ent, C.c_uint32(n), _ptr(out))
+        if rc:
+            raise PtcError(f"ptc_texpack_add_materials failed ({rc}): {self.lib.ptc_texpack_last_error(self.p).decode()}")
+        return out
+
+    def textures(self) -> list:
+        """Copies of the global texture table so far: float32 arrays (h, w, nb_chan)."""
+        n = int(self.lib.ptc_texpack_texture_count(self.p))
+        arr = (ptscene.PtcTexture * max(1, n))()
+        if self.lib.ptc_texpack_textures(self.p, arr, C.c_uint32(n)):
+            raise PtcError("ptc_texpack_textures failed")
+        out = []
+        for i in range(n):
+            t = arr[i]
+            cnt = t.w * t.h * t.nb_chan
+            out.append(np.ctypeslib.as_array((C.c_float * cnt).from_address(t.data)).copy().reshape(t.h, t.w, t.nb_chan))
+        return out
 
 
 class Core:

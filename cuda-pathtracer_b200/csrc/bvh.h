@@ -39,7 +39,7 @@ struct alignas(16) Node8
   uint32_t tri_base;   // index of this node's first triangle record
   uint32_t valid24;    // bit 3s+j: leaf slot s has a j-th triangle
   uint32_t occupied;   // bit s: slot s is not empty (diagnostic; the kernel needs imask/valid24 only)
-#if !defined(PTC_NODE_LAYOUT) || PTC_NODE_LAYOUT == 1
+#if defined(PTC_NODE_LAYOUT) && PTC_NODE_LAYOUT == 1
   // [axis][0 = lower planes, 1 = upper planes][slot]: the 32 bytes of one axis are one load
   uint16_t planes[3][2][8];
   uint16_t& lo_q(int axis, int slot) { return planes[axis][0][slot]; }

@@ -461,8 +461,10 @@ k_wave(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
 #ifndef PTC_EXTEND_BLOCKS
 #define PTC_EXTEND_BLOCKS 3
 #endif
+// batched triangle loads + node-line prefetch by every lane (traverse.cuh TB / PF = 2): -5 % frame
+// time on the 10 M-triangle scene, -2 % at 180 k triangles (profiles/r2_experiment_log.md)
 #ifndef PTC_TRI_BATCH
-#define PTC_TRI_BATCH 0
+#define PTC_TRI_BATCH 1
 #endif
 template <bool STATS>
 __global__ void __launch_bounds__(kBlock, PTC_EXTEND_BLOCKS)

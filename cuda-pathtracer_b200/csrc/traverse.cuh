@@ -15,8 +15,11 @@ namespace ptc {
 
 // node layout: 0 = lo[3][8], hi[3][8] (six 16-byte plane loads addressed by ray octant),
 // 1 = [axis][lo | hi][8] (three 32-byte loads + register selects); must match bvh_builder.cpp
+// Measured on B200 (profiles/r2_experiment_log.md): layout 1 is 1-1.4 % SLOWER than layout 0 on the
+// 28 KB and the 1.4 GB scene and equal once the triangle loads are batched -- the 24 register
+// selects cost what the three fewer load instructions save -- so layout 0 stays the default.
 #ifndef PTC_NODE_LAYOUT
-#define PTC_NODE_LAYOUT 1
+#define PTC_NODE_LAYOUT 0
 #endif
 
 // ---------------------------------------------------------------------------
@@ -380,7 +383,7 @@ trav_init_any(const DScene& sc, Trav& T, const float3 o, const float3 d)
 // on the 10 M-triangle scene (k_extend, 80 registers, no spills); +0.3 % in the fused path kernels,
 // whose 64-register cap turns the register pairs into extra spills -- so only k_extend asks for it.
 #ifndef PTC_PREFETCH_NODE
-#define PTC_PREFETCH_NODE 0
+#define PTC_PREFETCH_NODE 2
 #endif
 // the same two switches for the traversal inside the fused path kernels (64-register cap)
 #ifndef PTC_PATH_PF

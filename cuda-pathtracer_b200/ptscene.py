@@ -272,3 +272,62 @@ def load_ptix(path) -> IndexedMesh:
         off += 8 + 4 * nm
         shapes.append((idx, mids))
     return IndexedMesh(arrs[0], arrs[1], arrs[2], shapes, stride)
+
+
+# ---------------------------------------------------------------------------------------------
+# material / texture table input (include/ptcore.h ptc_mtl_entry, ptc_image)
+# ---------------------------------------------------------------------------------------------
+class PtcImage(C.Structure):
+    _fields_ = [("w", C.c_int32), ("h", C.c_int32), ("nb_chan", C.c_int32), ("_pad", C.c_int32),
+                ("data", C.c_void_p), ("name", C.c_char_p)]
+
+
+class PtcMtlEntry(C.Structure):
+    _fields_ = [("diffuse", C.c_float * 3), ("specular", C.c_float * 3), ("ior", C.c_float), ("_pad", C.c_uint32),
+                ("diffuse_map", C.POINTER(PtcImage)), ("specular_map", C.POINTER(PtcImage)),
+                ("normal_map", C.POINTER(PtcImage))]
+
+
+@dataclass
+class MtlSet:
+    """Materials of one OBJ as tinyobj parsed them + the decoded images they name."""
+    materials: list   # dicts: diffuse (3,), specular (3,), ior, names = (diffuse, specular, normal)
+    images: dict      # name -> float32 array (h, w, nb_chan), or None when the file failed to load
+
+
+def load_ptmt(path) -> MtlSet:
+    """Reads a .ptmt file (the reference loader's tinyobj materials + stb-decoded images, written
+    by the fixture tooling, tests/golden/make_fixtures.py)."""
+    raw = open(path, "rb").read()
+    assert raw[:4] == b"PTMT" and struct.unpack_from("<I", raw, 4)[0] == 1
+    off = 8
+
+    def u32():
+        nonlocal off
+        v = struct.unpack_from("<I", raw, off)[0]
+        off += 4
+        return v
+
+    def text():
+        nonlocal off
+        n = u32()
+        s = raw[off:off + n].decode()
+        off += n
+        return s
+
+    mats = []
+    for _ in range(u32()):
+        f = np.frombuffer(raw, np.float32, 7, off).copy()
+        off += 28
+        mats.append({"diffuse": f[0:3], "specular": f[3:6], "ior": float(f[6]), "names": (text(), text(), text())})
+    images = {}
+    for _ in range(u32()):
+        name = text()
+        w, h, nc = struct.unpack_from("<iii", raw, off)
+        off += 12
+        if nc:
+            images[name] = np.frombuffer(raw, np.float32, w * h * nc, off).copy().reshape(h, w, nc)
+            off += 4 * w * h * nc
+        else:
+            images[name] = None
+    return MtlSet(mats, images)

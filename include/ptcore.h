@@ -198,6 +198,45 @@ const char* ptc_last_error(const ptc_context* ctx);
 int ptc_upload_scene(ptc_context* ctx, const ptc_scene_desc* desc, int32_t* scene_id);
 int ptc_scene_info_get(const ptc_context* ctx, int32_t scene_id, ptc_scene_info* out);
 
+/* -- the material / texture table (replaces MaterialLoader::load, material_loader.cpp:153-401) --
+ * Input: per MTL material its constants and its DECODED maps (stbi_loadf output, linear floats;
+ * `name` = the texture name in the MTL, which is the cache key; a NULL map pointer or an empty
+ * name = the material names no such map; data == NULL or nb_chan == 0 = the file failed to load).
+ * Output: scene::Material per material with the reference's texture ids, and the global texture
+ * table: one RGBA texture per material (rgb = diffuse, a = specular mix; packed from a 3-channel
+ * and a 1-channel map, from one map and the material's constant, or a 1x1 unit texture) plus the
+ * normal maps.  Ids and caches live in the packer and continue across calls exactly like the
+ * reference's singleton across scenes: both maps -> packed once per name pair; one map -> packed
+ * again for every material naming it; failed diffuse / specular map -> unit texture; failed
+ * normal map -> -1.  Diffuse and specular maps of different sizes are PTC_ERR_INVALID (the
+ * reference rescales with stb_image_resize, third-party: resize first). */
+typedef struct ptc_image
+{
+  int32_t w, h, nb_chan;
+  int32_t _pad;
+  const float* data;
+  const char* name;
+} ptc_image;
+
+typedef struct ptc_mtl_entry
+{
+  float diffuse[3];  /* Kd */
+  float specular[3]; /* Ks: default specular mix = (Ks.r + Ks.g + Ks.b) / 3 (:174-176) */
+  float ior;         /* Ni */
+  uint32_t _pad;
+  const ptc_image* diffuse_map;  /* map_Kd */
+  const ptc_image* specular_map; /* map_Ks */
+  const ptc_image* normal_map;   /* map_bump if given, else norm (:184-187) */
+} ptc_mtl_entry;
+
+typedef struct ptc_texpack ptc_texpack;
+int ptc_texpack_create(ptc_texpack** out);
+void ptc_texpack_destroy(ptc_texpack* p);
+const char* ptc_texpack_last_error(const ptc_texpack* p);
+int ptc_texpack_add_materials(ptc_texpack* p, const ptc_mtl_entry* mats, uint32_t n, ptc_material* out);
+uint32_t ptc_texpack_texture_count(const ptc_texpack* p);
+int ptc_texpack_textures(const ptc_texpack* p, ptc_texture* out, uint32_t capacity);
+
 /* -- the step BEFORE Face[]: the mesh as the OBJ loader leaves it ------------------------------
  * Replaces the de-indexing loop of upload_meshes (scene.cpp:202-283): per shape a list of index
  * records (tinyobj::index_t: vertex, normal, texcoord index first; `index_stride_ints` ints per
@@ -422,9 +461,11 @@ int ptc_group_reset_accumulation(ptc_group* g);
  * ptc_flag_signal: after everything enqueued on `stream` so far, store `value` to the (possibly
  *   peer-mapped) 32-bit flag with system-scope release semantics ("my strips of frame k are in").
  * ptc_flag_wait: `stream` waits (a one-block kernel that spins) until flags[i * stride_words]
- *   has reached `value` for every i < n (n <= 256).  The producers must already be enqueued or
- *   be enqueued without synchronising the device in between; a wait of more than 20 s traps
- *   (the stream then reports a launch failure) instead of hanging the GPU.
+ *   has reached `value` for every i < n (n <= 256).  Enqueue it AFTER the producers that run in
+ *   the same process on the same GPU (a spinning kernel enqueued before them can sit in front of
+ *   them in a shared hardware queue) and never synchronise the device while it may be spinning;
+ *   a wait of more than 20 s traps (the stream then reports a launch failure) instead of hanging
+ *   the GPU.
  * ptc_memcpy_to_host: device -> host copy on `stream` (sync != 0: waits for it). */
 int ptc_shared_alloc(int device, uint64_t bytes, void** ptr, uint8_t handle[64]);
 int ptc_shared_open(int device, const uint8_t handle[64], void** ptr);

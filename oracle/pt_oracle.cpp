@@ -805,7 +805,8 @@ struct O2Node // mirrors the 128-byte layout documented in cuda-pathtracer_b200/
   uint32_t tri_base;
   uint32_t valid24;
   uint32_t occupied;
-  uint16_t planes[3][2][8]; // [axis][lower | upper][slot]: half floats holding the 8-bit quantised planes
+  uint16_t lo[3][8]; // half floats holding the 8-bit quantised planes
+  uint16_t hi[3][8];
 };
 static_assert(sizeof(O2Node) == 128, "node layout");
 
@@ -888,7 +889,7 @@ o2_closest(const O2Node* nodes, const O2Tri* tris, const ptc_scene_desc* desc, u
           uint32_t bits = (uint32_t)n.e[a] << 23;
           float sc;
           std::memcpy(&sc, &bits, 4);
-          float lo = n.origin[a] + o2_half(n.planes[a][0][i]) * sc, hi = n.origin[a] + o2_half(n.planes[a][1][i]) * sc;
+          float lo = n.origin[a] + o2_half(n.lo[a][i]) * sc, hi = n.origin[a] + o2_half(n.hi[a][i]) * sc;
           if (lo > hi) { // empty slot (inverted box)
             tmin = 1.0f, tmax = 0.0f;
             break;

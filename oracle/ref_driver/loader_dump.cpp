@@ -13,6 +13,7 @@
 #define STB_IMAGE_IMPLEMENTATION
 #include <stb/stb_image.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
@@ -175,6 +176,64 @@ main(int argc, char** argv)
       w.raw(sh.mesh.indices.data(), ni * sizeof(tinyobj::index_t));
       w.raw(&nm, 8);
       w.raw(sh.mesh.material_ids.data(), nm * 4);
+    }
+    fclose(fo);
+    return 0;
+  }
+  // ref_loader --materials OBJ_PATH MTL_DIR OUT.ptmt : the INPUT of MaterialLoader::load
+  // (material_loader.cpp:164-197) for this OBJ: per tinyobj material Kd, Ks, ior and the three
+  // texture names it looks at (diffuse, specular, bump-or-normal), then every distinct image
+  // decoded exactly as checkAndupload does (stbi_loadf(base + "/" + name, STBI_default), :84-114).
+  // Pins ptc_texpack_*: its materials / texture table for this input must equal the .ptscene dump.
+  if (argc == 5 && std::string(argv[1]) == "--materials") {
+    tinyobj::attrib_t attrib;
+    std::vector<tinyobj::shape_t> shapes;
+    std::vector<tinyobj::material_t> materials;
+    std::string err;
+    if (!tinyobj::LoadObj(&attrib, &shapes, &materials, &err, argv[2], argv[3])) {
+      std::cerr << "ref_loader: --materials: " << err << "\n";
+      return 1;
+    }
+    FILE* fo = fopen(argv[4], "wb");
+    if (!fo) {
+      perror("ref_loader: --materials output");
+      return 1;
+    }
+    Writer w{ fo };
+    w.raw("PTMT", 4);
+    w.u32(1);
+    auto str = [&](const std::string& s) {
+      w.u32((uint32_t)s.size());
+      w.raw(s.data(), s.size());
+    };
+    std::vector<std::string> names;
+    auto want = [&](const std::string& n) {
+      if (!n.empty() && std::find(names.begin(), names.end(), n) == names.end())
+        names.push_back(n);
+    };
+    w.u32((uint32_t)materials.size());
+    for (const tinyobj::material_t& m : materials) {
+      for (int k = 0; k < 3; ++k)
+        w.f32(m.diffuse[k]);
+      for (int k = 0; k < 3; ++k)
+        w.f32(m.specular[k]);
+      w.f32(m.ior);
+      const std::string nm = !m.bump_texname.empty() ? m.bump_texname : m.normal_texname; // :184-187
+      str(m.diffuse_texname), str(m.specular_texname), str(nm);
+      want(m.diffuse_texname), want(m.specular_texname), want(nm);
+    }
+    w.u32((uint32_t)names.size());
+    for (const std::string& n : names) {
+      int iw = 0, ih = 0, nc = 0;
+      float* px = stbi_loadf((std::string(argv[3]) + "/" + n).c_str(), &iw, &ih, &nc, STBI_default);
+      str(n);
+      if (!px)
+        iw = ih = nc = 0;
+      w.i32(iw), w.i32(ih), w.i32(nc);
+      if (px) {
+        w.raw(px, (size_t)iw * ih * nc * 4);
+        stbi_image_free(px);
+      }
     }
     fclose(fo);
     return 0;

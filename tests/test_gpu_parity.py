@@ -1014,7 +1014,7 @@ def test_full_image_store_and_flags(core):
     of a one-process-per-GPU job without a collective.  Two contexts render alternate strips into
     one shared full-size image (an IPC handle can only be opened from ANOTHER process, so the
     owner's pointer is used here); a flag kernel per producer, a waiting kernel on the consumer
-    stream enqueued first, then the copy to the host: == the single-context frame."""
+    stream, then the copy to the host: == the single-context frame."""
     import torch
     L = loaded(core, "indoor_tex")
     w, h, b = 1280, 720, 3
@@ -1030,20 +1030,24 @@ def test_full_image_store_and_flags(core):
         streams = [torch.cuda.Stream(), torch.cuda.Stream()]
         consumer = torch.cuda.Stream()
         host = np.zeros((h, w), np.uint32)
-        # everything is allocated and idle BEFORE the waiting kernel is enqueued: from here to the
-        # copy nothing may synchronise the device (the wait kernel spins until both flags are set)
         accs = [torch.zeros(c.band_rows(w, h, strips=(16, 2, r)), w, 3, device="cuda")
                 for r, c in enumerate([core, other])]
         torch.cuda.synchronize()
-        P.core.flag_wait(0, flags, 2, 1, 5, stream=consumer.cuda_stream)   # enqueued FIRST: really waits
         for rank, (c, l) in enumerate([(core, L), (other, L2)]):
             strips = (16, 2, rank)
             accb = accs[rank]
             c.render(l.sid, l.cid, L.sc, w, h, accb, shared.address, None, bounces=b, frame_nb=2, strips=strips,
                      out_full=True, stream=streams[rank].cuda_stream)
             P.core.flag_signal(0, flags + 4 * rank, 5, stream=streams[rank].cuda_stream)
+        # the consumer's wait is enqueued AFTER the producers of its own process, as a renderer does
+        # (rank 0 waits after its own frame; the other producers are other processes): a spinning
+        # kernel enqueued BEFORE local producers can sit in front of them in a shared hardware queue
+        P.core.flag_wait(0, flags, 2, 1, 5, stream=consumer.cuda_stream)
         shared.to_host(host, stream=consumer.cuda_stream, sync=True)
         assert (host == out.cpu().numpy().view(np.uint32)).all()
+        # flags are monotonic: a wait for an older frame passes at once, wrap-safe compare
+        P.core.flag_wait(0, flags, 2, 1, 3, stream=consumer.cuda_stream)
+        consumer.synchronize()
     finally:
         torch.cuda.synchronize()
         other.close()

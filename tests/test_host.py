@@ -120,14 +120,14 @@ def test_ptscene_parser_rejects_bad_input():
 # -- host BVH builder --------------------------------------------------------------------------
 NODE = np.dtype([("origin", "<f4", 3), ("e", "u1", 3), ("imask", "u1"), ("child_base", "<u4"),
                  ("tri_base", "<u4"), ("valid24", "<u4"), ("occupied", "<u4"),
-                 ("planes", "<f2", (3, 2, 8))])   # [axis][lower | upper][slot], csrc/bvh.h
+                 ("qlo", "<f2", (3, 8)), ("qhi", "<f2", (3, 8))])
 TRI = np.dtype([("v0", "<f4", 3), ("e1", "<f4", 3), ("e2", "<f4", 3), ("face_id", "<u4"), ("_pad", "<u4", 2)])
 
 
 def decode_child_box(n, i):
     scale = np.array([np.array([int(e) << 23], np.uint32).view(np.float32)[0] for e in n["e"]], np.float64)
-    lo = n["origin"].astype(np.float64) + n["planes"][:, 0, i].astype(np.float64) * scale
-    hi = n["origin"].astype(np.float64) + n["planes"][:, 1, i].astype(np.float64) * scale
+    lo = n["origin"].astype(np.float64) + n["qlo"][:, i].astype(np.float64) * scale
+    hi = n["origin"].astype(np.float64) + n["qhi"][:, i].astype(np.float64) * scale
     return lo, hi
 
 
@@ -164,10 +164,10 @@ def test_bvh_structure(name):
             cnt = bin((int(n["valid24"]) >> (3 * i)) & 7).count("1")
             if not ((int(n["occupied"]) >> i) & 1):
                 assert not inner and cnt == 0
-                assert (n["planes"][:, 0, i] > n["planes"][:, 1, i]).all()   # inverted box: never hit
+                assert (n["qlo"][:, i] > n["qhi"][:, i]).all()   # inverted box: never hit
                 continue
             lo, hi = decode_child_box(n, i)
-            assert (n["planes"][:, 0, i] == np.round(n["planes"][:, 0, i])).all() and n["planes"][:, 1, i].max() <= 255
+            assert (n["qlo"][:, i] == np.round(n["qlo"][:, i])).all() and n["qhi"][:, i].max() <= 255
             if inner:
                 assert cnt == 0
                 rel = bin(int(n["imask"]) & ((1 << i) - 1)).count("1")
@@ -519,3 +519,78 @@ def test_flatten_faces_parallel_and_errors(monkeypatch):
         P.core.flatten_faces(P.ptscene.IndexedMesh(verts, norms, uvs, [(bad, mids)], stride=3))
     faces, counts = P.core.flatten_faces(P.ptscene.IndexedMesh(verts, norms, uvs, [], stride=3))
     assert faces.shape == (0, 112) and counts.size == 0
+
+
+# -- material / texture table (ptc_texpack_*) ----------------------------------------
+def _same_textures(got, want):
+    return len(got) == len(want) and all(
+        a.shape == np.asarray(b).shape and (a.view(np.uint32) == np.ascontiguousarray(b, np.float32).view(np.uint32)).all()
+        for a, b in zip(got, want))
+
+
+def test_texpack_matches_reference_loader_fixture():
+    """tests/golden/mtl_cases.ptmt (tinyobj materials + stb-decoded images of a synthetic OBJ whose
+    16 materials walk every branch of MaterialLoader::getTextureId, frozen by make_fixtures.py)
+    through ptc_texpack_add_materials == what the REFERENCE's loader produced for the same files
+    (mtl_cases.ptscene): Material records with their texture ids, and every texel of the 16-entry
+    texture table -- unit textures, the three pack forms, cache hits, failed loads -- bit for bit."""
+    want = P.ptscene.load_ptscene(os.path.join(GOLDEN, "mtl_cases.ptscene"))
+    mtl = P.ptscene.load_ptmt(os.path.join(GOLDEN, "mtl_cases.ptmt"))
+    pk = P.core.TexPacker()
+    try:
+        mats = pk.add_materials(mtl)
+        assert mats.tolist() == want.materials.tolist()
+        # the branches are really in there
+        ids = [int(m[0]) for m in mats.tolist()]
+        assert ids[3] == ids[4] and ids[8] == ids[9]          # both maps: cached under the name pair
+        assert ids[1] != ids[5] and ids[11] != ids[12]        # one map / both failed: never cached
+        assert mats["normal_map"][3] == mats["normal_map"][4] == mats["normal_map"][15] and mats["normal_map"][5] == -1
+        tex = pk.textures()
+        assert _same_textures(tex, want.textures)
+        assert tex[0].shape == (1, 1, 4) and np.allclose(tex[0][0, 0], (0.1, 0.2, 0.3, 0.6))   # Kd, mean(Ks)
+        # the table grows across scenes and the caches survive (the reference's loader is a singleton
+        # whose _id / _packed_tex are never reset, material_loader.cpp:153-162): same files again
+        n0 = len(tex)
+        again = pk.add_materials(mtl)
+        assert again["diffuse_spec_map"][3] == mats["diffuse_spec_map"][3]        # cached pair
+        assert again["normal_map"][3] == mats["normal_map"][3]                    # cached normal map
+        assert again["diffuse_spec_map"][0] == n0 and again["diffuse_spec_map"][1] == n0 + 1   # new ids continue
+        assert len(pk.textures()) > n0
+    finally:
+        pk.close()
+
+
+def test_texpack_live_on_the_textured_indoor_scene(tmp_path):
+    """The headline scene with its real textures (66 MB of floats), live against the reference's
+    loader.  Needs /root/reference (build container)."""
+    import subprocess
+    sys.path.insert(0, os.path.join(REPO, "oracle"))
+    import build_ref
+    loader = os.path.join(REPO, "oracle", "_ref", "ref_loader")
+    if not (os.path.exists(loader) and build_ref.have_reference()):
+        pytest.skip("oracle/_ref/ref_loader or /root/reference not present")
+    fixed = build_ref.fixed_assets()   # MTL back-slashes fixed (SURVEY F6), as for indoor_tex.ptscene
+    obj = os.path.join(fixed, "obj", "indoor.obj")
+    ptmt = str(tmp_path / "indoor.ptmt")
+    subprocess.check_call([loader, "--materials", obj, os.path.dirname(obj) + "/", ptmt], stderr=subprocess.DEVNULL)
+    want = load_scene("indoor_tex")
+    pk = P.core.TexPacker()
+    try:
+        mats = pk.add_materials(P.ptscene.load_ptmt(ptmt))
+        assert mats.tolist() == want.materials.tolist()
+        assert _same_textures(pk.textures(), want.textures)
+    finally:
+        pk.close()
+
+
+def test_texpack_size_mismatch_is_refused():
+    rgb = np.random.default_rng(0).random((4, 4, 3)).astype(np.float32)
+    a = np.random.default_rng(1).random((2, 2, 1)).astype(np.float32)
+    mtl = P.ptscene.MtlSet([{"diffuse": [1, 1, 1], "specular": [0, 0, 0], "ior": 1.0, "names": ("d.png", "s.png", "")}],
+                           {"d.png": rgb, "s.png": a})
+    pk = P.core.TexPacker()
+    try:
+        with pytest.raises(P.PtcError, match="differ in size"):
+            pk.add_materials(mtl)
+    finally:
+        pk.close()

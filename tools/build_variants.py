@@ -11,7 +11,7 @@ for spec in sys.argv[1:]:
     cmd = ["/usr/local/cuda/bin/nvcc", "-std=c++17", "-O3", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a",
            "-Xcompiler", "-fPIC,-O2,-pthread,-ffp-contract=off", "-shared", "-I", os.path.join(REPO, "include"), "-I", CSRC]
     cmd += ["-D" + d for d in defs.split(",") if d]
-    cmd += [os.path.join(CSRC, f) for f in ("ptcore.cu", "kernels.cu", "group.cu", "bvh_builder.cpp", "flatten.cpp")] + ["-o", os.path.join(OUT, name + ".so")]
+    cmd += [os.path.join(CSRC, f) for f in ("ptcore.cu", "kernels.cu", "group.cu", "bvh_builder.cpp", "flatten.cpp", "texpack.cpp")] + ["-o", os.path.join(OUT, name + ".so")]
     procs.append((name, subprocess.Popen(cmd)))
 for name, p in procs:
     print(name, "rc", p.wait())
