@@ -69,7 +69,7 @@ class PtcHostBvh(C.Structure):
                 ("max_depth", C.c_uint32), ("_owner", C.c_void_p)]
 
 
-EXPORTS = ["ptc_abi_version", "ptc_create", "ptc_destroy", "ptc_last_error", "ptc_upload_scene",
+EXPORTS = ["ptc_abi_version", "ptc_render_static", "ptc_create", "ptc_destroy", "ptc_last_error", "ptc_upload_scene",
            "ptc_scene_info_get", "ptc_set_cubemap", "ptc_render", "ptc_render_host",
            "ptc_reset_accumulation", "ptc_counters_get", "ptc_counters_reset",
            "ptc_trace_primary", "ptc_intersect_rays", "ptc_debug_rng", "ptc_host_bvh_build",
@@ -92,6 +92,9 @@ _lib = None
 
 class PtcError(RuntimeError):
     pass
+
+
+STATIC_MAX_PIXELS = 262144  # PTC_STATIC_MAX_PIXELS (include/ptcore.h)
 
 
 def load_library() -> C.CDLL:
@@ -119,7 +122,7 @@ def load_library() -> C.CDLL:
                      "ptc_group_set_cubemap", "ptc_group_render", "ptc_group_sync", "ptc_group_read_image",
                      "ptc_group_gather_accum", "ptc_group_reset_accumulation", "ptc_shared_alloc",
                      "ptc_shared_open", "ptc_shared_close", "ptc_shared_free", "ptc_flag_signal",
-                     "ptc_flag_wait", "ptc_memcpy_to_host"]:
+                     "ptc_flag_wait", "ptc_memcpy_to_host", "ptc_render_static"]:
             getattr(lib, name).restype = C.c_int
         lib.ptc_indexed_face_count.restype = C.c_uint64
         lib.ptc_flatten_faces.restype = C.c_int
@@ -447,6 +450,12 @@ class Core:
         """Device-pointer render call (accum / out_rgba / radiance_out are device buffers)."""
         a = self._args(*args, **kw)
         self._check(self.lib.ptc_render(self.ctx, C.byref(a)), "ptc_render")
+
+    def render_static(self, *args, **kw):
+        """ptc_render without any allocation: scratch in the library's file-scope device array
+        (at most STATIC_MAX_PIXELS pixels per call; calls on one device must not overlap)."""
+        a = self._args(*args, **kw)
+        self._check(self.lib.ptc_render_static(self.ctx, C.byref(a)), "ptc_render_static")
 
     def upload_scene_indexed(self, mesh, scene) -> int:
         """ptc_upload_scene_indexed: `mesh` = ptscene.IndexedMesh, materials / lights / textures of `scene`."""

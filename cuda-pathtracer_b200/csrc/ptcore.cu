@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1093,6 +1094,85 @@ ptc_render(ptc_context* ctx, const ptc_render_args* args)
     return fail(ctx, PTC_ERR_INVALID, "accum is required");
   return enqueue_frame(ctx, args, fp, (float*)args->accum, (uint32_t*)args->out_rgba,
                        (float*)args->radiance_out, (cudaStream_t)args->stream);
+}
+
+// ---- ptc_render_static: the frame with no allocation -------------------------------------------------
+// Scratch of one pipeline of launches (two ray queues, hit records, parked pixels, queue / work
+// counters) for PTC_STATIC_MAX_PIXELS pixels, in a file-scope device array: every device that loads
+// the library holds it until exit.  Host code only ever names it in cudaGetSymbolAddress.
+namespace {
+
+constexpr size_t kStaticSlotBytes = (size_t)PTC_STATIC_MAX_PIXELS * 16; // one float4 / uint4 per queue slot
+constexpr size_t kStaticCountBytes = (sizeof(uint32_t) * kCountSlots + 255) & ~(size_t)255;
+constexpr size_t kStaticBytes = 11 * kStaticSlotBytes + kStaticCountBytes;
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu;
+unsigned char* g_static_base[kStaticMaxDevices] = {};
+
+// Device address of the array on `device` (which must be current); looked up once per device.
+cudaError_t
+static_scratch_base(int device, unsigned char** out)
+{
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_base[device]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess)
+      return e;
+    g_static_base[device] = (unsigned char*)p;
+  }
+  *out = g_static_base[device];
+  return cudaSuccess;
+}
+
+} // namespace
+
+int
+ptc_render_static(ptc_context* ctx, const ptc_render_args* args)
+{
+  if (!ctx)
+    return PTC_ERR_INVALID;
+  if (ctx->device < 0 || ctx->device >= kStaticMaxDevices)
+    return fail(ctx, PTC_ERR_INVALID, "ptc_render_static: device ordinal beyond the per-device address table");
+  DeviceGuard g(ctx->device);
+  // geometry first: an oversized frame is refused before the frame counter moves
+  FrameParams fp;
+  memset(&fp, 0, sizeof(fp));
+  if (args && args->width && args->height && band_geometry(args, fp)) {
+    const uint64_t px = (uint64_t)fp.band_rows * fp.width;
+    if (px > PTC_STATIC_MAX_PIXELS) {
+      char msg[160];
+      snprintf(msg, sizeof(msg), "ptc_render_static: band of %llu pixels exceeds the static scratch limit of %u pixels",
+               (unsigned long long)px, (unsigned)PTC_STATIC_MAX_PIXELS);
+      return fail(ctx, PTC_ERR_INVALID, msg);
+    }
+  }
+  int rc = fill_frame(ctx, args, fp, true);
+  if (rc)
+    return rc;
+  if (!args->accum)
+    return fail(ctx, PTC_ERR_INVALID, "accum is required");
+  unsigned char* base = nullptr;
+  CUDA_TRY(ctx, static_scratch_base(ctx->device, &base));
+  Lane L;
+  float4* slot = (float4*)base;
+  const size_t P = PTC_STATIC_MAX_PIXELS;
+  for (RayQueue& q : L.q) {
+    q.o = slot, q.d = slot + P, q.thr = slot + 2 * P, q.acc = slot + 3 * P;
+    slot += 4 * P;
+  }
+  L.hits = (uint4*)slot;
+  L.hits2 = (uint4*)(slot + P);
+  L.done = slot + 2 * P;
+  L.counts = (uint32_t*)(base + 11 * kStaticSlotBytes); // cleared by enqueue_part on the caller's stream
+  fp.part_row0 = 0;
+  fp.part_rows = fp.band_rows;
+  const FrameOut fo{ (float*)args->accum, (uint32_t*)args->out_rgba, (float*)args->radiance_out,
+                     (args->flags & PTC_OUT_FULL_IMAGE) ? 1u : 0u };
+  return enqueue_part(ctx, args, fp, fo, (cudaStream_t)args->stream, L, false, nullptr);
 }
 
 int

@@ -345,6 +345,24 @@ int ptc_set_cubemap_from_array(ptc_context* ctx, const void* cuda_array, int32_t
  * RGBA8 written to `out_rgba`.  Asynchronous on args->stream, no hidden syncs. */
 int ptc_render(ptc_context* ctx, const ptc_render_args* args);
 
+/* ptc_render for callers that cannot allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, same frame counter and the same bits in accum / out_rgba /
+ * radiance_out as ptc_render, but the frame's scratch (ray queues, hit records, parked pixels,
+ * counters: 176 bytes per pixel) is a file-scope device array inside the library instead of
+ * cudaMalloc'ed context state, so the call allocates nothing (no cudaMalloc / cudaFree / allocating
+ * library routine) and runs the frame as one pipeline on args->stream.
+ *   limit:  a band of at most PTC_STATIC_MAX_PIXELS pixels (rows rendered x width; 640x360 fits);
+ *           larger calls fail with PTC_ERR_INVALID and a message in ptc_last_error, and leave the
+ *           frame counter untouched.  The array is 44 MiB and every GPU that loads the library
+ *           holds it until exit.
+ *   shared: every call on a device -- from any context -- uses the same array.  It keeps the last
+ *           call's contents; the counters that must start at zero are cleared on args->stream
+ *           before the first launch.  Calls that overlap on the GPU (two streams, two contexts of
+ *           one device) race: serialise them.  ptc_render is unaffected (its scratch is its own). */
+#define PTC_STATIC_MAX_PIXELS 262144u
+int ptc_render_static(ptc_context* ctx, const ptc_render_args* args);
+
 /* Same, but accum / out_rgba / radiance_out are HOST buffers: accum is copied
  * host->device only when `upload_accum` != 0 (first frame of a resumed
  * accumulation), rendered, and out_rgba (and accum when `download_accum`)
