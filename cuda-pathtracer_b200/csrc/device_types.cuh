@@ -18,6 +18,10 @@ constexpr int kShadeVec = 5;          // float4 per ShadeRecord
 // descending until it has tested some triangles)
 constexpr int kStackSize = 40;
 constexpr int kTriBacklog = 8;
+// shared-memory copy of a small scene's BVH (SharedSceneStack, traverse.cuh): node / triangle record
+// strides, and the deferred-triangle-group backlog of that form (8 KB less stack per CTA)
+constexpr uint32_t kSmemNodeBytes = 144, kSmemTriBytes = 48;
+constexpr int kSmemSceneBacklog = 4;
 constexpr int kBlock = 256;           // threads per CTA of the path kernels (8 warps)
 constexpr int kTileW = 8, kTileH = 4; // pixels one warp covers in the first wavefront stage
 

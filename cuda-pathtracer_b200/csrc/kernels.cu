@@ -17,6 +17,8 @@
 // No tensor cores (traversal is not a dense contraction), no RT cores (B200 has none).
 #include "kernels.cuh"
 
+#include <type_traits>
+
 #include "shade.cuh"
 
 namespace ptc {
@@ -37,7 +39,10 @@ warp_sum(uint32_t v)
 #ifndef PTC_PATH_BLOCKS
 #define PTC_PATH_BLOCKS 4
 #endif
-template <bool FIRST, bool STATS, bool HITS>
+// SMS: the scene's nodes + triangle records are copied into shared memory behind the stacks at
+// kernel start and the traversal reads them with LDS (SharedSceneStack, traverse.cuh); chosen per
+// scene by the host when PTC_PATH_BLOCKS CTAs still fit an SM that way.
+template <bool FIRST, bool STATS, bool HITS, bool SMS = false>
 __global__ void __launch_bounds__(kBlock, PTC_PATH_BLOCKS)
 k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, const RayQueue qin,
        const uint4* __restrict__ hits,
@@ -55,9 +60,17 @@ k_path(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
   __shared__ uint8_t s_perm[HITS ? 4 : kPermBytes];
   if (!HITS)
     trav_tables_init(s_perm, s_spread);
-  SharedStack stack{ s_stack + threadIdx.x, stack_cap, s_perm, s_spread };
+  typename std::conditional<SMS, SharedSceneStack, SharedStack>::type stack;
+  stack.base = s_stack + threadIdx.x, stack.cap = stack_cap, stack.perm = s_perm, stack.spread = s_spread;
+  if constexpr (SMS) {
+    uint4* s_nodes = reinterpret_cast<uint4*>(s_stack + (size_t)stack_cap * kBlock);
+    uint4* s_tris = s_nodes + sc.n_nodes * (kSmemNodeBytes / 16u);
+    smem_scene_fill(sc, s_nodes, s_tris);
+    stack.nodes_s = (uint32_t)__cvta_generic_to_shared(s_nodes);
+    stack.tris_s = (uint32_t)__cvta_generic_to_shared(s_tris);
+  }
 #else
-  SharedStack stack{ s_stack + threadIdx.x, stack_cap };
+  SharedStack stack{ {}, s_stack + threadIdx.x, stack_cap };
 #endif
 #endif
   __shared__ uint32_t s_rays[16];
@@ -282,9 +295,9 @@ k_wave(const FrameParams fp, const DScene sc, const cudaTextureObject_t cube, co
   __shared__ uint32_t s_spread[kSpreadWords];
   __shared__ uint8_t s_perm[kPermBytes];
   trav_tables_init(s_perm, s_spread);
-  SharedStack stack{ s_stack + threadIdx.x, stack_cap, s_perm, s_spread };
+  SharedStack stack{ {}, s_stack + threadIdx.x, stack_cap, s_perm, s_spread };
 #else
-  SharedStack stack{ s_stack + threadIdx.x, stack_cap };
+  SharedStack stack{ {}, s_stack + threadIdx.x, stack_cap };
 #endif
   __shared__ uint32_t s_nrays;
   __shared__ float s_cam[8];
@@ -481,9 +494,9 @@ k_extend(const DScene sc, const RayQueue qin, const uint32_t* __restrict__ qin_c
   __shared__ uint8_t s_perm[kPermBytes];
   trav_tables_init(s_perm, s_spread);
   __syncthreads();
-  SharedStack stack{ s_stack + threadIdx.x, stack_cap, s_perm, s_spread };
+  SharedStack stack{ {}, s_stack + threadIdx.x, stack_cap, s_perm, s_spread };
 #else
-  SharedStack stack{ s_stack + threadIdx.x, stack_cap };
+  SharedStack stack{ {}, s_stack + threadIdx.x, stack_cap };
 #endif
 #endif
   const uint32_t lane = threadIdx.x & 31u;
@@ -666,15 +679,36 @@ max_optin_smem()
   return v - 128 - kPermBytes - 4 * kSpreadWords; // static shared memory of the stage kernels: counters, camera basis, tables
 }
 
-template <bool FIRST, bool STATS, bool HITS>
+template <bool FIRST, bool STATS, bool HITS, bool SMS = false>
 static int
 occ(size_t smem)
 {
   int n = 0;
-  cudaFuncSetAttribute(k_path<FIRST, STATS, HITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin_smem());
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_path<FIRST, STATS, HITS>, kBlock, smem) != cudaSuccess)
+  cudaFuncSetAttribute(k_path<FIRST, STATS, HITS, SMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin_smem());
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_path<FIRST, STATS, HITS, SMS>, kBlock, smem) != cudaSuccess)
     n = 0;
   return n;
+}
+
+size_t
+scene_smem_bytes(const DScene& sc)
+{
+  return (size_t)sc.n_nodes * kSmemNodeBytes + (size_t)sc.n_tris * kSmemTriBytes;
+}
+
+int
+path_kernel_blocks_per_sm_scene(bool first, bool stats, int stack_cap, const DScene& sc)
+{
+#if defined(PTC_TABLES) && !defined(PTC_STAGE_LOCAL_STACK) && !defined(PTC_NO_SMEM_SCENE)
+  const size_t smem = stack_smem_bytes(stack_cap) + scene_smem_bytes(sc);
+  if (smem > (size_t)max_optin_smem())
+    return 0;
+  if (first)
+    return stats ? occ<true, true, false, true>(smem) : occ<true, false, false, true>(smem);
+  return stats ? occ<false, true, false, true>(smem) : occ<false, false, false, true>(smem);
+#else
+  return 0;
+#endif
 }
 
 // Resident CTAs per SM for a scene whose traversal stack needs `stack_cap` entries per thread
@@ -730,17 +764,38 @@ extend_kernel_blocks_per_sm(bool stats, int stack_cap)
 #define PTC_LAUNCH_PATH(F, S, H, SMEM)                                                             \
   k_path<F, S, H><<<grid, kBlock, SMEM, s>>>(fp, sc, cube, qin, hits, qin_count, qout, qout_count, fo, ctr, \
                                              work, bounce0, n_iters, stack_cap, done_q, done_ctl, done_mode)
+#define PTC_LAUNCH_PATH_SMS(F, S, SMEM)                                                            \
+  k_path<F, S, false, true><<<grid, kBlock, SMEM, s>>>(fp, sc, cube, qin, hits, qin_count, qout, qout_count, fo, \
+                                                       ctr, work, bounce0, n_iters, stack_cap, done_q, done_ctl,  \
+                                                       done_mode)
 
 void
 launch_path(bool first, bool stats, uint32_t grid, const FrameParams& fp, const DScene& sc,
             cudaTextureObject_t cube, const RayQueue& qin, const uint4* hits, const uint32_t* qin_count,
             const RayQueue& qout, uint32_t* qout_count, const FrameOut& fo, Counters* ctr,
             uint32_t* work, int bounce0, int n_iters, int stack_cap, float4* done_q, uint32_t* done_ctl,
-            int done_mode, cudaStream_t s)
+            int done_mode, cudaStream_t s, bool scene_in_smem)
 {
   if (!grid)
     return;
   const size_t smem = stack_smem_bytes(stack_cap);
+#if defined(PTC_TABLES) && !defined(PTC_STAGE_LOCAL_STACK) && !defined(PTC_NO_SMEM_SCENE)
+  if (scene_in_smem && !hits) {
+    const size_t both = smem + scene_smem_bytes(sc);
+    if (first) {
+      if (stats)
+        PTC_LAUNCH_PATH_SMS(true, true, both);
+      else
+        PTC_LAUNCH_PATH_SMS(true, false, both);
+    } else {
+      if (stats)
+        PTC_LAUNCH_PATH_SMS(false, true, both);
+      else
+        PTC_LAUNCH_PATH_SMS(false, false, both);
+    }
+    return;
+  }
+#endif
   if (first) {
     if (stats)
       PTC_LAUNCH_PATH(true, true, false, smem);

@@ -13,6 +13,11 @@ size_t stack_smem_bytes(int stack_cap);
 // grids; 0 = the stack does not fit).  Also opts the kernel in to the shared memory it needs.
 int path_kernel_blocks_per_sm(bool first, bool stats, bool pretraced, int stack_cap);
 int extend_kernel_blocks_per_sm(bool stats, int stack_cap);
+// the fused path kernels with the scene's nodes + triangle records copied into shared memory
+// behind the stacks (SharedSceneStack, traverse.cuh): bytes of that copy, and resident CTAs per SM
+// (0 = does not fit)
+size_t scene_smem_bytes(const DScene& sc);
+int path_kernel_blocks_per_sm_scene(bool first, bool stats, int stack_cap, const DScene& sc);
 
 // One wavefront step: `n_iters` x [extend -> shade] starting at radiance-loop iteration
 // `bounce0`.  first: rays are generated (8x4 pixel tile per warp) instead of read from
@@ -27,7 +32,8 @@ void launch_path(bool first, bool stats, uint32_t grid, const FrameParams& fp, c
                  cudaTextureObject_t cube, const RayQueue& qin, const uint4* hits,
                  const uint32_t* qin_count, const RayQueue& qout, uint32_t* qout_count,
                  const FrameOut& fo, Counters* ctr, uint32_t* work, int bounce0, int n_iters,
-                 int stack_cap, float4* done_q, uint32_t* done_ctl, int done_mode, cudaStream_t s);
+                 int stack_cap, float4* done_q, uint32_t* done_ctl, int done_mode, cudaStream_t s,
+                 bool scene_in_smem = false);
 
 // One stage of the SHIFTED schedule (k_wave): shade iteration bounce-1 from the queued hit records
 // `hin` (not for the first stage), intersect iteration `bounce`, finish the rays that miss, queue

@@ -34,6 +34,11 @@ struct SceneDev
   int stack_cap = 0;
   int grid_first[2] = { 0, 0 }, grid_next[2] = { 0, 0 }, grid_shade[2] = { 0, 0 }, grid_extend[2] = { 0, 0 };
   int grid_wave_first[2] = { 0, 0 }, grid_wave_next[2] = { 0, 0 }; // shifted schedule (k_wave)
+  // fused path kernels reading the BVH from a per-CTA shared-memory copy (kernels.cuh): stack
+  // entries and grids of that form; smem_scene = it keeps the path kernels' resident CTA count
+  int stack_cap_s = 0;
+  int grid_first_s[2] = { 0, 0 }, grid_next_s[2] = { 0, 0 };
+  bool smem_scene = false;
 };
 
 struct CubeDev
@@ -63,6 +68,11 @@ struct ptc_context
   uint4* hits2 = nullptr;      // shifted stages: hit records of the odd queue
   float4* done = nullptr;      // (radiance, pixel) of paths that finished before the last stage
   int defer = 1;               // epilogue of those pixels runs in the last stage; PTC_DEFER=0: in place
+  // scenes that fit: BVH read from a per-CTA shared-memory copy in the fused path kernels.  Measured on
+  // B200 and NOT the default: +5 % frame time (indoor 1080p), +3 % (4K, 8 iterations) -- the LSU
+  // wavefronts drop (56 -> 46 % of peak) but the L1 that is left (28 KB beside 4 x 50 KB of shared
+  // memory) no longer holds shading records and texels (L1 hit rate 63 -> 25 %).  PTC_SMEM_SCENE=1.
+  int smem_scene = 0;
   // a frame runs as TWO half-band pipelines on two streams, so that the tail of every stage of
   // one half (SMs draining while the last warps finish) is filled by the other half's stage
   int dual = 1;                // extra pipelines (0..3); PTC_DUAL overrides (experiments)
@@ -414,9 +424,10 @@ enqueue_part(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp, 
         CUDA_TRY(ctx, cudaEventRecord(ev[++n_ev], s));
       continue;
     }
+    const bool sms = sc.smem_scene && ctx->smem_scene && !split;
     if (st.first) {
       const uint32_t want = (tiles + kBlock / 32 - 1) / (kBlock / 32);
-      const uint32_t cap = (uint32_t)sc.grid_first[stats];
+      const uint32_t cap = (uint32_t)(sms ? sc.grid_first_s[stats] : sc.grid_first[stats]);
       grid = want < cap ? want : cap;
     } else if (split) {
       launch_extend(stats, (uint32_t)sc.grid_extend[stats], sc.d, L.q[k & 1], L.counts + k, L.hits, work + 1,
@@ -427,7 +438,7 @@ enqueue_part(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp, 
       hits = L.hits;
       grid = (uint32_t)sc.grid_shade[stats];
     } else {
-      grid = (uint32_t)sc.grid_next[stats];
+      grid = (uint32_t)(sms ? sc.grid_next_s[stats] : sc.grid_next[stats]);
     }
     // every pixel finishes exactly once per frame; in a stage that is not the last, finished pixels
     // are parked and the last stage runs their epilogue (kernels.cuh)
@@ -435,8 +446,8 @@ enqueue_part(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp, 
     if (ctx->defer && n_steps > 1)
       done_mode = k + 1 < n_steps ? kDoneDefer : kDoneDrain;
     launch_path(st.first, stats, grid, fp, sc.d, cm.tex, L.q[k & 1], hits, L.counts + k, L.q[(k + 1) & 1],
-                L.counts + k + 1, fo, ctx->ctr, work, st.bounce0, st.n_iters, sc.stack_cap, L.done,
-                L.counts + kCountSlots - 2, done_mode, s);
+                L.counts + k + 1, fo, ctx->ctr, work, st.bounce0, st.n_iters, sms ? sc.stack_cap_s : sc.stack_cap,
+                L.done, L.counts + kCountSlots - 2, done_mode, s, sms);
     ctx->launches++;
     if (ev)
       CUDA_TRY(ctx, cudaEventRecord(ev[++n_ev], s));
@@ -579,6 +590,8 @@ ptc_create(int device, ptc_context** out)
     ctx->wave_small = atoi(e) != 0;
   if (const char* e = getenv("PTC_DEFER"))
     ctx->defer = atoi(e) != 0;
+  if (const char* e = getenv("PTC_SMEM_SCENE"))
+    ctx->smem_scene = atoi(e) != 0;
   if (const char* e = getenv("PTC_DUAL")) {
     ctx->dual = atoi(e);
     ctx->dual = ctx->dual < 0 ? 0 : (ctx->dual > 3 ? 3 : ctx->dual);
@@ -789,6 +802,15 @@ upload_prepared(ptc_context* ctx, const ptc_scene_desc* desc, const PreparedScen
   }
   if (!s.grid_first[0] || !s.grid_next[0] || !s.grid_extend[0] || !s.grid_first[1] || !s.grid_extend[1])
     return fail(ctx, PTC_ERR_INVALID, "traversal stack does not fit in shared memory");
+  // shared-memory copy of nodes + triangle records for the fused path kernels: only when as many
+  // CTAs stay resident as without it
+  s.stack_cap_s = (int)bvh.stats.wide_depth + 1 + kSmemSceneBacklog;
+  for (int st = 0; st < 2; ++st) {
+    s.grid_first_s[st] = ctx->n_sms * path_kernel_blocks_per_sm_scene(true, st != 0, s.stack_cap_s, s.d);
+    s.grid_next_s[st] = ctx->n_sms * path_kernel_blocks_per_sm_scene(false, st != 0, s.stack_cap_s, s.d);
+  }
+  s.smem_scene = s.grid_first_s[0] && s.grid_first_s[0] >= s.grid_first[0] && s.grid_next_s[0] >= s.grid_next[0] &&
+                 s.grid_first_s[1] && s.grid_next_s[1];
 
   s.info.n_faces = n_faces;
   s.info.n_lights = desc->n_lights;
@@ -799,7 +821,7 @@ upload_prepared(ptc_context* ctx, const ptc_scene_desc* desc, const PreparedScen
   s.info.tri_bytes = sizeof(TriRecord);
   s.info.shade_bytes = sizeof(ShadeRecord);
   s.info.texture_bytes = total;
-  s.info.smem_resident = 0;
+  s.info.smem_resident = s.smem_scene && ctx->smem_scene ? 1u : 0u;
   rollback.armed = false;
   ctx->scenes.push_back(std::move(s));
   *scene_id = (int32_t)ctx->scenes.size() - 1;

@@ -252,7 +252,43 @@ constexpr int kPermBytes = 8 * 256, kSpreadWords = 256;
 //    per lane that sits at a different depth (measured on the 10 M-triangle scene: 37 % of all
 //    L1 wavefronts of k_extend).  `cap` = levels of the scene's wide tree + 1 + kTriBacklog.
 //  * LocalStack -- the debug / parity kernels (one thread per ray, no shared-memory budget).
-struct LocalStack
+// 32-byte read-only load (sm_100: LDG.E.256): one L1 tag request where two 16-byte loads make two.
+__device__ __forceinline__ void
+ldg256(const uint4* p, uint4& a, uint4& b)
+{
+  asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+      : "l"(p));
+}
+
+// Where a stack type reads the BVH from (every stack type carries the same five loaders, so that
+// trav_step is written once): global memory through the read-only path ...
+struct GlobalBvhLoads
+{
+  static constexpr int kBacklog = kTriBacklog;
+  __device__ __forceinline__ void ld_node_hdr(const DScene& sc, uint32_t node, uint4& a, uint4& b) const
+  {
+    ldg256(sc.nodes + node * kNodeVec, a, b);
+  }
+  __device__ __forceinline__ uint4 ld_node_vec(const DScene& sc, uint32_t node, uint32_t k) const
+  {
+    return __ldg(sc.nodes + node * kNodeVec + k);
+  }
+  __device__ __forceinline__ void ld_node_vec2(const DScene& sc, uint32_t node, uint32_t k, uint4& a, uint4& b) const
+  {
+    ldg256(sc.nodes + node * kNodeVec + k, a, b);
+  }
+  __device__ __forceinline__ float4 ld_tri(const DScene& sc, uint32_t rec, uint32_t k) const
+  {
+    return __ldg(sc.tris + (size_t)rec * kTriVec + k);
+  }
+  __device__ __forceinline__ void prefetch_node(const DScene& sc, uint32_t node) const
+  {
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(sc.nodes + node * kNodeVec));
+  }
+};
+
+struct LocalStack : GlobalBvhLoads
 {
   uint2 a[kStackSize];
   __device__ __forceinline__ uint32_t permute(uint32_t m, uint32_t oct_inv) const { return xor_permute8(m, oct_inv); }
@@ -262,7 +298,7 @@ struct LocalStack
   __device__ __forceinline__ int top() const { return kStackSize; }
 };
 
-struct SharedStack
+struct SharedStack : GlobalBvhLoads
 {
   uint2* base; // smem + threadIdx.x
   int cap;
@@ -280,6 +316,66 @@ struct SharedStack
   __device__ __forceinline__ int top() const { return cap; }
 };
 
+// ... or, for a scene whose nodes + triangle records fit beside the stacks of PTC_PATH_BLOCKS
+// resident CTAs (every scene the reference ships: 10-30 KB), a per-CTA copy in SHARED memory.
+// Lanes of a warp read different nodes, so a node load is one L1 wavefront per distinct line in
+// global memory (l1tex__data_pipe_lsu_wavefronts was the busiest unit of the path kernels, 57-62 %
+// of peak); here nodes are 144 bytes apart (128 + 16 of padding), so the same word of eight
+// different nodes lies in eight different bank groups, and an LDS is a short-scoreboard wait.
+
+struct SharedSceneStack
+{
+  static constexpr int kBacklog = kSmemSceneBacklog;
+  uint2* base;
+  int cap;
+  const uint8_t* perm;
+  const uint32_t* spread;
+  uint32_t nodes_s, tris_s; // shared-window byte addresses of the copies
+  __device__ __forceinline__ uint32_t permute(uint32_t m, uint32_t oct_inv) const { return perm[(oct_inv << 8) | m]; }
+  __device__ __forceinline__ uint32_t spread7(uint32_t m) const { return spread[m]; }
+  __device__ __forceinline__ uint2 get(int i) const { return base[i * kBlock]; }
+  __device__ __forceinline__ void put(int i, uint2 v) { base[i * kBlock] = v; }
+  __device__ __forceinline__ int top() const { return cap; }
+  static __device__ __forceinline__ uint4 lds128(uint32_t a)
+  {
+    uint4 v;
+    asm("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    return v;
+  }
+  __device__ __forceinline__ void ld_node_hdr(const DScene&, uint32_t node, uint4& a, uint4& b) const
+  {
+    const uint32_t p = nodes_s + node * kSmemNodeBytes;
+    a = lds128(p), b = lds128(p + 16u);
+  }
+  __device__ __forceinline__ uint4 ld_node_vec(const DScene&, uint32_t node, uint32_t k) const
+  {
+    return lds128(nodes_s + node * kSmemNodeBytes + k * 16u);
+  }
+  __device__ __forceinline__ void ld_node_vec2(const DScene&, uint32_t node, uint32_t k, uint4& a, uint4& b) const
+  {
+    const uint32_t p = nodes_s + node * kSmemNodeBytes + k * 16u;
+    a = lds128(p), b = lds128(p + 16u);
+  }
+  __device__ __forceinline__ float4 ld_tri(const DScene&, uint32_t rec, uint32_t k) const
+  {
+    const uint4 v = lds128(tris_s + rec * kSmemTriBytes + k * 16u);
+    return make_float4(__uint_as_float(v.x), __uint_as_float(v.y), __uint_as_float(v.z), __uint_as_float(v.w));
+  }
+  __device__ __forceinline__ void prefetch_node(const DScene&, uint32_t) const {}
+};
+
+// Copies the scene's nodes (padded to kSmemNodeBytes) and triangle records behind the stacks (all
+// threads of the CTA; the caller synchronises afterwards).
+__device__ __forceinline__ void
+smem_scene_fill(const DScene& sc, uint4* nodes_dst, uint4* tris_dst)
+{
+  for (uint32_t i = threadIdx.x; i < sc.n_nodes * (uint32_t)kNodeVec; i += blockDim.x)
+    nodes_dst[(i >> 3) * (kSmemNodeBytes / 16u) + (i & 7u)] = __ldg(sc.nodes + i);
+  const uint4* tsrc = reinterpret_cast<const uint4*>(sc.tris);
+  for (uint32_t i = threadIdx.x; i < sc.n_tris * (uint32_t)kTriVec; i += blockDim.x)
+    tris_dst[i] = __ldg(tsrc + i);
+}
+
 // Fills the two tables (all threads of the CTA; the caller synchronises afterwards).
 __device__ __forceinline__ void
 trav_tables_init(uint8_t* perm, uint32_t* spread)
@@ -288,15 +384,6 @@ trav_tables_init(uint8_t* perm, uint32_t* spread)
     perm[i] = (uint8_t)xor_permute8(i & 0xFFu, i >> 8);
   for (uint32_t i = threadIdx.x; i < (uint32_t)kSpreadWords; i += blockDim.x)
     spread[i] = spread3(i) * 7u;
-}
-
-// 32-byte read-only load (sm_100: LDG.E.256): one L1 tag request where two 16-byte loads make two.
-__device__ __forceinline__ void
-ldg256(const uint4* p, uint4& a, uint4& b)
-{
-  asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-      : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
-      : "l"(p));
 }
 
 // Traversal state of one ray (registers; the stack: see above).
@@ -414,8 +501,8 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
   // requests its line from L1 (CCTL.E.PF1): 1 = the lanes that also hold triangles, 2 = every lane
   // with a node, 3 = the node header itself is loaded here.  PF == 0 selects it after them (the
   // early selection alone costs the fused path kernels 2 %).
-  bool do_node = (T.ng.y & 0xFF000000u) && T.tsp < kTriBacklog;
-  uint32_t vec0 = 0;
+  bool do_node = (T.ng.y & 0xFF000000u) && T.tsp < Stack::kBacklog;
+  uint32_t node = 0;
   uint4 n0 = make_uint4(0, 0, 0, 0), n1 = n0;
   auto select_node = [&]() {
     const uint32_t bit = 31u - __clz(T.ng.y);
@@ -425,14 +512,14 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
       stack.put(T.sp++, T.ng);
     const uint32_t slot = (bit - 24u) ^ T.oct_inv;
     const uint32_t rel = __popc(imask_parent & ~(0xFFFFFFFFu << slot));
-    vec0 = (T.ng.x + rel) * kNodeVec;
+    node = T.ng.x + rel;
   };
   if (PF != 0 && do_node) {
     select_node();
     if (PF == 3)
-      ldg256(sc.nodes + vec0, n0, n1);
+      stack.ld_node_hdr(sc, node, n0, n1);
     else if (PF == 2 || (PF == 1 && T.tmask))
-      asm volatile("prefetch.global.L1 [%0];" ::"l"(sc.nodes + vec0));
+      stack.prefetch_node(sc, node);
   }
 
   // -- at most PTC_TRI_PER_ITER triangle tests --------------------------------------------------
@@ -466,12 +553,12 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
       const bool two = T.tmask != 0u;
       const uint32_t bit1 = two ? __ffs(T.tmask) - 1u : bit0;
       T.tmask &= T.tmask - 1u;
-      const float4* tp0 = sc.tris + (size_t)(T.tg.x + __popc(T.tg.y & ((1u << bit0) - 1u))) * kTriVec;
-      const float4* tp1 = sc.tris + (size_t)(T.tg.x + __popc(T.tg.y & ((1u << bit1) - 1u))) * kTriVec;
-      const float4 a0 = __ldg(tp0), a1 = __ldg(tp0 + 1), a2 = __ldg(tp0 + 2);
+      const uint32_t r0 = T.tg.x + __popc(T.tg.y & ((1u << bit0) - 1u));
+      const uint32_t r1 = T.tg.x + __popc(T.tg.y & ((1u << bit1) - 1u));
+      const float4 a0 = stack.ld_tri(sc, r0, 0), a1 = stack.ld_tri(sc, r0, 1), a2 = stack.ld_tri(sc, r0, 2);
       float4 b0 = a0, b1 = a1, b2 = a2;
       if (two)
-        b0 = __ldg(tp1), b1 = __ldg(tp1 + 1), b2 = __ldg(tp1 + 2);
+        b0 = stack.ld_tri(sc, r1, 0), b1 = stack.ld_tri(sc, r1, 1), b2 = stack.ld_tri(sc, r1, 2);
       if (STATS)
         n_tris += two ? 2u : 1u;
       float t, u, v;
@@ -487,8 +574,7 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
         const uint32_t bit = __ffs(T.tmask) - 1u;
         T.tmask &= T.tmask - 1u;
         const uint32_t rec = T.tg.x + __popc(T.tg.y & ((1u << bit) - 1u));
-        const float4* tp = sc.tris + (size_t)rec * kTriVec;
-        const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+        const float4 t0 = stack.ld_tri(sc, rec, 0), t1 = stack.ld_tri(sc, rec, 1), t2 = stack.ld_tri(sc, rec, 2);
         if (STATS)
           n_tris++;
         float t, u, v;
@@ -505,14 +591,14 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
     if (PF == 0)
       select_node();
     if (PF != 3)
-      ldg256(sc.nodes + vec0, n0, n1);
+      stack.ld_node_hdr(sc, node, n0, n1);
 #if PTC_NODE_LAYOUT == 0
     // near / far plane sets picked by ray octant through the load address, not by selects
     // (measured: deriving the far index as near ^ c instead of the subtraction is slower; so is
     // summing the indices in 32 bits first, +1.3 %, although it is two instructions shorter per set)
-    const uint4 NX = __ldg(sc.nodes + vec0 + T.vnx), FX = __ldg(sc.nodes + vec0 + 7u - T.vnx);
-    const uint4 NY = __ldg(sc.nodes + vec0 + T.vny), FY = __ldg(sc.nodes + vec0 + 9u - T.vny);
-    const uint4 NZ = __ldg(sc.nodes + vec0 + T.vnz), FZ = __ldg(sc.nodes + vec0 + 11u - T.vnz);
+    const uint4 NX = stack.ld_node_vec(sc, node, T.vnx), FX = stack.ld_node_vec(sc, node, 7u - T.vnx);
+    const uint4 NY = stack.ld_node_vec(sc, node, T.vny), FY = stack.ld_node_vec(sc, node, 9u - T.vny);
+    const uint4 NZ = stack.ld_node_vec(sc, node, T.vnz), FZ = stack.ld_node_vec(sc, node, 11u - T.vnz);
 #else
     // One 32-byte load per axis (lower and upper planes of the axis are adjacent, bvh.h): the node
     // is FOUR load instructions instead of seven.  Every lane of a warp reads a different node, so
@@ -521,9 +607,9 @@ trav_step(const DScene& sc, Trav& T, Stack& stack, uint32_t& n_nodes, uint32_t& 
     // saturate first (ncu: l1tex__data_pipe_lsu_wavefronts 62-73 % of peak on the L2-resident
     // 180 k-triangle scene).  The near / far set is then a register select on the ray's octant.
     uint4 X0, X1, Y0, Y1, Z0, Z1;
-    ldg256(sc.nodes + vec0 + 2, X0, X1);
-    ldg256(sc.nodes + vec0 + 4, Y0, Y1);
-    ldg256(sc.nodes + vec0 + 6, Z0, Z1);
+    stack.ld_node_vec2(sc, node, 2, X0, X1);
+    stack.ld_node_vec2(sc, node, 4, Y0, Y1);
+    stack.ld_node_vec2(sc, node, 6, Z0, Z1);
     const bool ngx = T.oct & 1u, ngy = T.oct & 2u, ngz = T.oct & 4u;
 #define PTC_SEL4(c, A, B) make_uint4((c) ? (A).x : (B).x, (c) ? (A).y : (B).y, (c) ? (A).z : (B).z, (c) ? (A).w : (B).w)
     const uint4 NX = PTC_SEL4(ngx, X1, X0), FX = PTC_SEL4(ngx, X0, X1);

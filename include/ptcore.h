@@ -178,7 +178,9 @@ typedef struct ptc_scene_info
   uint32_t tri_bytes;      /* bytes per intersection record                    */
   uint32_t shade_bytes;    /* bytes per shading record                         */
   uint64_t texture_bytes;  /* device bytes of texels                           */
-  uint32_t smem_resident;  /* 1 if nodes+triangles are staged in shared memory */
+  uint32_t smem_resident;  /* 1 if the fused path kernels read nodes + triangles from a shared-memory
+                              copy (scene fits beside the stacks AND the context was created with
+                              PTC_SMEM_SCENE=1; off by default: measured slower on B200) */
 } ptc_scene_info;
 
 typedef struct ptc_context ptc_context;

@@ -134,6 +134,43 @@ main(int argc, char** argv)
     fclose(fo);
     return 0;
   }
+  // ref_loader --cross-u8 IN.jpg OUT.bin : a shipped cube cross (assets/cubemap/*.jpg) as the 8-bit
+  // texels stb_image decodes + the 256 floats stbi_loadf turns them into (uploadCubemap loads with
+  // stbi_loadf, gpu_processor.cpp:96; stb_image.h:1565-1582 maps every 8-bit value through one
+  // pow()).  Checks here that table[u8] reproduces stbi_loadf's output exactly, so the GPU box can
+  // rebuild the float cross from 36 MB instead of 151 MB.  Layout: u32 w, h, nb_chan; 256 floats;
+  // w*h*nb_chan bytes.
+  if (argc == 4 && std::string(argv[1]) == "--cross-u8") {
+    int w = 0, h = 0, nc = 0, w2 = 0, h2 = 0, nc2 = 0;
+    unsigned char* u8 = stbi_load(argv[2], &w, &h, &nc, STBI_default);
+    float* f32 = stbi_loadf(argv[2], &w2, &h2, &nc2, STBI_default);
+    if (!u8 || !f32 || w != w2 || h != h2 || nc != nc2) {
+      std::cerr << "ref_loader: --cross-u8: cannot decode " << argv[2] << std::endl;
+      return 1;
+    }
+    float table[256];
+    for (int v = 0; v < 256; ++v)
+      table[v] = stb_gamma((unsigned char)v);
+    const size_t n = (size_t)w * h * nc;
+    for (size_t i = 0; i < n; ++i)
+      if (memcmp(&table[u8[i]], &f32[i], 4) != 0) {
+        std::cerr << "ref_loader: --cross-u8: stbi_loadf differs from the table at texel " << i << std::endl;
+        return 1;
+      }
+    FILE* fo = fopen(argv[3], "wb");
+    if (!fo) {
+      perror("ref_loader: --cross-u8 output");
+      return 1;
+    }
+    const uint32_t hdr[3] = { (uint32_t)w, (uint32_t)h, (uint32_t)nc };
+    fwrite(hdr, 4, 3, fo);
+    fwrite(table, 4, 256, fo);
+    fwrite(u8, 1, n, fo);
+    fclose(fo);
+    stbi_image_free(u8);
+    stbi_image_free(f32);
+    return 0;
+  }
   if (argc < 4) {
     std::cerr << "usage: ref_loader ASSET_FOLDER SCENE_FILE OUT.ptscene\n";
     return 2;

@@ -48,6 +48,17 @@ def _f32p(a):
     return a.ctypes.data_as(C.c_void_p)
 
 
+def load_cube_cross(name):
+    """One of the reference's shipped cube crosses (assets/cubemap/<name>.jpg) as the float image
+    stbi_loadf hands to uploadCubemap, rebuilt from tests/golden/_large/<name>.cross_u8.npz
+    (tests/golden/make_cubemap_fixture.py); None when that file was not generated."""
+    p = os.path.join(GOLDEN, "_large", name + ".cross_u8.npz")
+    if not os.path.exists(p):
+        return None
+    z = np.load(p)
+    return z["table"][z["texels"]]
+
+
 def cube_of(sc):
     if sc.cubemap is None:
         raise ValueError("fixture carries no cubemap faces")

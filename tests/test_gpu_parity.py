@@ -235,6 +235,51 @@ def test_accumulator_bit_identical_to_reference_kernel(core, g0_factory, name, w
     assert (out_m.cpu().numpy() == out_g.cpu().numpy()).all()
 
 
+@pytest.mark.parametrize("scene,cross", [("color_sample_plain", "field_with_house"), ("island_plain", "water")])
+def test_shipped_cube_cross_bit_identical_to_reference_kernel(core, scene, cross):
+    """The reference's own 4096x3072 cube crosses (assets/cubemap/*.jpg -> six 1024^2 RGBA32F faces,
+    100 MB, gpu_processor.cpp:96-161) through ptc_set_cubemap_from_cross, on the two scene files that
+    name them: accumulator and RGBA8 equal the reference kernel's (given the same faces) bit for bit
+    at 1080p -- the filtered lookup at real size, not the 32^2 gradient of the other cases."""
+    import copy
+    import torch
+    from pt_testlib import load_cube_cross
+    img = load_cube_cross(cross)
+    if img is None:
+        pytest.skip("tests/golden/_large not generated (needs /root/reference at build time)")
+    assert img.shape == (3072, 4096, 3)
+    sc = copy.copy(loaded(core, scene).sc)
+    faces, fell_back = P.core.cubemap_faces_from_cross(img)
+    assert not fell_back and faces.shape == (6, 1024, 1024, 4)
+    sc.cubemap, sc.cubemap_size = faces, 1024
+    sid = loaded(core, scene).sid
+    cid, fb = core.set_cubemap_from_cross(img)
+    assert not fb
+    try:
+        g0 = RefGpu(sc)
+    except FileNotFoundError:
+        pytest.skip("oracle/_ref/libref_gpu.so not built")
+    try:
+        w, h, bounces = 1920, 1080, 4
+        acc_m, out_m, _ = dev_buffers(w, h)
+        acc_g, out_g, _ = dev_buffers(w, h)
+        for k in (1, 2):
+            core.render(sid, cid, sc, w, h, acc_m, out_m, None, bounces=bounces, frame_nb=k)
+            g0.kernel(w, h, k, bounces, acc_g.data_ptr(), out_g.data_ptr())
+        torch.cuda.synchronize()
+        neq = (bits(acc_m.cpu().numpy()) != bits(acc_g.cpu().numpy())).any(axis=-1)
+        assert neq.sum() == 0, f"{int(neq.sum())} of {w * h} pixels differ"
+        assert (out_m.cpu().numpy() == out_g.cpu().numpy()).all()
+        # the environment is actually in the picture: the frame differs from the gradient-cubemap one
+        acc_s, out_s, _ = dev_buffers(w, h)
+        L = loaded(core, scene)
+        core.render(L.sid, L.cid, L.sc, w, h, acc_s, out_s, None, bounces=bounces, frame_nb=1)
+        torch.cuda.synchronize()
+        assert (out_s.cpu().numpy() != out_m.cpu().numpy()).mean() > 0.05
+    finally:
+        g0.close()
+
+
 def test_preview_and_post_process_bit_identical_to_reference_kernel(core, g0_factory):
     import torch
     L = loaded(core, "indoor_tex")
@@ -952,6 +997,46 @@ def test_two_half_pipelines_equal_single_pipeline(core, monkeypatch):
         assert core.launch_count() - n0 == 2 * (single.launch_count() - m0)
     finally:
         single.close()
+
+
+def test_bvh_in_shared_memory_equals_global_memory(core, monkeypatch):
+    """PTC_SMEM_SCENE=1: the fused path kernels read a per-CTA shared-memory copy of the scene's
+    nodes + triangle records (144-byte node stride, 4 deferred triangle groups instead of 8).
+    Measured slower than the L1 path on B200, so it is an option, not the default --
+    and it must not change a bit: every reference scene that fits, odd size, 3..8 iterations, the
+    preview frame."""
+    import torch
+    P = pkg()
+    monkeypatch.setenv("PTC_SMEM_SCENE", "1")
+    sm = P.Core(0)
+    monkeypatch.delenv("PTC_SMEM_SCENE")
+    try:
+        for name, w, h, b in (("indoor_tex", 1920, 1080, 3), ("indoor_tex", 333, 77, 8),
+                              ("color_sample_plain", 640, 360, 5), ("island_plain", 320, 180, 4)):
+            L = loaded(core, name)
+            L1 = Loaded(sm, L.sc)
+            assert sm.scene_info(L1.sid).smem_resident == 1, name
+            acc_d, out_d, _ = dev_buffers(w, h)
+            acc_s, out_s, _ = dev_buffers(w, h)
+            for k in (1, 2):
+                core.render(L.sid, L.cid, L.sc, w, h, acc_d, out_d, None, bounces=b, frame_nb=k)
+                sm.render(L1.sid, L1.cid, L.sc, w, h, acc_s, out_s, None, bounces=b, frame_nb=k)
+            torch.cuda.synchronize()
+            assert (bits(acc_d.cpu().numpy()) == bits(acc_s.cpu().numpy())).all(), (name, w, h)
+            assert (out_d.cpu().numpy() == out_s.cpu().numpy()).all(), (name, w, h)
+        L = loaded(core, "indoor_tex")
+        L1 = Loaded(sm, L.sc)
+        acc_d, out_d, _ = dev_buffers(320, 180)
+        acc_s, out_s, _ = dev_buffers(320, 180)
+        core.render(L.sid, L.cid, L.sc, 320, 180, acc_d, out_d, None, bounces=3, frame_nb=1, moved=True)
+        sm.render(L1.sid, L1.cid, L.sc, 320, 180, acc_s, out_s, None, bounces=3, frame_nb=1, moved=True)
+        torch.cuda.synchronize()
+        assert (out_d.cpu().numpy() == out_s.cpu().numpy()).all()
+        # a scene that does not fit beside the stacks keeps the global-memory form
+        big = loaded(core, "synth300")
+        assert core.scene_info(big.sid).smem_resident == 0
+    finally:
+        sm.close()
 
 
 # -- several GPUs behind one call (ptc_group_*) ---------------------------------------------------
