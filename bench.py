@@ -430,8 +430,48 @@ def run_ours(args):
     # host buffers).  N > 1 (--gather store): every step ends with the ASSEMBLED full image in
     # rank 0's pinned host memory (the consumer the reference's window is, gpu_processor.cpp:365-386).
     e2e_d2h = int(bh) * w * 4
+    e2e_what = "every rank's RGBA8 band -> its pinned host memory every step"
     barrier()
-    if store is not None:
+    if world > 1 and interleaved:
+        # one page-locked host image in POSIX shared memory, mapped by every rank's process; each rank's
+        # strips go straight to their rows over that rank's own PCIe link (ptc_memcpy_strips_to_host) on
+        # a copy stream, two device bands / two host images alternating, so the copy of frame k overlaps
+        # the rendering of frame k + 1.  The full image is assembled on the host every step without
+        # crossing one GPU's link (66 MB per frame at N = 8 would take two frame times over one).
+        box = [f"/ptc_bench_{os.getpid()}"]
+        dist.broadcast_object_list(box, src=0)
+        himg = P.core.HostImage(box[0], h, w, slots=2, create=True) if rank == 0 else None
+        barrier()
+        if rank != 0:
+            himg = P.core.HostImage(box[0], h, w, slots=2, create=False)
+        bands = [out, torch.zeros_like(out)]
+        copy_stream = torch.cuda.Stream(device=dev)
+        ev_r = [torch.cuda.Event() for _ in range(2)]
+        ev_c = [torch.cuda.Event() for _ in range(2)]
+
+        def host_frame(k, i):
+            b = i & 1
+            if bh:
+                stream.wait_event(ev_c[b])      # the copy that last read this device band is done
+                core.render(sid, cid, sc, w, h, accum, bands[b], None, bounces=args.bounces, frame_nb=k, stream=cs,
+                            **rows_kw)
+                ev_r[b].record(stream)
+                copy_stream.wait_event(ev_r[b])
+                himg.put_strips(local, b, bands[b], strips, stream=copy_stream.cuda_stream)
+                ev_c[b].record(copy_stream)
+
+        for k in range(W):
+            host_frame(k + 1, k)
+        copy_stream.synchronize()
+        barrier()
+        t0 = time.perf_counter()
+        for k in range(K):
+            host_frame(W + 1 + k, k)
+        copy_stream.synchronize()
+        torch.cuda.synchronize()
+        e2e_what = ("every rank's strips -> their rows of ONE page-locked host image in shared memory (assembled on the "
+                    "host every step, each rank over its own PCIe link, copy overlapped with the next frame)")
+    elif store is not None:
         h_img = [torch.zeros(h, w, dtype=torch.int32).pin_memory() for _ in range(2)] if rank == 0 else None
         for k in range(W):
             frame(k + 1, h_img[k & 1].numpy() if rank == 0 else None)
@@ -441,6 +481,7 @@ def run_ours(args):
             frame(W + 1 + k, h_img[k & 1].numpy() if rank == 0 else None)
         torch.cuda.synchronize()
         e2e_d2h = w * h * 4 if rank == 0 else 0
+        e2e_what = "assembled full image -> rank 0 pinned host memory every step"
     else:
         h_accum = torch.zeros(max(bh, 1), w, 3).pin_memory()
         h_out = [torch.zeros(max(bh, 1), w, dtype=torch.int32).pin_memory() for _ in range(2)]
@@ -503,12 +544,13 @@ def run_ours(args):
                 "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_ms / K,
                         "h2d_bytes_per_step": (C.sizeof(P.core.PtcRenderArgs) + 64) * world,
                         "d2h_bytes_per_step": e2e_d2h_total,
-                        "what": ("assembled full image -> rank 0 pinned host memory every step" if store is not None
-                                 else "every rank's RGBA8 band -> its pinned host memory every step")},
+                        "what": e2e_what},
                 "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu_base,
                 "reference_kernel_same_gpu": gpu_base}
         print(json.dumps(line))
     barrier()
+    if world > 1 and interleaved:
+        himg.close()
     if store is not None:
         store.close()
     core.close()

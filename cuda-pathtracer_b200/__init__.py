@@ -8,4 +8,4 @@ from . import ptscene  # noqa: F401
 from . import synth  # noqa: F401
 from . import tiles  # noqa: F401
 from . import core  # noqa: F401,E402
-from .core import Core, Group, PtcError, SharedBuffer, host_bvh, load_library  # noqa: F401,E402
+from .core import Core, Group, HostImage, PtcError, SharedBuffer, host_bvh, load_library  # noqa: F401,E402

@@ -69,7 +69,8 @@ class PtcHostBvh(C.Structure):
                 ("max_depth", C.c_uint32), ("_owner", C.c_void_p)]
 
 
-EXPORTS = ["ptc_abi_version", "ptc_render_static", "ptc_create", "ptc_destroy", "ptc_last_error", "ptc_upload_scene",
+EXPORTS = ["ptc_abi_version", "ptc_render_static", "ptc_host_image_open", "ptc_host_image_close",
+           "ptc_memcpy_strips_to_host", "ptc_create", "ptc_destroy", "ptc_last_error", "ptc_upload_scene",
            "ptc_scene_info_get", "ptc_set_cubemap", "ptc_render", "ptc_render_host",
            "ptc_reset_accumulation", "ptc_counters_get", "ptc_counters_reset",
            "ptc_trace_primary", "ptc_intersect_rays", "ptc_debug_rng", "ptc_host_bvh_build",
@@ -122,7 +123,8 @@ def load_library() -> C.CDLL:
                      "ptc_group_set_cubemap", "ptc_group_render", "ptc_group_sync", "ptc_group_read_image",
                      "ptc_group_gather_accum", "ptc_group_reset_accumulation", "ptc_shared_alloc",
                      "ptc_shared_open", "ptc_shared_close", "ptc_shared_free", "ptc_flag_signal",
-                     "ptc_flag_wait", "ptc_memcpy_to_host", "ptc_render_static"]:
+                     "ptc_flag_wait", "ptc_memcpy_to_host", "ptc_render_static", "ptc_host_image_open",
+                     "ptc_host_image_close", "ptc_memcpy_strips_to_host"]:
             getattr(lib, name).restype = C.c_int
         lib.ptc_indexed_face_count.restype = C.c_uint64
         lib.ptc_flatten_faces.restype = C.c_int
@@ -632,6 +634,39 @@ class SharedBuffer:
                                          C.c_int(int(sync)))
         if rc:
             raise PtcError(f"ptc_memcpy_to_host failed: {rc}")
+
+
+class HostImage:
+    """A page-locked host image in POSIX shared memory that every rank's process maps
+    (ptc_host_image_open); ``slots`` full RGBA8 images of ``height`` x ``width``."""
+
+    def __init__(self, name, height, width, slots=1, create=False):
+        self.lib = load_library()
+        self.name, self.h, self.w, self.slots, self.created = name, height, width, slots, create
+        self.nbytes = slots * height * width * 4
+        self.ptr = C.c_void_p()
+        rc = self.lib.ptc_host_image_open(name.encode(), C.c_uint64(self.nbytes), C.c_int(int(create)), C.byref(self.ptr))
+        if rc:
+            raise PtcError(f"ptc_host_image_open({name}) failed: {rc}")
+
+    def array(self) -> np.ndarray:
+        buf = (C.c_uint32 * (self.nbytes // 4)).from_address(self.ptr.value)
+        return np.frombuffer(buf, dtype=np.uint32).reshape(self.slots, self.h, self.w)
+
+    def put_strips(self, device, slot, dev_band, strips, stream=0):
+        """This rank's band (device) -> its rows of image ``slot``; asynchronous on ``stream``."""
+        rows, stride, phase = strips
+        dst = C.c_void_p(self.ptr.value + slot * self.h * self.w * 4)
+        rc = self.lib.ptc_memcpy_strips_to_host(C.c_int(device), dst, _ptr(dev_band), C.c_uint32(self.w), C.c_uint32(self.h),
+                                                C.c_uint32(rows), C.c_uint32(stride), C.c_uint32(phase),
+                                                C.c_void_p(int(stream)) if stream else None)
+        if rc:
+            raise PtcError(f"ptc_memcpy_strips_to_host failed: {rc}")
+
+    def close(self):
+        if self.ptr:
+            self.lib.ptc_host_image_close(self.ptr, C.c_uint64(self.nbytes), self.name.encode() if self.created else None)
+            self.ptr = C.c_void_p()
 
 
 def flag_signal(device, address, value, stream=0):

@@ -21,6 +21,10 @@
 // Also here: the CUDA IPC helpers and the flag kernels that give the same direct-store assembly
 // to a one-process-per-GPU job (bench.py under torchrun).
 #include <cuda_runtime.h>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 #include <atomic>
 #include <condition_variable>
@@ -550,6 +554,81 @@ ptc_memcpy_to_host(int device, void* host, const void* dev, uint64_t bytes, void
   if (cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, s) != cudaSuccess)
     return PTC_ERR_STATE;
   if (sync && cudaStreamSynchronize(s) != cudaSuccess)
+    return PTC_ERR_STATE;
+  return PTC_OK;
+}
+
+// -- one process per GPU, image consumed on the HOST: a POSIX shared-memory image every process maps
+// and page-locks, and every rank's own strips copied into it over that rank's own PCIe link --------
+
+int
+ptc_host_image_open(const char* name, uint64_t bytes, int create, void** ptr)
+{
+  if (!name || !bytes || !ptr)
+    return PTC_ERR_INVALID;
+  *ptr = nullptr;
+  const int fd = shm_open(name, create ? (O_CREAT | O_RDWR) : O_RDWR, 0600);
+  if (fd < 0)
+    return PTC_ERR_STATE;
+  if (create && ftruncate(fd, (off_t)bytes) != 0) {
+    close(fd);
+    shm_unlink(name);
+    return PTC_ERR_ALLOC;
+  }
+  void* p = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_SHARED | MAP_POPULATE, fd, 0);
+  close(fd);
+  if (p == MAP_FAILED) {
+    if (create)
+      shm_unlink(name);
+    return PTC_ERR_ALLOC;
+  }
+  const cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    munmap(p, bytes);
+    if (create)
+      shm_unlink(name);
+    return (int)e;
+  }
+  *ptr = p;
+  return PTC_OK;
+}
+
+int
+ptc_host_image_close(void* ptr, uint64_t bytes, const char* unlink_name)
+{
+  if (!ptr || !bytes)
+    return PTC_ERR_INVALID;
+  cudaHostUnregister(ptr);
+  munmap(ptr, bytes);
+  if (unlink_name)
+    shm_unlink(unlink_name);
+  return PTC_OK;
+}
+
+int
+ptc_memcpy_strips_to_host(int device, void* host_image, const void* dev_band, uint32_t width, uint32_t height,
+                          uint32_t strip_rows, uint32_t strip_stride, uint32_t strip_phase, void* stream)
+{
+  if (!host_image || !dev_band || !width || !height || !strip_rows || !strip_stride || strip_phase >= strip_stride)
+    return PTC_ERR_INVALID;
+  DevGuard dg(device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t strip_bytes = (size_t)strip_rows * width * 4;
+  const uint32_t n_strips = (height + strip_rows - 1) / strip_rows;
+  if (strip_phase >= n_strips)
+    return PTC_OK; // this rank owns no strip of an image this small
+  const uint32_t mine = (n_strips - strip_phase + strip_stride - 1) / strip_stride; // strips phase, phase + stride, ...
+  const uint32_t last = strip_phase + (mine - 1) * strip_stride;
+  const uint32_t last_rows = (last + 1) * strip_rows <= height ? strip_rows : height - last * strip_rows;
+  const uint32_t full = last_rows == strip_rows ? mine : mine - 1;
+  uint8_t* dst = (uint8_t*)host_image + (size_t)strip_phase * strip_bytes;
+  if (full && cudaMemcpy2DAsync(dst, strip_bytes * strip_stride, dev_band, strip_bytes, strip_bytes, full,
+                                cudaMemcpyDeviceToHost, s) != cudaSuccess)
+    return PTC_ERR_STATE;
+  if (full != mine &&
+      cudaMemcpyAsync((uint8_t*)host_image + (size_t)last * strip_bytes, (const uint8_t*)dev_band + (size_t)full * strip_bytes,
+                      (size_t)last_rows * width * 4, cudaMemcpyDeviceToHost, s) != cudaSuccess)
     return PTC_ERR_STATE;
   return PTC_OK;
 }

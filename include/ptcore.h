@@ -495,6 +495,22 @@ int ptc_flag_signal(int device, void* flag, uint32_t value, void* stream);
 int ptc_flag_wait(int device, const void* flags, uint32_t n, uint32_t stride_words, uint32_t value, void* stream);
 int ptc_memcpy_to_host(int device, void* host, const void* dev, uint64_t bytes, void* stream, int sync);
 
+/* -- one process per GPU, image consumed on the HOST ---------------------------------------------
+ * The reference's consumer of a frame is the host side of the GL interop (interop.cpp:67-72).  With
+ * one process per GPU, the assembled image does not have to cross one GPU's PCIe link: every rank
+ * copies ITS strips straight into one host image all processes map.
+ * ptc_host_image_open: POSIX shared memory `name` ("/..." as for shm_open) of `bytes`, created
+ *   (create != 0, one rank) or opened (the others, after the creator), mapped and page-locked for
+ *   this process's CUDA context; ptc_host_image_close unmaps it (unlink_name != NULL also removes it).
+ * ptc_memcpy_strips_to_host: device band of this rank (band-local rows = its strips one after the
+ *   other, what ptc_render writes for strip_rows / strip_stride / strip_phase) -> the rows those
+ *   strips have in the full width x height RGBA8 host image; asynchronous on `stream` (at most two
+ *   DMA transfers: a pitched one for the whole strips, one for a short last strip). */
+int ptc_host_image_open(const char* name, uint64_t bytes, int create, void** ptr);
+int ptc_host_image_close(void* ptr, uint64_t bytes, const char* unlink_name);
+int ptc_memcpy_strips_to_host(int device, void* host_image, const void* dev_band, uint32_t width, uint32_t height,
+                              uint32_t strip_rows, uint32_t strip_stride, uint32_t strip_phase, void* stream);
+
 /* -- parity / debugging entry points (used by tests, not by a renderer) -------- */
 
 /* Primary rays of sample `frame_nb` (RNG + camera + DOF as raytrace.cu:227-240),

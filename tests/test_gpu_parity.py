@@ -999,6 +999,39 @@ def test_two_half_pipelines_equal_single_pipeline(core, monkeypatch):
         single.close()
 
 
+def test_strips_scattered_into_shared_host_image(core):
+    """ptc_host_image_open + ptc_memcpy_strips_to_host (bench.py's end-to-end path at N > 1): the
+    bands of three strip phases, copied by pitched DMA into one page-locked shared-memory image,
+    equal the full frame -- with a short last strip (1000 = 62 x 16 + 8 rows) owned by phase 2, with
+    whole strips only (96 rows), and with fewer strips than phases (20 rows)."""
+    import torch
+    L = loaded(core, "indoor_tex")
+    name = f"/ptc_test_{os.getpid()}"
+    for (w, h) in ((640, 1000), (333, 96), (200, 20)):
+        _, full, _ = dev_buffers(w, h)
+        acc = torch.zeros(h, w, 3, device="cuda")
+        core.render(L.sid, L.cid, L.sc, w, h, acc, full, None, bounces=3, frame_nb=2)
+        img = P.HostImage(name, h, w, slots=2, create=True)
+        try:
+            second = P.HostImage(name, h, w, slots=2, create=False)   # what another rank's process does
+            view = img.array()
+            view[:] = 0xDEADBEEF
+            for p in range(3):
+                strips = (16, 3, p)
+                bh = core.band_rows(w, h, strips=strips)
+                band = torch.zeros(max(bh, 1), w, dtype=torch.int32, device="cuda")
+                bacc = torch.zeros(max(bh, 1), w, 3, device="cuda")
+                if bh:
+                    core.render(L.sid, L.cid, L.sc, w, h, bacc, band, None, bounces=3, frame_nb=2, strips=strips)
+                (second if p == 1 else img).put_strips(0, 1, band, strips)
+            torch.cuda.synchronize()
+            assert (view[1] == full.cpu().numpy().view(np.uint32)).all(), (w, h)
+            assert (view[0] == 0xDEADBEEF).all()
+            second.close()
+        finally:
+            img.close()
+
+
 def test_bvh_in_shared_memory_equals_global_memory(core, monkeypatch):
     """PTC_SMEM_SCENE=1: the fused path kernels read a per-CTA shared-memory copy of the scene's
     nodes + triangle records (144-byte node stride, 4 deferred triangle groups instead of 8).

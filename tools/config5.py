@@ -9,15 +9,18 @@ mode tiles : every rank renders its round-robin 16-row strips of every scene.
 Prints one JSON line: per-scene ms/frame and Mrays/s, aggregate Mrays/s (segments of all scenes /
 max over ranks of the device time), and -- on 1 GPU -- the reference kernel (G0) on the same frames.
 Scenes come from tests/golden (crate_land only when its fixture was generated locally:
-tests/golden/make_fixtures.py); cubemaps larger than 64^2 are not part of the fixtures, a smooth
-synthetic cubemap stands in for them (same for both implementations)."""
+tests/golden/make_fixtures.py).  Cubemaps: the reference's shipped 4096x3072 crosses for the scenes
+that name them (color_sample / crate_land: field_with_house.jpg, island: water.jpg -> six 1024^2
+faces, 100 MB) when tests/golden/_large was generated (tests/golden/make_cubemap_fixture.py); a
+smooth synthetic cubemap otherwise and for the scenes whose JPEG is not shipped (same for both
+implementations; the line says which)."""
 import argparse, copy, json, os, sys
 import numpy as np
 import torch
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, REPO); sys.path.insert(0, os.path.join(REPO, "tests"))
 import bench
-from pt_testlib import load_scene, RefGpu
+from pt_testlib import load_scene, load_cube_cross, RefGpu
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--frames", type=int, default=8)
@@ -26,6 +29,7 @@ ap.add_argument("--height", type=int, default=4320)
 ap.add_argument("--bounces", type=int, default=3)
 ap.add_argument("--mode", default="tiles", choices=["scenes", "tiles"])
 ap.add_argument("--no-reference", action="store_true")
+ap.add_argument("--out", default=None, help="also write the JSON line to this file (stdout carries NCCL's banner too)")
 a = ap.parse_args()
 
 rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("WORLD_SIZE", 1), ("LOCAL_RANK", 0)))
@@ -35,14 +39,23 @@ if world > 1:
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 P = bench.pkg()
 names = ["indoor_tex", "crate_land_plain", "island_plain", "color_sample_plain", "sss_crate_plain"]
-scenes = {}
+scenes, cubes = {}, {}
 for n in names:
     try:
         sc = copy.copy(load_scene(n))
     except Exception:
         continue
-    if sc.cubemap is None or n != "indoor_tex":
+    cross = {"color_sample_plain": "field_with_house", "crate_land_plain": "field_with_house", "island_plain": "water"}.get(n)
+    img = load_cube_cross(cross) if cross else None
+    if img is not None:
+        faces, _ = P.core.cubemap_faces_from_cross(img)
+        sc.cubemap, sc.cubemap_size = faces, faces.shape[1]
+        cubes[n] = f"{cross}.jpg ({faces.shape[1]}^2 faces)"
+    elif sc.cubemap is None or n != "indoor_tex":
         sc.cubemap, sc.cubemap_size = P.synth.gradient_cubemap(32), 32
+        cubes[n] = "synthetic gradient 32^2"
+    else:
+        cubes[n] = "constant colour (garden.jpg is not shipped: the reference's fallback)"
     if n.startswith("sss_crate"):  # legacy camera line -> fov 0 in the reference's parser
         sc.camera = P.synth.camera_array((-2.7, 2.06, 2.52), (0.62, -0.348, -0.7), aperture=0.02, focus_dist=3.555)
     scenes[n] = sc
@@ -81,7 +94,7 @@ if rank == 0:
             "aggregate_Mrays_s": float(t[1]) / (float(mx[0]) * 1e-3) / 1e6, "ms_all_scenes_max_rank": float(mx[0]), "scenes": {}}
     for j, n in enumerate(scenes):
         ms, seg = float(mx[2 + 2 * j]), float(t[3 + 2 * j])
-        line["scenes"][n] = {"faces": scenes[n].n_faces, "ms_per_frame": ms / a.frames,
+        line["scenes"][n] = {"faces": scenes[n].n_faces, "cubemap": cubes.get(n), "ms_per_frame": ms / a.frames,
                              "Mrays_s": seg / (ms * 1e-3) / 1e6 if ms else None}
     if world == 1 and not a.no_reference:
         ref = {}
@@ -94,6 +107,9 @@ if rank == 0:
                 ref[n] = {"error": str(e)}
         line["reference_kernel_same_gpu"] = ref
     print(json.dumps(line))
+    if a.out:
+        with open(a.out, "w") as f:
+            f.write(json.dumps(line, indent=1) + "\n")
 core.close()
 if world > 1:
     dist.destroy_process_group()
