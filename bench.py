@@ -309,10 +309,23 @@ def run_ours(args):
     # the frame complete when all ranks' flags are in -- the image is assembled EVERY frame, inside
     # the per-frame timing.  --gather nccl: round 1's one all_gather_into_tensor after the last frame.
     store = P.tiles.StoreAssembly(P.core, local, h, w, world, rank) if world > 1 and args.gather == "store" else None
+    # --gather copy (default): as above, but the pixels of ranks != 0 travel by DMA -- local band, pitched
+    # peer copy on a copy stream overlapped with the next frame -- and rank 0 holds frame k complete
+    # while it renders frame k + 1 (tiles.CopyAssembly); finish() closes the last frame inside the timing.
+    if world > 1 and args.gather == "copy":
+        if not interleaved:
+            raise SystemExit("--gather copy needs --partition strips")
+        store = P.tiles.CopyAssembly(P.core, local, h, w, world, rank, torch, out)
+    lagged = isinstance(store, P.tiles.CopyAssembly)
     seq = [0]  # frames issued through the assembly so far (flag values must only grow)
 
     def frame(k, host=None):
-        if store is not None:
+        if lagged:
+            seq[0] += 1
+            store.frame(lambda o, full, st: bh and core.render(sid, cid, sc, w, h, accum, o, None, bounces=args.bounces,
+                                                               frame_nb=k, stream=st, out_full=full, **rows_kw),
+                        strips, stream, host)
+        elif store is not None:
             seq[0] += 1
             f = seq[0]
             store.before_frame(f, cs)
@@ -329,6 +342,8 @@ def run_ours(args):
             core.render(sid, cid, sc, w, h, accum, out, None, bounces=args.bounces, frame_nb=k, stream=cs, **rows_kw)
 
     def barrier():
+        if lagged:
+            store.finish(stream)    # no frame left open (and no spinning wait left) across a synchronisation
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -355,6 +370,8 @@ def run_ours(args):
     g0.record(stream)
     if world > 1 and store is None and bh:
         geom.gather(out.view(torch.uint8).view(bh, w, 4))
+    if lagged:
+        store.finish(stream)        # the last frame's assembly, inside the timed region
     g1.record(stream)
     barrier()
     t_wall1 = time.time()
@@ -412,6 +429,8 @@ def run_ours(args):
         s0.record(stream)
         for k in range(n_sus):
             frame(K + 1 + k)
+        if lagged:
+            store.finish(stream)
         s1.record(stream)
         barrier()
         tw1 = time.time()
@@ -534,6 +553,10 @@ def run_ours(args):
                 "traced_per_step": traced / K, "ms_per_step_steady_no_flush": ms_steady,
                 "ms_gather_once": ms_gather,
                 "gather": ("none (1 GPU)" if world == 1 else
+                           "every frame: each rank's strips DMA-copied (pitched peer copy over NVLink, CUDA IPC) into the "
+                           "full image on rank 0, overlapped with the next frame; rank 0's stream waits for all ranks' "
+                           "flags of frame k while frame k + 1 renders, the last frame's wait is inside the timed region "
+                           "(ms_gather_once); no collective" if lagged else
                            "every frame: kernels store RGBA8 into the full image on rank 0 over NVLink (CUDA IPC), "
                            "rank 0's stream waits for all ranks' flags inside the per-frame timing; no collective"
                            if store is not None else "one NCCL all_gather_into_tensor after the last timed frame"),
@@ -712,8 +735,9 @@ def main():
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS),
                     help="a BASELINE.json configuration (sets scene / size / bounces / scaling)")
     ap.add_argument("--scaling", default=None, choices=["weak", "strong"])
-    ap.add_argument("--gather", default="store", choices=["store", "nccl"],
-                    help="N > 1: image assembled every frame by peer stores (default) or one NCCL gather at the end")
+    ap.add_argument("--gather", default="copy", choices=["copy", "store", "nccl"],
+                    help="N > 1: image assembled on rank 0 every frame by overlapped peer DMA copies (default) or by the "
+                         "kernels' own peer stores, or one NCCL gather at the end")
     ap.add_argument("--verify", action="store_true",
                     help="compare the N-GPU accumulator (and image) bit for bit with a 1-GPU render on rank 0")
     ap.add_argument("--sustain-s", type=float, default=5.0, help="length of the sustained block (0 = skip)")

@@ -69,8 +69,9 @@ class PtcHostBvh(C.Structure):
                 ("max_depth", C.c_uint32), ("_owner", C.c_void_p)]
 
 
-EXPORTS = ["ptc_abi_version", "ptc_render_static", "ptc_host_image_open", "ptc_host_image_close",
-           "ptc_memcpy_strips_to_host", "ptc_create", "ptc_destroy", "ptc_last_error", "ptc_upload_scene",
+EXPORTS = ["ptc_abi_version", "ptc_render_static", "ptc_group_upload_scene_from_device",
+           "ptc_group_set_cubemap_from_array", "ptc_host_image_open", "ptc_host_image_close",
+           "ptc_memcpy_strips_to_host", "ptc_memcpy_strips_to_device", "ptc_create", "ptc_destroy", "ptc_last_error", "ptc_upload_scene",
            "ptc_scene_info_get", "ptc_set_cubemap", "ptc_render", "ptc_render_host",
            "ptc_reset_accumulation", "ptc_counters_get", "ptc_counters_reset",
            "ptc_trace_primary", "ptc_intersect_rays", "ptc_debug_rng", "ptc_host_bvh_build",
@@ -124,7 +125,7 @@ def load_library() -> C.CDLL:
                      "ptc_group_gather_accum", "ptc_group_reset_accumulation", "ptc_shared_alloc",
                      "ptc_shared_open", "ptc_shared_close", "ptc_shared_free", "ptc_flag_signal",
                      "ptc_flag_wait", "ptc_memcpy_to_host", "ptc_render_static", "ptc_host_image_open",
-                     "ptc_host_image_close", "ptc_memcpy_strips_to_host"]:
+                     "ptc_host_image_close", "ptc_memcpy_strips_to_host", "ptc_memcpy_strips_to_device"]:
             getattr(lib, name).restype = C.c_int
         lib.ptc_indexed_face_count.restype = C.c_uint64
         lib.ptc_flatten_faces.restype = C.c_int
@@ -667,6 +668,17 @@ class HostImage:
         if self.ptr:
             self.lib.ptc_host_image_close(self.ptr, C.c_uint64(self.nbytes), self.name.encode() if self.created else None)
             self.ptr = C.c_void_p()
+
+
+def strips_to_device(device, image_address, dev_band, width, height, strips, stream=0):
+    """ptc_memcpy_strips_to_device: this rank's band -> its rows of a (possibly peer-mapped) device image."""
+    rows, stride, phase = strips
+    rc = load_library().ptc_memcpy_strips_to_device(C.c_int(device), C.c_void_p(int(image_address)), _ptr(dev_band),
+                                                    C.c_uint32(width), C.c_uint32(height), C.c_uint32(rows),
+                                                    C.c_uint32(stride), C.c_uint32(phase),
+                                                    C.c_void_p(int(stream)) if stream else None)
+    if rc:
+        raise PtcError(f"ptc_memcpy_strips_to_device failed: {rc}")
 
 
 def flag_signal(device, address, value, stream=0):

@@ -347,6 +347,38 @@ ptc_group_set_cubemap(ptc_group* g, const float* faces, uint32_t size, int32_t* 
 }
 
 int
+ptc_group_upload_scene_from_device(ptc_group* g, const ptc_ref_scenes* scenes, uint32_t scene_index, int32_t* scene_id)
+{
+  if (!g || !scenes || !scene_id)
+    return PTC_ERR_INVALID;
+  ptc_context* root = g->members[0].ctx; // the caller's tree lives on devices[0]
+  bool read_back = false; // a failure before the sink ran is the read-back's: its message is in the root context
+  const int rc = ptc::scene_from_device(root, scenes, scene_index, [&](const ptc_scene_desc* d) {
+    read_back = true;
+    return ptc_group_upload_scene(g, d, scene_id);
+  });
+  if (rc && !read_back)
+    g->err = ptc_last_error(root);
+  return rc;
+}
+
+int
+ptc_group_set_cubemap_from_array(ptc_group* g, const void* cuda_array, int32_t* cubemap_id)
+{
+  if (!g || !cuda_array || !cubemap_id)
+    return PTC_ERR_INVALID;
+  ptc_context* root = g->members[0].ctx;
+  bool read_back = false;
+  const int rc = ptc::cubemap_from_array(root, cuda_array, [&](const float* faces, uint32_t size) {
+    read_back = true;
+    return ptc_group_set_cubemap(g, faces, size, cubemap_id);
+  });
+  if (rc && !read_back)
+    g->err = ptc_last_error(root);
+  return rc;
+}
+
+int
 ptc_group_render(ptc_group* g, const ptc_render_args* args)
 {
   if (!g || !args)
@@ -606,9 +638,15 @@ ptc_host_image_close(void* ptr, uint64_t bytes, const char* unlink_name)
   return PTC_OK;
 }
 
+} // extern "C"
+
+namespace {
+
+// A rank's band (band-local rows = its strips one after the other) -> the rows those strips have
+// in a full image, by DMA: a pitched copy for the whole strips, one more for a short last strip.
 int
-ptc_memcpy_strips_to_host(int device, void* host_image, const void* dev_band, uint32_t width, uint32_t height,
-                          uint32_t strip_rows, uint32_t strip_stride, uint32_t strip_phase, void* stream)
+copy_strips(int device, void* host_image, const void* dev_band, uint32_t width, uint32_t height, uint32_t strip_rows,
+            uint32_t strip_stride, uint32_t strip_phase, void* stream, cudaMemcpyKind kind)
 {
   if (!host_image || !dev_band || !width || !height || !strip_rows || !strip_stride || strip_phase >= strip_stride)
     return PTC_ERR_INVALID;
@@ -623,14 +661,34 @@ ptc_memcpy_strips_to_host(int device, void* host_image, const void* dev_band, ui
   const uint32_t last_rows = (last + 1) * strip_rows <= height ? strip_rows : height - last * strip_rows;
   const uint32_t full = last_rows == strip_rows ? mine : mine - 1;
   uint8_t* dst = (uint8_t*)host_image + (size_t)strip_phase * strip_bytes;
-  if (full && cudaMemcpy2DAsync(dst, strip_bytes * strip_stride, dev_band, strip_bytes, strip_bytes, full,
-                                cudaMemcpyDeviceToHost, s) != cudaSuccess)
+  if (full && cudaMemcpy2DAsync(dst, strip_bytes * strip_stride, dev_band, strip_bytes, strip_bytes, full, kind, s) !=
+                cudaSuccess)
     return PTC_ERR_STATE;
   if (full != mine &&
       cudaMemcpyAsync((uint8_t*)host_image + (size_t)last * strip_bytes, (const uint8_t*)dev_band + (size_t)full * strip_bytes,
-                      (size_t)last_rows * width * 4, cudaMemcpyDeviceToHost, s) != cudaSuccess)
+                      (size_t)last_rows * width * 4, kind, s) != cudaSuccess)
     return PTC_ERR_STATE;
   return PTC_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int
+ptc_memcpy_strips_to_host(int device, void* host_image, const void* dev_band, uint32_t width, uint32_t height,
+                          uint32_t strip_rows, uint32_t strip_stride, uint32_t strip_phase, void* stream)
+{
+  return copy_strips(device, host_image, dev_band, width, height, strip_rows, strip_stride, strip_phase, stream,
+                     cudaMemcpyDeviceToHost);
+}
+
+int
+ptc_memcpy_strips_to_device(int device, void* image, const void* dev_band, uint32_t width, uint32_t height,
+                            uint32_t strip_rows, uint32_t strip_stride, uint32_t strip_phase, void* stream)
+{
+  return copy_strips(device, image, dev_band, width, height, strip_rows, strip_stride, strip_phase, stream,
+                     cudaMemcpyDefault);
 }
 
 } // extern "C"

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -1006,6 +1007,28 @@ ptc_upload_scene_from_device(ptc_context* ctx, const ptc_ref_scenes* scenes, uin
 {
   if (!ctx || !scenes || !scene_id)
     return PTC_ERR_INVALID;
+  return ptc::scene_from_device(ctx, scenes, scene_index,
+                                [&](const ptc_scene_desc* d) { return ptc_upload_scene(ctx, d, scene_id); });
+}
+
+int
+ptc_set_cubemap_from_array(ptc_context* ctx, const void* cuda_array, int32_t* cubemap_id)
+{
+  if (!ctx || !cuda_array || !cubemap_id)
+    return PTC_ERR_INVALID;
+  return ptc::cubemap_from_array(ctx, cuda_array, [&](const float* faces, uint32_t size) {
+    return ptc_set_cubemap(ctx, faces, size, cubemap_id);
+  });
+}
+
+} // extern "C"
+
+// The reference's device tree / cubemap array read back to the host (through `ctx`'s device) and
+// handed to `sink` -- ptc_upload_scene for one context, ptc_group_upload_scene for a group.
+int
+ptc::scene_from_device(ptc_context* ctx, const ptc_ref_scenes* scenes, uint32_t scene_index,
+                       const std::function<int(const ptc_scene_desc*)>& sink)
+{
   if (!scenes->scenes)
     return fail(ctx, PTC_ERR_INVALID, "Scenes.scenes is null");
   DeviceGuard g(ctx->device);
@@ -1073,14 +1096,13 @@ ptc_upload_scene_from_device(ptc_context* ctx, const ptc_ref_scenes* scenes, uin
   d.n_lights = (uint32_t)lights.size();
   d.textures = tex.data();
   d.n_textures = (uint32_t)tex.size();
-  return ptc_upload_scene(ctx, &d, scene_id);
+  return sink(&d);
 }
 
 int
-ptc_set_cubemap_from_array(ptc_context* ctx, const void* cuda_array, int32_t* cubemap_id)
+ptc::cubemap_from_array(ptc_context* ctx, const void* cuda_array,
+                        const std::function<int(const float*, uint32_t)>& sink)
 {
-  if (!ctx || !cuda_array || !cubemap_id)
-    return PTC_ERR_INVALID;
   DeviceGuard g(ctx->device);
   cudaArray_t src = (cudaArray_t)const_cast<void*>(cuda_array);
   cudaChannelFormatDesc desc;
@@ -1099,8 +1121,10 @@ ptc_set_cubemap_from_array(ptc_context* ctx, const void* cuda_array, int32_t* cu
   p.extent = make_cudaExtent(ext.width, ext.height, 6);
   p.kind = cudaMemcpyDeviceToHost;
   CUDA_TRY(ctx, cudaMemcpy3D(&p));
-  return ptc_set_cubemap(ctx, faces.data(), (uint32_t)ext.width, cubemap_id);
+  return sink(faces.data(), (uint32_t)ext.width);
 }
+
+extern "C" {
 
 int
 ptc_render(ptc_context* ctx, const ptc_render_args* args)

@@ -193,3 +193,64 @@ class StoreAssembly:
 
     def close(self):
         self.buf.close()
+
+
+class CopyAssembly(StoreAssembly):
+    """Same image, same flags, but the pixels of ranks != 0 travel by DMA instead of by the kernels'
+    stores: a rank renders into a local band, and a copy stream scatters the band's strips into rank
+    0's image (ptc_memcpy_strips_to_device: one pitched peer copy over NVLink), then raises the
+    rank's flag.  Two local bands alternate, so the copy of frame k overlaps the rendering of frame
+    k + 1; rank 0 (whose own strips are stored by its kernels, locally) holds frame k complete while
+    it renders frame k + 1 -- the consumer runs ONE frame behind, ``finish`` closes the last one.
+
+    Why: seven GPUs storing 32-byte pixel runs into one GPU during the short last stage of a frame
+    cost 0.16 ms per 0.62 ms frame on 8 B200 (StoreAssembly: 0.778 ms/frame); see DESIGN.md 6.
+    """
+
+    def __init__(self, core_mod, device, height, width, world, rank, torch, band_like):
+        super().__init__(core_mod, device, height, width, world, rank)
+        self.torch = torch
+        self.frames = 0      # frames issued
+        self.closed = 0      # frames whose completion rank 0 has waited for
+        if rank != 0:
+            self.copy_stream = torch.cuda.Stream(device=band_like.device)
+            self.bands = [torch.zeros_like(band_like), torch.zeros_like(band_like)]
+            self.ev_r = [torch.cuda.Event() for _ in range(2)]
+            self.ev_c = [torch.cuda.Event() for _ in range(2)]
+
+    def frame(self, render, strips, stream, host=None):
+        """One frame.  ``render(out, out_full, stream_handle)`` enqueues this rank's strips;
+        ``stream`` is the torch stream of the render.  Rank 0: ``host`` (numpy) receives the frame
+        that completes during this call (the previous one)."""
+        self.frames += 1
+        f, cs = self.frames, stream.cuda_stream
+        if self.rank == 0:
+            render(self.image(f), True, cs)          # own strips: local stores into the image
+            self.after_frame(f, cs)
+            if f > 1:
+                self._close(f - 1, cs, host)
+            return
+        b = f & 1
+        stream.wait_event(self.ev_c[b])              # the copy that last read this band is done
+        render(self.bands[b], False, cs)
+        self.ev_r[b].record(stream)
+        self.copy_stream.wait_event(self.ev_r[b])
+        ccs = self.copy_stream.cuda_stream
+        if f > 2:                                     # the image of frame f was last used by frame f - 2
+            self.m.flag_wait(self.device, self.flags + self.world * self.LINE, 1, 1, f - 2, ccs)
+        self.m.strips_to_device(self.device, self.image(f), self.bands[b], self.w, self.h, strips, ccs)
+        self.m.flag_signal(self.device, self.flags + self.rank * self.LINE, f, ccs)
+        self.ev_c[b].record(self.copy_stream)
+
+    def _close(self, f, cs, host=None):
+        self.wait_complete(f, cs)
+        if host is not None:
+            self.to_host(f, host, cs)
+        self.consumed(f, cs)
+        self.closed = f
+
+    def finish(self, stream, host=None):
+        """Rank 0: wait for the last issued frame too (inside the caller's timing)."""
+        if self.rank == 0 and self.closed < self.frames:
+            self._close(self.frames, stream.cuda_stream, host)
+

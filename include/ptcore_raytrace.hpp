@@ -34,6 +34,7 @@ namespace ptc_compat {
 
 struct Registry
 {
+  ptc_group* group = nullptr;                                // use_devices(): every call drives this group
   std::map<int, ptc_context*> ctx;                           // device -> context
   std::map<std::pair<int, unsigned>, int32_t> scene;         // (device, scene_id) -> core id
   std::map<std::pair<int, const void*>, int32_t> cubemap;    // (device, cudaArray) -> core id
@@ -41,6 +42,8 @@ struct Registry
   {
     for (auto& kv : ctx)
       ptc_destroy(kv.second);
+    if (group)
+      ptc_group_destroy(group);
   }
 };
 
@@ -58,16 +61,49 @@ report(ptc_context* c, const char* what, int rc)
   return cudaErrorUnknown;
 }
 
-// Forget every derived scene / cubemap (call after the caller re-uploads its Scenes tree).
+// Forget every derived scene / cubemap (call after the caller re-uploads its Scenes tree); also
+// leaves the several-GPU mode.
 inline void
 invalidate()
 {
   Registry& r = registry();
   for (auto& kv : r.ctx)
     ptc_destroy(kv.second);
+  if (r.group)
+    ptc_group_destroy(r.group);
+  r.group = nullptr;
   r.ctx.clear();
   r.scene.clear();
   r.cubemap.clear();
+}
+
+// Opt-in: every later raytrace() call renders on ALL of `devices` (ptc_group_*, ptcore.h): the
+// image is split into round-robin 16-row strips, devices[0] must be the device the caller's Scenes
+// tree, cubemap arrays and output image live on (the current device of the reference's
+// GPUProcessor), every device's kernels store their pixels straight into the caller's image there,
+// and the result is bit-identical to one GPU.  The group owns one accumulator per device:
+// `temporal_framebuffer` is then neither read nor written (read the samples back with
+// ptc_group_gather_accum(ptc_compat::registry().group, ...)).  The frame counter follows
+// raytrace.cu:296-300 as before.
+inline cudaError_t
+use_devices(const int* devices, unsigned n)
+{
+  invalidate();
+  Registry& r = registry();
+  const int rc = ptc_group_create(devices, n, &r.group);
+  if (rc) {
+    std::fprintf(stderr, "ptcore: ptc_group_create failed (%d)\n", rc);
+    r.group = nullptr;
+    return cudaErrorUnknown;
+  }
+  return cudaSuccess;
+}
+
+inline cudaError_t
+report_group(ptc_group* g, const char* what, int rc)
+{
+  std::fprintf(stderr, "ptcore: %s failed (%d): %s\n", what, rc, ptc_group_last_error(g));
+  return cudaErrorUnknown;
 }
 
 } // namespace ptc_compat
@@ -89,6 +125,41 @@ raytrace(uchar4* out_rgba, const Scenes& scenes, unsigned int scene_id, const st
   static_assert(sizeof(Scenes) == sizeof(ptc_ref_scenes), "scene::Scenes layout (scene_data.h:83-87)");
   static_assert(sizeof(Camera) == sizeof(ptc_camera), "scene::Camera layout (scene_data.h:123-133)");
   ptc_compat::Registry& r = ptc_compat::registry();
+  if (r.group) { // several GPUs behind the same call (ptc_compat::use_devices)
+    ptc_group* g = r.group;
+    int rc;
+    auto sk = std::make_pair(-1, scene_id);
+    auto sit = r.scene.find(sk);
+    if (sit == r.scene.end()) {
+      int32_t id;
+      if ((rc = ptc_group_upload_scene_from_device(g, reinterpret_cast<const ptc_ref_scenes*>(&scenes), scene_id, &id)))
+        return ptc_compat::report_group(g, "ptc_group_upload_scene_from_device", rc);
+      sit = r.scene.emplace(sk, id).first;
+    }
+    if (cubemap_id < 0 || (size_t)cubemap_id >= cubemaps.size())
+      return ptc_compat::report_group(g, "cubemap_id out of range", PTC_ERR_INVALID);
+    auto ck = std::make_pair(-1, (const void*)cubemaps[cubemap_id].cubemap);
+    auto cit = r.cubemap.find(ck);
+    if (cit == r.cubemap.end()) {
+      int32_t id;
+      if ((rc = ptc_group_set_cubemap_from_array(g, cubemaps[cubemap_id].cubemap, &id)))
+        return ptc_compat::report_group(g, "ptc_group_set_cubemap_from_array", rc);
+      cit = r.cubemap.emplace(ck, id).first;
+    }
+    ptc_render_args a{};
+    a.scene_id = sit->second;
+    a.cubemap_id = cit->second;
+    a.camera = reinterpret_cast<const ptc_camera*>(cam);
+    a.width = width;
+    a.height = height;
+    a.moved = moved ? 1u : 0u;
+    a.post_id = post_id;
+    a.out_rgba = out_rgba; // the caller's image on devices[0]; accumulators are the group's
+    a.stream = stream;
+    if ((rc = ptc_group_render(g, &a)))
+      return ptc_compat::report_group(g, "ptc_group_render", rc);
+    return cudaSuccess;
+  }
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess)
     return cudaErrorUnknown;

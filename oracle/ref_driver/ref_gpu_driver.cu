@@ -350,6 +350,24 @@ ref_gpu_compat_reset()
   ptc_compat::invalidate();
 }
 
+// The overload's several-GPU opt-in (ptc_compat::use_devices) and the group's accumulator, so the
+// parity test can compare the samples too.
+int
+ref_gpu_compat_use_devices(const int* devices, unsigned n)
+{
+  return (int)ptc_compat::use_devices(devices, n);
+}
+
+int
+ref_gpu_compat_gather_accum(float* host_accum)
+{
+  ptc_group* g = ptc_compat::registry().group;
+  if (!g)
+    return -1;
+  int rc = ptc_group_sync(g);
+  return rc ? rc : ptc_group_gather_accum(g, host_accum);
+}
+
 // Same launch as raytrace.cu:315-322 but for an explicit sample number, so tests
 // can compare frame k without replaying frames 1..k-1.
 int

@@ -207,6 +207,20 @@ class RefGpu:
     def compat_reset(self):
         self.lib.ref_gpu_compat_reset()
 
+    def compat_use_devices(self, devices):
+        """ptc_compat::use_devices: later raytrace_compat calls render on all of `devices`."""
+        arr = (C.c_int * len(devices))(*devices)
+        rc = self.lib.ref_gpu_compat_use_devices(arr, C.c_uint(len(devices)))
+        if rc:
+            raise RuntimeError(f"ptc_compat::use_devices failed: {rc}")
+
+    def compat_gather_accum(self, w, h):
+        out = np.zeros((h, w, 3), np.float32)
+        rc = self.lib.ref_gpu_compat_gather_accum(_f32p(out))
+        if rc:
+            raise RuntimeError(f"ptc_group_gather_accum failed: {rc}")
+        return out
+
     def primary(self, w, h, frame):
         cam = self.sc.camera_struct()
         o = np.zeros((h * w, 3), np.float32)

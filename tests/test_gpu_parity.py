@@ -325,6 +325,37 @@ def test_source_compatible_raytrace_overload(g0_factory):
         g0.compat_reset()
 
 
+def test_raytrace_overload_over_several_gpus(g0_factory):
+    """ptc_compat::use_devices (include/ptcore_raytrace.hpp): the same raytrace(uchar4*, ...) call,
+    fed with the reference's own device tree on devices[0], drives every visible GPU (one GPU: three
+    contexts on it) through ptc_group_*; the image lands in the CALLER's buffer and equals the
+    reference's own raytrace() call by call, and so do the samples the group accumulated."""
+    import torch
+    P = pkg()
+    from pt_testlib import load_scene
+    import copy
+    sc = copy.copy(load_scene("indoor_tex"))
+    sc.cubemap = P.synth.gradient_cubemap(32)
+    sc.cubemap_size = 32
+    g0 = g0_factory("indoor_tex_compat", sc)
+    w, h = 640, 360
+    acc_g, out_g, _ = dev_buffers(w, h)
+    unused, out_m, _ = dev_buffers(w, h)
+    n = torch.cuda.device_count()
+    try:
+        g0.compat_use_devices(list(range(n)) if n > 1 else [0, 0, 0])
+        for i, (moved, post) in enumerate([(True, 0), (False, 0), (False, 0), (False, 1), (True, 2), (False, 2)]):
+            g0.raytrace(w, h, 3, acc_g.data_ptr(), out_g.data_ptr(), moved=moved, post_id=post)
+            g0.raytrace_compat(w, h, unused.data_ptr(), out_m.data_ptr(), moved=moved, post_id=post)
+            torch.cuda.synchronize()
+            ga = g0.compat_gather_accum(w, h)
+            assert (out_m.cpu().numpy() == out_g.cpu().numpy()).all(), f"RGBA8, call {i}"
+            assert (bits(ga) == bits(acc_g.cpu().numpy())).all(), f"accumulator, call {i}"
+        assert not unused.any()   # the group owns the accumulators
+    finally:
+        g0.compat_reset()
+
+
 @pytest.mark.parametrize("name,bounces", [("color_sample_plain", 3), ("island_plain", 4), ("sss_crate_plain", 3),
                                           ("synth24", 6)])
 def test_radiance_vs_oracle_other_scenes(core, oracle, name, bounces):
