@@ -339,7 +339,8 @@ frame_schedule(const ptc_context* ctx, const FrameParams& fp, size_t bvh_bytes, 
 {
   int n = 0;
   // automatic (measured on B200 with the path kernels at 4 CTAs per SM and two half-frame
-  // pipelines, tools/sweep2.py): ONE radiance-loop iteration per stage everywhere, and
+  // pipelines, tools/sweep2.py): ONE radiance-loop iteration per LATER stage everywhere (the first
+  // stage: see below), and
   //  * nodes + triangles <= 64 KB (L1-resident; the reference's scenes are 10-30 KB): every
   //    later stage traverses AND shades in one launch -- 0.638 ms against 0.671 ms for the split
   //    form on the 1080p indoor frame;
@@ -366,8 +367,16 @@ frame_schedule(const ptc_context* ctx, const FrameParams& fp, size_t bvh_bytes, 
     return n;
   }
   int first = (int)ctx->first_iters;
-  if (first == 0)
-    first = 1;
+  if (first == 0) {
+    // measured per frame size and iteration count on B200 (tools/sweep_first.py,
+    // profiles/r2_sweep_first.jsonl; three reference scenes, 640x360 .. 3840x2160, 3 / 4 / 8 iterations):
+    // in the fused form TWO iterations in the first stage beat one at every size (-6 % at 1080p, 3
+    // iterations; -4 % at 4K, 8 iterations: a path that ends at its second segment -- 44 % of them on
+    // the indoor view -- never enters a queue, and a frame is one launch shorter), and a frame small
+    // enough to run as one pipeline (< 256 K pixels, 1.5 waves of warps) likes three (-25 % at 640x360);
+    // in the split form (scenes beyond 64 KB) one stays ahead (+4 % / +8 % with two on 180 k / 10 M triangles)
+    first = split ? 1 : ((uint64_t)fp.band_rows * fp.width < (1u << 18) ? 3 : 2);
+  }
   int b = first < fp.max_bounces ? first : fp.max_bounces;
   steps[n++] = Step{ true, 0, b };
   while (b < fp.max_bounces) {
