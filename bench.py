@@ -313,9 +313,10 @@ def run_ours(args):
     # peer copy on a copy stream overlapped with the next frame -- and rank 0 holds frame k complete
     # while it renders frame k + 1 (tiles.CopyAssembly); finish() closes the last frame inside the timing.
     if world > 1 and args.gather == "copy":
-        if not interleaved:
-            raise SystemExit("--gather copy needs --partition strips")
-        store = P.tiles.CopyAssembly(P.core, local, h, w, world, rank, torch, out)
+        if interleaved:
+            store = P.tiles.CopyAssembly(P.core, local, h, w, world, rank, torch, out)
+        else:   # contiguous bands: the strip scatter does not apply, the kernels store into the image
+            store = P.tiles.StoreAssembly(P.core, local, h, w, world, rank)
     lagged = isinstance(store, P.tiles.CopyAssembly)
     seq = [0]  # frames issued through the assembly so far (flag values must only grow)
 

@@ -64,6 +64,27 @@ def test_no_cpu_fallback_without_device():
         P.Core(0)
 
 
+def test_new_entry_points_refuse_null_arguments():
+    """Argument checks of the round-2 entry points come before any CUDA call, so they hold on a
+    machine without a GPU: nothing is dereferenced, nothing is allocated, PTC_ERR_INVALID (-1)."""
+    lib = P.load_library()
+    null = C.c_void_p(None)
+    out = C.c_void_p()
+    sid = C.c_int32(0)
+    assert lib.ptc_render_static(null, null) == -1
+    assert lib.ptc_host_image_open(None, C.c_uint64(16), 1, C.byref(out)) == -1
+    assert lib.ptc_host_image_open(b"/ptc_never_created", C.c_uint64(0), 1, C.byref(out)) == -1
+    assert lib.ptc_host_image_close(null, C.c_uint64(16), None) == -1
+    for fn in (lib.ptc_memcpy_strips_to_host, lib.ptc_memcpy_strips_to_device):
+        assert fn(0, null, null, 64, 64, 16, 2, 0, null) == -1          # no image, no band
+        assert fn(0, C.c_void_p(16), C.c_void_p(16), 64, 64, 16, 2, 2, null) == -1   # phase >= stride
+        assert fn(0, C.c_void_p(16), C.c_void_p(16), 64, 64, 0, 2, 0, null) == -1    # zero strip height
+    assert lib.ptc_group_upload_scene_from_device(null, null, 0, C.byref(sid)) == -1
+    assert lib.ptc_group_set_cubemap_from_array(null, null, C.byref(sid)) == -1
+    # opening a shared host image nobody created fails without a GPU as well (PTC_ERR_STATE, not a crash)
+    assert lib.ptc_host_image_open(b"/ptc_never_created", C.c_uint64(4096), 0, C.byref(out)) != 0
+
+
 def test_missing_library_fails_loudly(monkeypatch):
     monkeypatch.setattr(P.core, "_lib", None)
     monkeypatch.setattr(P.core, "LIB_PATH", "/nonexistent/libptcore.so")
