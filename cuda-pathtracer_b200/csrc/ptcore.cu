@@ -77,6 +77,7 @@ struct ptc_context
   // a frame runs as TWO half-band pipelines on two streams, so that the tail of every stage of
   // one half (SMs draining while the last warps finish) is filled by the other half's stage
   int dual = 1;                // extra pipelines (0..3); PTC_DUAL overrides (experiments)
+  bool dual_forced = false;    // PTC_DUAL was given: no per-frame choice (frame_pipelines)
   cudaStream_t side_stream[3] = { nullptr, nullptr, nullptr };
   cudaEvent_t ev_fork = nullptr, ev_join[3] = { nullptr, nullptr, nullptr };
   uint64_t launches = 0;
@@ -468,10 +469,20 @@ enqueue_part(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp, 
 
 // Pipelines a frame of this size is rendered as by ptc_render (see enqueue_frame).
 uint32_t
-frame_pipelines(const ptc_context* ctx, const FrameParams& fp)
+frame_pipelines(const ptc_context* ctx, const FrameParams& fp, size_t bvh_bytes)
 {
   const uint32_t n = fp.band_rows * fp.width;
   uint32_t parts = ctx->dual && fp.is_static && n >= (1u << 18) ? (uint32_t)ctx->dual + 1u : 1u;
+  // Overlapping the stage tails of two half frames pays when a frame has tails to overlap.  A frame
+  // of one or two launches (the reference's three iterations in the fused form) is 0.5-2 % faster as
+  // ONE pipeline at every size up to 2720x1530 and equal at 4K (profiles/r2_sweep_dual.jsonl); eight
+  // iterations (-1.5 %) and the split form (10 M triangles: -6 %) keep two.  PTC_DUAL set: as asked.
+  if (parts > 1 && !ctx->dual_forced) {
+    Step steps[kMaxBounces + 2];
+    bool split = false;
+    if (frame_schedule(ctx, fp, bvh_bytes, steps, &split) <= 2 && !split)
+      parts = 1;
+  }
   const uint32_t strips = (fp.band_rows + 15u) / 16u;
   return parts > strips ? strips : parts;
 }
@@ -494,7 +505,7 @@ enqueue_frame(ptc_context* ctx, const ptc_render_args* a, const FrameParams& fp_
   fp.part_row0 = 0;
   fp.part_rows = fp.band_rows;
   const uint32_t strips = (fp.band_rows + 15u) / 16u;
-  const int parts = stats || ev ? 1 : (int)frame_pipelines(ctx, fp);
+  const int parts = stats || ev ? 1 : (int)frame_pipelines(ctx, fp, scene_bvh_bytes(ctx, a->scene_id));
   if (parts <= 1)
     return enqueue_part(ctx, a, fp, fo, s, A, stats, ev);
 
@@ -605,6 +616,7 @@ ptc_create(int device, ptc_context** out)
   if (const char* e = getenv("PTC_DUAL")) {
     ctx->dual = atoi(e);
     ctx->dual = ctx->dual < 0 ? 0 : (ctx->dual > 3 ? 3 : ctx->dual);
+    ctx->dual_forced = true;
   }
   cudaDeviceGetAttribute(&ctx->n_sms, cudaDevAttrMultiProcessorCount, device);
   *out = ctx;
@@ -1516,7 +1528,7 @@ ptc_profile_frame(ptc_context* ctx, const ptc_render_args* args, uint32_t repeat
   float shipped = 0.f;
   cudaEventElapsedTime(&shipped, evf.ev[0], evf.ev[1]);
   out->frame_ms_shipped = shipped / repeats;
-  out->pipelines = frame_pipelines(ctx, fp);
+  out->pipelines = frame_pipelines(ctx, fp, scene_bvh_bytes(ctx, args->scene_id));
   return PTC_OK;
 }
 

@@ -33,8 +33,12 @@ extern "C" {
  * 4: rgb_hex of the cube-cross calls: PTC_CUBEMAP_DEFAULT_COLOR selects the default colour, 0 is
  *    black; ptc_profile_frame no longer touches the caller's buffers and reports more;
  *    ptc_render_args._pad became `flags` (PTC_OUT_FULL_IMAGE); ptc_group_* (several GPUs behind
- *    one call), ptc_shared_* / ptc_flag_* (the same across processes). */
-#define PTC_ABI_VERSION 4
+ *    one call), ptc_shared_* / ptc_flag_* (the same across processes).
+ * 5: additions only -- ptc_render_static, ptc_flatten_faces / ptc_upload_scene_indexed,
+ *    ptc_texpack_*, ptc_group_upload_scene_from_device / ptc_group_set_cubemap_from_array,
+ *    ptc_host_image_* / ptc_memcpy_strips_to_host / ptc_memcpy_strips_to_device;
+ *    ptc_scene_info.smem_resident now reports what it says. */
+#define PTC_ABI_VERSION 5
 
 typedef enum ptc_status
 {

@@ -1010,7 +1010,7 @@ def test_two_half_pipelines_equal_single_pipeline(core, monkeypatch):
     monkeypatch.delenv("PTC_DUAL")
     try:
         L1 = Loaded(single, L.sc)
-        for w, h, b in ((1920, 1080, 3), (1001, 523, 4)):
+        for w, h, b in ((1920, 1080, 4), (1001, 523, 4), (1920, 1080, 8)):
             acc_d, out_d, _ = dev_buffers(w, h)
             acc_s, out_s, _ = dev_buffers(w, h)
             for k in (1, 2):
@@ -1019,13 +1019,16 @@ def test_two_half_pipelines_equal_single_pipeline(core, monkeypatch):
             torch.cuda.synchronize()
             assert (bits(acc_d.cpu().numpy()) == bits(acc_s.cpu().numpy())).all(), (w, h)
             assert (out_d.cpu().numpy() == out_s.cpu().numpy()).all(), (w, h)
-        # the default context really launched twice as many kernels per frame
-        n0, m0 = core.launch_count(), single.launch_count()
+        # the default context really launched twice as many kernels per frame -- for a frame of more
+        # than two launches (four iterations: 3); a frame of one or two launches runs as one pipeline
+        # by default (frame_pipelines, profiles/r2_sweep_dual.jsonl)
         acc_d, out_d, _ = dev_buffers(1920, 1080)
-        core.render(L.sid, L.cid, L.sc, 1920, 1080, acc_d, out_d, None, bounces=3, frame_nb=1)
-        single.render(L1.sid, L1.cid, L.sc, 1920, 1080, acc_d, out_d, None, bounces=3, frame_nb=1)
-        torch.cuda.synchronize()
-        assert core.launch_count() - n0 == 2 * (single.launch_count() - m0)
+        for b, ratio in ((4, 2), (3, 1)):
+            n0, m0 = core.launch_count(), single.launch_count()
+            core.render(L.sid, L.cid, L.sc, 1920, 1080, acc_d, out_d, None, bounces=b, frame_nb=1)
+            single.render(L1.sid, L1.cid, L.sc, 1920, 1080, acc_d, out_d, None, bounces=b, frame_nb=1)
+            torch.cuda.synchronize()
+            assert core.launch_count() - n0 == ratio * (single.launch_count() - m0), b
     finally:
         single.close()
 

@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     for s in syms:
         assert hasattr(lib, s), f"{s} declared in include/ptcore.h but not exported"
     assert sorted(P.core.EXPORTS) == syms
-    assert lib.ptc_abi_version() == 4
+    assert lib.ptc_abi_version() == 5
 
 
 def test_record_layouts_match_reference_contract():
