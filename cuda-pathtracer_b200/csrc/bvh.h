@@ -96,6 +96,7 @@ struct HostBvh
 void build_bvh(const ptc_scene_desc* desc, HostBvh& out);
 
 // Shading records in global face order.
-void build_shade_records(const ptc_scene_desc* desc, std::vector<ShadeRecord>& out);
+// returns the largest material id any face names (0 for an empty scene), found in the same pass
+uint32_t build_shade_records(const ptc_scene_desc* desc, std::vector<ShadeRecord>& out);
 
 } // namespace ptc

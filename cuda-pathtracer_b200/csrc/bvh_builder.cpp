@@ -18,6 +18,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <numeric>
 #include <thread>
 
@@ -122,7 +123,23 @@ struct Builder
     uint32_t id;
   };
   std::vector<Prim> prims;
-  std::vector<BinNode> nodes;
+  // 2 n + 1 node slots, handed out by n_nodes.  NOT value-initialised up front: constructing 20 M
+  // BinNodes (0.8 GB) on one thread was a third of the SAH phase at 10 M triangles; a slot is
+  // initialised by the build() call that takes it, on the thread that then fills it.
+  struct RawNodes
+  {
+    BinNode* p = nullptr;
+    size_t n = 0;
+    ~RawNodes() { std::free(p); }
+    void reserve(size_t count)
+    {
+      p = static_cast<BinNode*>(std::malloc(count * sizeof(BinNode)));
+      n = count;
+    }
+    BinNode& operator[](size_t i) { return p[i]; }
+    const BinNode& operator[](size_t i) const { return p[i]; }
+  } raw;
+  std::vector<BinNode> nodes; // the used prefix, copied out after the build (finish)
   std::atomic<uint32_t> n_nodes{ 0 };
   std::atomic<uint32_t> max_depth{ 0 };
   std::atomic<int> idle_threads;
@@ -140,7 +157,19 @@ struct Builder
           prims[i].c[a] = 0.5f * (b[i].lo[a] + b[i].hi[a]);
       }
     });
-    nodes.resize(b.size() * 2 + 1);
+    raw.reserve(b.size() * 2 + 1);
+  }
+
+  // after build(): the used slots as a vector (what the collapse and the emission read)
+  void finish()
+  {
+    const uint32_t n = n_nodes.load();
+    nodes.resize(n);
+    BinNode* dst = nodes.data();
+    const BinNode* src = raw.p;
+    parallel_for(n, [=](uint32_t lo, uint32_t hi) { std::memcpy(dst + lo, src + lo, (size_t)(hi - lo) * sizeof(BinNode)); });
+    std::free(raw.p);
+    raw.p = nullptr;
   }
 
   // f(lo, hi, chunk) over [first, last) in up to n_threads contiguous chunks
@@ -178,12 +207,21 @@ struct Builder
     while (depth > seen && !max_depth.compare_exchange_weak(seen, depth, std::memory_order_relaxed)) {
     }
     const int idx = (int)n_nodes.fetch_add(1u);
+    new (&raw[idx]) BinNode();
+    BinNode* const nodes = raw.p; // this function fills raw slots; the member vector is built by finish()
     // `top`: no other task is running beside this node, its passes may use all the threads
     const bool wide = top && count >= kParallel && n_threads > 1;
 
+    // (the per-chunk partial results of a node that runs on one thread live on the stack: two
+    // heap allocations per node, 20 M nodes, were a fifth of the single-thread build)
     Box box, cbox;
-    {
-      std::vector<Box> pb(wide ? n_threads : 1u), pc(wide ? n_threads : 1u);
+    if (!wide) {
+      for (uint32_t i = first; i < first + count; ++i) {
+        box.grow(prims[i].box);
+        cbox.grow(prims[i].c);
+      }
+    } else {
+      std::vector<Box> pb(n_threads), pc(n_threads);
       parallel_chunks(first, first + count, wide, [&](uint32_t lo, uint32_t hi, unsigned k) {
         Box bb, cc;
         for (uint32_t i = lo; i < hi; ++i) {
@@ -208,7 +246,10 @@ struct Builder
       ext[a] = cbox.hi[a] - cbox.lo[a];
       scale[a] = ext[a] > 0.f ? kBins / ext[a] : 0.f;
     }
-    std::vector<Bins> part(wide ? n_threads : 1u);
+    Bins one;
+    std::vector<Bins> many(wide ? n_threads : 0u);
+    Bins* const part = wide ? many.data() : &one;
+    const size_t n_part = wide ? many.size() : 1u;
     parallel_chunks(first, first + count, wide, [&](uint32_t lo, uint32_t hi, unsigned k) {
       Bins& B = part[k];
       for (uint32_t i = lo; i < hi; ++i) {
@@ -223,7 +264,7 @@ struct Builder
       }
     });
     Bins& B = part[0];
-    for (size_t k = 1; k < part.size(); ++k)
+    for (size_t k = 1; k < n_part; ++k)
       for (int a = 0; a < 3; ++a)
         for (int bn = 0; bn < kBins; ++bn)
           if (part[k].cnt[a][bn]) {
@@ -329,11 +370,42 @@ struct CollapseDp
     uint8_t use_dist[8]; // c[i] came from distribute(i) (else from c[i-1]), i = 2..7
     bool leaf1;        // c[1] is the leaf alternative
   };
-  std::vector<Entry> e;
+  std::unique_ptr<Entry[]> e; // one per binary node; every entry is written by solve()
+  std::atomic<int> idle_threads;
+  static constexpr uint32_t kSpawn = 1u << 15; // subtrees with more primitives may run as tasks
 
-  explicit CollapseDp(const std::vector<BinNode>& n) : nodes(n), e(n.size())
+  // An entry depends on its two children only, so the subtrees of a node are independent: big
+  // ones run concurrently (the serial index-order loop this replaces was 0.5 s at 10 M triangles).
+  explicit CollapseDp(const std::vector<BinNode>& n, int root)
+    : nodes(n), e(new Entry[n.size()]), idle_threads((int)build_threads() - 1)
   {
-    for (int idx = (int)nodes.size() - 1; idx >= 0; --idx) { // children have larger indices
+    solve(root);
+  }
+
+  void solve(int idx)
+  {
+    {
+      const BinNode& n = nodes[idx];
+      if (!n.leaf()) {
+        bool spawned = false;
+        if (n.count >= kSpawn && nodes[n.left].count >= kSpawn / 2 && nodes[n.right].count >= kSpawn / 2) {
+          int idle = idle_threads.load();
+          while (idle > 0 && !idle_threads.compare_exchange_weak(idle, idle - 1)) {
+          }
+          spawned = idle > 0;
+        }
+        if (spawned) {
+          std::thread t([&] { solve(n.left); });
+          solve(n.right);
+          t.join();
+          idle_threads.fetch_add(1);
+        } else {
+          solve(n.left);
+          solve(n.right);
+        }
+      }
+    }
+    {
       const BinNode& n = nodes[idx];
       Entry& en = e[idx];
       std::memset(&en, 0, sizeof(en));
@@ -343,7 +415,7 @@ struct CollapseDp
         for (int i = 1; i < 8; ++i)
           en.c[i] = c_leaf;
         en.leaf1 = true;
-        continue;
+        return;
       }
       const Entry &l = e[n.left], &r = e[n.right];
       float dist[9];
@@ -523,12 +595,32 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
   // Triangle boxes, padded.  The pad absorbs (a) the rounding of the slab test
   // against the exact box and (b) the fp32 error of Moeller-Trumbore near edges,
   // so a ray the reference's test accepts is never culled by a box.
+  const bool timing = getenv("PTC_BUILD_TIMING") != nullptr;
+  auto now = [] { return std::chrono::steady_clock::now(); };
+  auto secs = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+    return std::chrono::duration<double>(b - a).count();
+  };
+  const auto t_begin = now();
+  // (threaded like everything below: one pass over 1.12 GB of Face records at 10 M triangles; the
+  // scene box is a min/max reduction, so it does not depend on how the range is cut)
   std::vector<Box> boxes(n_faces);
   Box scene;
-  for (uint32_t f = 0; f < n_faces; ++f) {
-    for (int v = 0; v < 3; ++v)
-      boxes[f].grow(desc->faces[f].vertices[v]);
-    scene.grow(boxes[f]);
+  {
+    const unsigned t = build_threads();
+    std::vector<Box> part(t);
+    const uint32_t per = (n_faces + t - 1) / t;
+    parallel_for(n_faces, [&](uint32_t lo, uint32_t hi) {
+      Box sb;
+      for (uint32_t f = lo; f < hi; ++f) {
+        for (int v = 0; v < 3; ++v)
+          boxes[f].grow(desc->faces[f].vertices[v]);
+        sb.grow(boxes[f]);
+      }
+      part[per ? lo / per : 0] = sb; // parallel_for cuts [0, n) into chunks of `per`
+    });
+    for (const Box& pb : part)
+      if (pb.valid())
+        scene.grow(pb);
   }
   float extent = 0.f, maxabs = 0.f;
   if (n_faces)
@@ -537,11 +629,13 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
       maxabs = std::max(maxabs, std::max(std::fabs(scene.lo[a]), std::fabs(scene.hi[a])));
     }
   const float pad = std::ldexp(std::max(extent, maxabs), -15) + FLT_MIN;
-  for (Box& b : boxes)
-    for (int a = 0; a < 3; ++a) {
-      b.lo[a] -= pad;
-      b.hi[a] += pad;
-    }
+  parallel_for(n_faces, [&](uint32_t lo, uint32_t hi) {
+    for (uint32_t f = lo; f < hi; ++f)
+      for (int a = 0; a < 3; ++a) {
+        boxes[f].lo[a] -= pad;
+        boxes[f].hi[a] += pad;
+      }
+  });
 
   auto emit_tri = [&](uint32_t at, uint32_t f) {
     const ptc_face& face = desc->faces[f];
@@ -566,15 +660,14 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
     return;
   }
 
-  const bool timing = getenv("PTC_BUILD_TIMING") != nullptr;
-  auto now = [] { return std::chrono::steady_clock::now(); };
-  auto secs = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
-    return std::chrono::duration<double>(b - a).count();
-  };
   const auto t0 = now();
+  if (timing)
+    fprintf(stderr, "build_bvh: triangle boxes %.2f s\n", secs(t_begin, t0));
   Builder b(boxes);
+  if (timing)
+    fprintf(stderr, "build_bvh: builder set-up %.2f s\n", secs(t0, now()));
   int root = b.build(0, n_faces, 0);
-  b.nodes.resize(b.n_nodes.load());
+  b.finish();
   out.stats.max_depth = b.max_depth.load();
   const auto t1 = now();
 
@@ -587,7 +680,7 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
     out.stats.sah_cost = root_area > 0 ? (float)(cost / root_area) : 0.f;
   }
 
-  const CollapseDp dp(b.nodes);
+  const CollapseDp dp(b.nodes, root);
   const auto t2 = now();
 
   // Emission, level by level (== the order a serial breadth-first queue would give, so node
@@ -609,6 +702,9 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
   };
   std::vector<Item> level{ Item{ root, 0u } }, next;
   std::vector<Plan> plan;
+  out.tris.reserve(n_faces);     // every face is emitted exactly once: no regrowth copies
+  out.face_ids.reserve(n_faces);
+  out.nodes.reserve(n_faces / 4 + 16);
   out.nodes.resize(1);
   uint32_t depth = 0;
   while (!level.empty()) {
@@ -759,21 +855,30 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
             secs(t0, t1), secs(t1, t2), secs(t2, now()));
 }
 
-void
+uint32_t
 build_shade_records(const ptc_scene_desc* desc, std::vector<ShadeRecord>& out)
 {
+  std::atomic<uint32_t> max_material{ 0 };
   uint32_t n_faces = 0;
   for (uint32_t m = 0; m < desc->n_meshes; ++m)
     n_faces += desc->mesh_face_counts[m];
   out.resize(n_faces);
-  for (uint32_t f = 0; f < n_faces; ++f) {
-    const ptc_face& face = desc->faces[f];
-    ShadeRecord& s = out[f];
-    std::memcpy(s.n, face.normals, sizeof(s.n));
-    std::memcpy(s.uv, face.texcoords, sizeof(s.uv));
-    std::memcpy(s.tangent, face.tangent, sizeof(s.tangent));
-    s.material_id = face.material_id;
-  }
+  parallel_for(n_faces, [&](uint32_t lo, uint32_t hi) {
+    uint32_t mx = 0;
+    for (uint32_t f = lo; f < hi; ++f) {
+      const ptc_face& face = desc->faces[f];
+      ShadeRecord& s = out[f];
+      std::memcpy(s.n, face.normals, sizeof(s.n));
+      std::memcpy(s.uv, face.texcoords, sizeof(s.uv));
+      std::memcpy(s.tangent, face.tangent, sizeof(s.tangent));
+      s.material_id = face.material_id;
+      mx = std::max(mx, (uint32_t)face.material_id);
+    }
+    uint32_t seen = max_material.load();
+    while (mx > seen && !max_material.compare_exchange_weak(seen, mx)) {
+    }
+  });
+  return max_material.load();
 }
 
 } // namespace ptc

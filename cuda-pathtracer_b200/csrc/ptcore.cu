@@ -700,11 +700,14 @@ prepare_scene(const ptc_scene_desc* desc, PreparedScene& ps, std::string& err)
   uint32_t n_faces = 0;
   for (uint32_t m = 0; m < desc->n_meshes; ++m)
     n_faces += desc->mesh_face_counts[m];
-  for (uint32_t f = 0; f < n_faces; ++f)
-    if (desc->faces[f].material_id >= desc->n_materials) {
-      err = "face references a material outside the table";
-      return PTC_ERR_INVALID;
-    }
+  // shading records first: the (threaded) pass that splits them off also finds the largest
+  // material id, which replaces a serial scan over 1.12 GB of Face records at 10 M triangles
+  if (n_faces && build_shade_records(desc, ps.shade) >= desc->n_materials) {
+    err = "face references a material outside the table";
+    return PTC_ERR_INVALID;
+  }
+  if (!n_faces)
+    ps.shade.clear();
   for (uint32_t i = 0; i < desc->n_materials; ++i) {
     const ptc_material& m = desc->materials[i];
     if (m.diffuse_spec_map < 0 || (uint32_t)m.diffuse_spec_map >= desc->n_textures ||
@@ -727,7 +730,6 @@ prepare_scene(const ptc_scene_desc* desc, PreparedScene& ps, std::string& err)
     err = "BVH too deep for the traversal stack";
     return PTC_ERR_INVALID;
   }
-  build_shade_records(desc, ps.shade);
   return PTC_OK;
 }
 
