@@ -1,13 +1,13 @@
 // bvh_builder.cpp -- host builder for the 8-wide compressed BVH (bvh.h).
 //
 // Pipeline: padded triangle boxes -> binary BVH by binned SAH (leaves <= 3
-// triangles) -> collapse to 8-wide by repeatedly opening the child with the
-// largest surface area -> octant-ordered slot assignment -> breadth-first
-// emission (internal children contiguous, a node's triangles contiguous) with
-// outward-rounded 8-bit quantisation.
+// triangles) -> optimal collapse to 8-wide nodes (dynamic program) -> octant-ordered
+// slot assignment -> breadth-first emission (internal children contiguous, a node's
+// triangles contiguous) with outward-rounded 8-bit quantisation.
 //
 // New work relative to the reference, which tests every face per ray
-// (cuda_opengl/include/shaders/intersection.cuh:179-196).
+// (cuda_opengl/include/shaders/intersection.cuh:179-196).  The reference-side step this
+// build replaces at load time is Scene::upload_meshes (cuda_opengl/src/scene/scene.cpp:202-283).
 #include "bvh.h"
 
 #include <algorithm>
@@ -15,12 +15,22 @@
 #include <cfloat>
 #include <chrono>
 #include <cmath>
+#include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <memory>
+#include <mutex>
 #include <numeric>
 #include <thread>
+
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#define PTC_BUILD_SSE 1
+#else
+#define PTC_BUILD_SSE 0
+#endif
 
 namespace ptc {
 namespace {
@@ -55,7 +65,7 @@ struct BinNode
 {
   Box box;
   int left = -1, right = -1; // children (internal) ...
-  uint32_t first = 0, count = 0; // ... or a range of the partitioned primitive array (leaf)
+  uint32_t first = 0, count = 0; // ... or a range of Builder::ids (leaf)
   bool leaf() const { return left < 0; }
 };
 
@@ -68,7 +78,6 @@ trav_cost()
   static float c = getenv("PTC_TRAV_COST") ? (float)atof(getenv("PTC_TRAV_COST")) : 1.0f;
   return c;
 }
-
 
 // Worker threads for the host build: hardware threads, capped; PTC_BUILD_THREADS overrides.
 static unsigned
@@ -102,254 +111,543 @@ parallel_for(uint32_t n, F f)
     x.join();
 }
 
-// Binned-SAH binary tree, built top-down.  Parallel in two ways (scene.cpp:202-283 builds
-// nothing, so at 10 M triangles this step IS the load time): the bin/partition passes of a
-// large node are split over the worker threads, and the two children of a node with more than
-// kSpawn primitives are built concurrently.  Node slots come from one atomic counter, so a
-// child always has a larger index than its parent (the collapse DP walks indices downwards);
-// the tree itself does not depend on the thread count or on timing -- every reduction is a
-// min/max or an integer sum.
+// The workers of ONE build: created once, woken per pass (a build of 10 M triangles runs a few
+// hundred data-parallel passes; a thread per pass and chunk was measurable).  run(f) calls f(k)
+// on every thread k (the caller is thread 0) and returns when all are back.  Not re-entrant.
+class Pool
+{
+public:
+  explicit Pool(unsigned n) : n_(std::max(1u, n))
+  {
+    for (unsigned k = 1; k < n_; ++k)
+      th_.emplace_back([this, k] { worker(k); });
+  }
+  ~Pool()
+  {
+    {
+      std::lock_guard<std::mutex> l(m_);
+      stop_ = true;
+      ++gen_;
+    }
+    start_.notify_all();
+    for (std::thread& t : th_)
+      t.join();
+  }
+  unsigned size() const { return n_; }
+
+  template <typename F>
+  void run(F&& f)
+  {
+    if (n_ == 1) {
+      f(0u);
+      return;
+    }
+    const std::function<void(unsigned)> job = [&f](unsigned k) { f(k); };
+    {
+      std::lock_guard<std::mutex> l(m_);
+      job_ = &job;
+      pending_ = n_ - 1;
+      ++gen_;
+    }
+    start_.notify_all();
+    f(0u);
+    std::unique_lock<std::mutex> l(m_);
+    done_.wait(l, [&] { return pending_ == 0; });
+    job_ = nullptr;
+  }
+
+  // f(lo, hi, k) over [first, last) cut into size() contiguous chunks (chunk k on thread k;
+  // short ranges run on the caller as chunk 0)
+  template <typename F>
+  void chunks(uint32_t first, uint32_t last, F&& f)
+  {
+    const uint32_t n = last - first;
+    if (n_ == 1 || n < 4096) {
+      if (n)
+        f(first, last, 0u);
+      return;
+    }
+    const uint32_t per = (n + n_ - 1) / n_;
+    run([&](unsigned k) {
+      const uint32_t lo = first + std::min(n, k * per), hi = first + std::min(n, (k + 1) * per);
+      if (lo < hi)
+        f(lo, hi, k);
+    });
+  }
+
+  // f(i) for i in [0, n), handed out one at a time (uneven items: subtrees)
+  template <typename F>
+  void dynamic(uint32_t n, F&& f)
+  {
+    std::atomic<uint32_t> next{ 0 };
+    run([&](unsigned) {
+      for (uint32_t i; (i = next.fetch_add(1u, std::memory_order_relaxed)) < n;)
+        f(i);
+    });
+  }
+
+private:
+  void worker(unsigned k)
+  {
+    uint64_t seen = 0;
+    for (;;) {
+      const std::function<void(unsigned)>* job;
+      {
+        std::unique_lock<std::mutex> l(m_);
+        start_.wait(l, [&] { return gen_ != seen; });
+        seen = gen_;
+        if (stop_)
+          return;
+        job = job_;
+      }
+      (*job)(k);
+      {
+        std::lock_guard<std::mutex> l(m_);
+        if (--pending_ == 0)
+          done_.notify_one();
+      }
+    }
+  }
+  const unsigned n_;
+  std::vector<std::thread> th_;
+  std::mutex m_;
+  std::condition_variable start_, done_;
+  const std::function<void(unsigned)>* job_ = nullptr;
+  uint64_t gen_ = 0;
+  unsigned pending_ = 0;
+  bool stop_ = false;
+};
+
+// malloc'ed array that is NOT value-initialised: the thread that fills a range is the one that
+// first touches its pages (one thread zero-filling 0.4 - 1 GB arrays was a third of the old build).
+template <typename T>
+struct Raw
+{
+  T* p = nullptr;
+  Raw() = default;
+  Raw(const Raw&) = delete;
+  Raw& operator=(const Raw&) = delete;
+  ~Raw() { std::free(p); }
+  void alloc(size_t count)
+  {
+    std::free(p);
+    p = static_cast<T*>(std::malloc(std::max<size_t>(1, count) * sizeof(T)));
+    if (!p)
+      throw std::bad_alloc();
+  }
+  void release()
+  {
+    std::free(p);
+    p = nullptr;
+  }
+  T& operator[](size_t i) { return p[i]; }
+  const T& operator[](size_t i) const { return p[i]; }
+};
+
+// Binned-SAH binary tree, built top-down (scene.cpp:202-283 builds nothing, so at 10 M triangles
+// this step IS the load time).  Two phases:
+//  1. "wide" nodes (more than `wide_min` primitives) are handled one at a time by ALL threads:
+//     every thread bins its slice of the node's range, and a stable two-buffer scatter partitions
+//     it (the per-thread bin counts of the chosen axis already say how many primitives of each
+//     slice go left, so no counting pass is needed);
+//  2. the subtrees below them are independent tasks, handed to the threads largest first; each is
+//     the plain serial recursion, in place, with node slots from a range reserved for the task
+//     (no shared counter: 20 M fetch_adds on one line serialise 16 threads).
+// A node costs TWO passes over its primitives: the bins of the chosen axis also hold the boxes of
+// the two children (min / max are exact, so this is the box a separate pass would compute), and
+// the children's centroid boxes are gathered while partitioning.
+// The tree does not depend on the thread count or on timing: bins, boxes and counts are
+// min / max / integer sums, a split depends only on WHICH primitives a node holds, and the one
+// place where their order would matter (coincident centroids: a positional median split) orders
+// them by face id first.  Leaves list their faces in ascending id (emission).
 struct Builder
 {
-  static constexpr uint32_t kSpawn = 1u << 16;    // children of bigger nodes run as tasks
-  static constexpr uint32_t kParallel = 1u << 19; // bigger nodes bin their range in parallel
-
-  // Primitive records are PARTITIONED IN PLACE (no index indirection): every pass over a node's
-  // range is a sequential read, which is what makes the passes scale across threads.
   struct Prim
   {
     Box box;
     float c[3]; // centroid
     uint32_t id;
   };
-  std::vector<Prim> prims;
-  // 2 n + 1 node slots, handed out by n_nodes.  NOT value-initialised up front: constructing 20 M
-  // BinNodes (0.8 GB) on one thread was a third of the SAH phase at 10 M triangles; a slot is
-  // initialised by the build() call that takes it, on the thread that then fills it.
-  struct RawNodes
-  {
-    BinNode* p = nullptr;
-    size_t n = 0;
-    ~RawNodes() { std::free(p); }
-    void reserve(size_t count)
-    {
-      p = static_cast<BinNode*>(std::malloc(count * sizeof(BinNode)));
-      n = count;
-    }
-    BinNode& operator[](size_t i) { return p[i]; }
-    const BinNode& operator[](size_t i) const { return p[i]; }
-  } raw;
-  std::vector<BinNode> nodes; // the used prefix, copied out after the build (finish)
-  std::atomic<uint32_t> n_nodes{ 0 };
-  std::atomic<uint32_t> max_depth{ 0 };
-  std::atomic<int> idle_threads;
-  const unsigned n_threads;
+  static_assert(sizeof(Prim) == 40, "Prim is read as two overlapping 16-byte loads");
 
-  explicit Builder(const std::vector<Box>& b) : idle_threads(0), n_threads(build_threads())
-  {
-    idle_threads = (int)n_threads - 1;
-    prims.resize(b.size());
-    parallel_chunks(0, (uint32_t)b.size(), true, [&](uint32_t lo, uint32_t hi, unsigned) {
-      for (uint32_t i = lo; i < hi; ++i) {
-        prims[i].box = b[i];
-        prims[i].id = i;
-        for (int a = 0; a < 3; ++a)
-          prims[i].c[a] = 0.5f * (b[i].lo[a] + b[i].hi[a]);
-      }
-    });
-    raw.reserve(b.size() * 2 + 1);
-  }
-
-  // after build(): the used slots as a vector (what the collapse and the emission read)
-  void finish()
-  {
-    const uint32_t n = n_nodes.load();
-    nodes.resize(n);
-    BinNode* dst = nodes.data();
-    const BinNode* src = raw.p;
-    parallel_for(n, [=](uint32_t lo, uint32_t hi) { std::memcpy(dst + lo, src + lo, (size_t)(hi - lo) * sizeof(BinNode)); });
-    std::free(raw.p);
-    raw.p = nullptr;
-  }
-
-  // f(lo, hi, chunk) over [first, last) in up to n_threads contiguous chunks
-  template <typename F>
-  void parallel_chunks(uint32_t first, uint32_t last, bool parallel, F f)
-  {
-    const uint32_t n = last - first;
-    const unsigned t = parallel && n >= kParallel ? n_threads : 1u;
-    if (t <= 1) {
-      f(first, last, 0u);
-      return;
-    }
-    std::vector<std::thread> th;
-    const uint32_t per = (n + t - 1) / t;
-    for (unsigned k = 1; k < t; ++k) {
-      const uint32_t lo = first + std::min(n, k * per), hi = first + std::min(n, (k + 1) * per);
-      if (lo < hi)
-        th.emplace_back([=, &f] { f(lo, hi, k); });
-    }
-    f(first, first + std::min(n, per), 0u);
-    for (std::thread& x : th)
-      x.join();
-  }
-
+  // bins of one node (or of one thread's slice of it), all three axes filled in one pass
   struct Bins
   {
+#if PTC_BUILD_SSE
+    __m128 lo[3][kBins], hi[3][kBins]; // lanes 0..2 = x, y, z; lane 3 is scratch
+#else
     Box box[3][kBins];
+#endif
     uint32_t cnt[3][kBins];
-    Bins() { std::memset(cnt, 0, sizeof(cnt)); }
+    Bins()
+    {
+      std::memset(cnt, 0, sizeof(cnt));
+#if PTC_BUILD_SSE
+      const __m128 big = _mm_set1_ps(FLT_MAX), small = _mm_set1_ps(-FLT_MAX);
+      for (int a = 0; a < 3; ++a)
+        for (int b = 0; b < kBins; ++b)
+          lo[a][b] = big, hi[a][b] = small;
+#endif
+    }
+    // operand order: min_ps(x, acc) / max_ps(x, acc) return acc unless x is strictly smaller /
+    // larger -- exactly std::min(acc, x) / std::max(acc, x), signed zeros included
+    void add(int a, int b, const Prim& p)
+    {
+#if PTC_BUILD_SSE
+      lo[a][b] = _mm_min_ps(_mm_loadu_ps(p.box.lo), lo[a][b]);
+      hi[a][b] = _mm_max_ps(_mm_loadu_ps(p.box.hi), hi[a][b]); // reads hi[0..2] and c[0]
+#else
+      box[a][b].grow(p.box);
+#endif
+      cnt[a][b]++;
+    }
+    void merge(const Bins& o)
+    {
+      for (int a = 0; a < 3; ++a)
+        for (int b = 0; b < kBins; ++b) {
+#if PTC_BUILD_SSE
+          lo[a][b] = _mm_min_ps(o.lo[a][b], lo[a][b]);
+          hi[a][b] = _mm_max_ps(o.hi[a][b], hi[a][b]);
+#else
+          box[a][b].grow(o.box[a][b]);
+#endif
+          cnt[a][b] += o.cnt[a][b];
+        }
+    }
+    Box get(int a, int b) const
+    {
+      Box r;
+#if PTC_BUILD_SSE
+      alignas(16) float l[4], h[4];
+      _mm_store_ps(l, lo[a][b]);
+      _mm_store_ps(h, hi[a][b]);
+      for (int k = 0; k < 3; ++k)
+        r.lo[k] = l[k], r.hi[k] = h[k];
+#else
+      r = box[a][b];
+#endif
+      return r;
+    }
   };
 
-  int build(uint32_t first, uint32_t count, uint32_t depth, bool top = true)
+  struct Split
   {
-    uint32_t seen = max_depth.load(std::memory_order_relaxed);
-    while (depth > seen && !max_depth.compare_exchange_weak(seen, depth, std::memory_order_relaxed)) {
-    }
-    const int idx = (int)n_nodes.fetch_add(1u);
-    new (&raw[idx]) BinNode();
-    BinNode* const nodes = raw.p; // this function fills raw slots; the member vector is built by finish()
-    // `top`: no other task is running beside this node, its passes may use all the threads
-    const bool wide = top && count >= kParallel && n_threads > 1;
+    int axis = -1, bin = -1; // primitives whose bin on `axis` is <= `bin` go left
+    float cost = FLT_MAX;
+    float scale[3], lo[3];
+    bool on[3];
+    int bin_of(const Prim& p, int a) const { return std::min(kBins - 1, (int)((p.c[a] - lo[a]) * scale[a])); }
+  };
 
-    // (the per-chunk partial results of a node that runs on one thread live on the stack: two
-    // heap allocations per node, 20 M nodes, were a fifth of the single-thread build)
+  // a subtree that one thread builds (phase 2), or a wide node waiting for phase 1
+  struct Job
+  {
+    uint32_t first, count, depth;
+    int src;      // which of the two primitive buffers holds [first, first + count)
     Box box, cbox;
-    if (!wide) {
-      for (uint32_t i = first; i < first + count; ++i) {
-        box.grow(prims[i].box);
-        cbox.grow(prims[i].c);
-      }
-    } else {
-      std::vector<Box> pb(n_threads), pc(n_threads);
-      parallel_chunks(first, first + count, wide, [&](uint32_t lo, uint32_t hi, unsigned k) {
-        Box bb, cc;
-        for (uint32_t i = lo; i < hi; ++i) {
-          bb.grow(prims[i].box);
-          cc.grow(prims[i].c);
-        }
-        pb[k] = bb, pc[k] = cc;
-      });
-      for (size_t k = 0; k < pb.size(); ++k)
-        if (pb[k].valid())
-          box.grow(pb[k]), cbox.grow(pc[k]);
-    }
-    nodes[idx].box = box;
-    nodes[idx].first = first;
-    nodes[idx].count = count;
-    if (count <= 1)
-      return idx;
+    int parent;   // node that gets this subtree as its left (side 0) or right child; -1 = root
+    int side;
+    uint32_t node_base; // first of the 2 * count - 1 node slots reserved for the task
+  };
 
-    // binned SAH over the three axes (one pass fills the bins of all three)
-    float ext[3], scale[3];
+  Pool& pool;
+  const uint32_t n;
+  Raw<Prim> buf[2];
+  Raw<BinNode> nodes;      // slots: wide nodes first, then one range per task (gaps stay untouched)
+  size_t n_slots = 0;
+  Raw<uint32_t> ids;       // position -> face id, what the leaves' [first, first + count) index
+  std::vector<Job> tasks;  // the subtrees of phase 2; tasks[i]'s root is node tasks[i].node_base
+  uint32_t n_wide = 0;     // nodes [0, n_wide) are the wide nodes, parents before children
+  int root = 0;
+  uint32_t max_depth = 0;
+
+  Builder(Pool& p, uint32_t n_prims) : pool(p), n(n_prims)
+  {
+    buf[0].alloc(n);
+    ids.alloc(n);
+  }
+
+  static void prepare_split(Split& s, const Box& cbox)
+  {
     for (int a = 0; a < 3; ++a) {
-      ext[a] = cbox.hi[a] - cbox.lo[a];
-      scale[a] = ext[a] > 0.f ? kBins / ext[a] : 0.f;
+      const float ext = cbox.hi[a] - cbox.lo[a];
+      s.on[a] = ext > 0.f;
+      s.scale[a] = s.on[a] ? kBins / ext : 0.f;
+      s.lo[a] = cbox.lo[a];
     }
-    Bins one;
-    std::vector<Bins> many(wide ? n_threads : 0u);
-    Bins* const part = wide ? many.data() : &one;
-    const size_t n_part = wide ? many.size() : 1u;
-    parallel_chunks(first, first + count, wide, [&](uint32_t lo, uint32_t hi, unsigned k) {
-      Bins& B = part[k];
-      for (uint32_t i = lo; i < hi; ++i) {
-        const Prim& p = prims[i];
-        for (int a = 0; a < 3; ++a) {
-          if (!(ext[a] > 0.f))
-            continue;
-          const int bn = std::min(kBins - 1, (int)((p.c[a] - cbox.lo[a]) * scale[a]));
-          B.box[a][bn].grow(p.box);
-          B.cnt[a][bn]++;
-        }
-      }
-    });
-    Bins& B = part[0];
-    for (size_t k = 1; k < n_part; ++k)
+  }
+
+  static void fill_bins(Bins& B, const Split& s, const Prim* p, uint32_t lo, uint32_t hi)
+  {
+    for (uint32_t i = lo; i < hi; ++i)
       for (int a = 0; a < 3; ++a)
-        for (int bn = 0; bn < kBins; ++bn)
-          if (part[k].cnt[a][bn]) {
-            B.box[a][bn].grow(part[k].box[a][bn]);
-            B.cnt[a][bn] += part[k].cnt[a][bn];
-          }
+        if (s.on[a])
+          B.add(a, s.bin_of(p[i], a), p[i]);
+  }
 
-    float best_cost = FLT_MAX;
-    int best_axis = -1, best_split = -1;
+  // the cheapest of the 3 x 15 candidate planes (first one wins ties: axis, then bin, ascending).
+  // Only planes right behind an OCCUPIED bin are evaluated: between two occupied bins the cost does
+  // not change and the first plane of such a run is the one a sweep over all 15 would keep (strict
+  // <), so the choice is the same -- and most nodes are small, with two to four occupied bins.
+  static void choose(Split& s, const Bins& B)
+  {
     for (int a = 0; a < 3; ++a) {
-      if (!(ext[a] > 0.f))
+      if (!s.on[a])
         continue;
+      int occ[kBins], m = 0;
+      for (int b = 0; b < kBins; ++b)
+        if (B.cnt[a][b])
+          occ[m++] = b;
       float right_area[kBins];
       uint32_t right_cnt[kBins];
       Box acc;
       uint32_t cnt = 0;
-      for (int b = kBins - 1; b > 0; --b) {
-        if (B.cnt[a][b])
-          acc.grow(B.box[a][b]);
-        cnt += B.cnt[a][b];
-        right_area[b] = acc.valid() ? acc.half_area() : 0.f;
-        right_cnt[b] = cnt;
+      for (int i = m - 1; i > 0; --i) {
+        acc.grow(B.get(a, occ[i]));
+        cnt += B.cnt[a][occ[i]];
+        right_area[i] = acc.half_area();
+        right_cnt[i] = cnt;
       }
       acc = Box();
       cnt = 0;
-      for (int b = 0; b < kBins - 1; ++b) {
-        if (B.cnt[a][b])
-          acc.grow(B.box[a][b]);
-        cnt += B.cnt[a][b];
-        if (!cnt || !right_cnt[b + 1])
-          continue;
-        float cost = acc.half_area() * cnt + right_area[b + 1] * right_cnt[b + 1];
-        if (cost < best_cost) {
-          best_cost = cost;
-          best_axis = a;
-          best_split = b;
+      for (int i = 0; i + 1 < m; ++i) {
+        acc.grow(B.get(a, occ[i]));
+        cnt += B.cnt[a][occ[i]];
+        const float cost = acc.half_area() * cnt + right_area[i + 1] * right_cnt[i + 1];
+        if (cost < s.cost) {
+          s.cost = cost;
+          s.axis = a;
+          s.bin = occ[i];
         }
       }
     }
+  }
 
-    uint32_t mid;
-    if (best_axis < 0) {
-      // all centroids coincide: leaf if small enough, else split in the middle
+  static void child_boxes(const Split& s, const Bins& B, Box& left, Box& right)
+  {
+    for (int b = 0; b < kBins; ++b)
+      if (B.cnt[s.axis][b])
+        (b <= s.bin ? left : right).grow(B.get(s.axis, b));
+  }
+
+  static bool keep_leaf(const Box& box, uint32_t count, const Split& s)
+  {
+    return count <= kMaxLeaf && box.half_area() * count <= s.cost + box.half_area() * trav_cost();
+  }
+
+  // Coincident centroids (no plane separates anything): ordered by face id, cut in the middle.
+  static uint32_t median_by_id(Prim* p, uint32_t first, uint32_t count, Box lr[2], Box clr[2])
+  {
+    std::sort(p + first, p + first + count, [](const Prim& x, const Prim& y) { return x.id < y.id; });
+    const uint32_t mid = first + count / 2;
+    for (uint32_t i = first; i < first + count; ++i) {
+      lr[i >= mid].grow(p[i].box);
+      clr[i >= mid].grow(p[i].c);
+    }
+    return mid;
+  }
+
+  // ---- phase 2: one subtree on one thread, in place in buffer p ----------------------------
+  struct Local
+  {
+    uint32_t next_node; // next free slot of the task's range
+    uint32_t max_depth = 0;
+  };
+
+  // bins + partition of one node; false = it stays a leaf.  Not inlined: its 1.7 KB of bins must
+  // not sit in every frame of the recursion below.
+  __attribute__((noinline)) static bool split_serial(Prim* p, uint32_t first, uint32_t count, const Box& box,
+                                                     const Box& cbox, uint32_t& mid, Box lr[2], Box clr[2])
+  {
+    Split s;
+    prepare_split(s, cbox);
+    if (!(s.on[0] || s.on[1] || s.on[2])) {
       if (count <= kMaxLeaf)
-        return idx;
-      mid = first + count / 2;
-    } else {
-      float leaf_cost = box.half_area() * count;
-      if (count <= kMaxLeaf && leaf_cost <= best_cost + box.half_area() * trav_cost())
-        return idx; // cheaper (or as cheap) to keep as a leaf
-      const float sc = scale[best_axis];
-      const float lo = cbox.lo[best_axis];
-      auto it = std::partition(prims.begin() + first, prims.begin() + first + count, [&](const Prim& p) {
-        int b = std::min(kBins - 1, (int)((p.c[best_axis] - lo) * sc));
-        return b <= best_split;
-      });
-      mid = (uint32_t)(it - prims.begin());
-      if (mid == first || mid == first + count)
-        mid = first + count / 2;
+        return false;
+      mid = median_by_id(p, first, count, lr, clr);
+      return true;
     }
-
-    int l, r;
-    const uint32_t nl = mid - first, nr = first + count - mid;
-    // both children big: build the left one on another thread if one is free.  While a node
-    // is still "top" only one of its children can stay so (the larger), the other runs beside it.
-    bool spawned = false;
-    if (std::min(nl, nr) >= kSpawn && n_threads > 1) {
-      int idle = idle_threads.load();
-      while (idle > 0 && !idle_threads.compare_exchange_weak(idle, idle - 1)) {
+    Bins B;
+    fill_bins(B, s, p, first, first + count);
+    choose(s, B);
+    if (keep_leaf(box, count, s))
+      return false; // cheaper (or as cheap) to keep as a leaf
+    child_boxes(s, B, lr[0], lr[1]);
+    // in-place partition (the exchange order of std::partition); every primitive is classified
+    // exactly once, and its centroid joins the box of the side it lands on
+    const int a = s.axis;
+    uint32_t i = first, j = first + count;
+    for (;;) {
+      while (i < j && s.bin_of(p[i], a) <= s.bin) {
+        clr[0].grow(p[i].c);
+        ++i;
       }
-      spawned = idle > 0;
+      if (i == j)
+        break;
+      clr[1].grow(p[i].c);
+      --j;
+      while (i < j && !(s.bin_of(p[j], a) <= s.bin)) {
+        clr[1].grow(p[j].c);
+        --j;
+      }
+      if (i == j)
+        break;
+      clr[0].grow(p[j].c);
+      std::swap(p[i], p[j]);
+      ++i;
     }
-    if (spawned) {
-      std::thread t([&] { l = build(first, nl, depth + 1, false); });
-      r = build(mid, nr, depth + 1, false);
-      t.join();
-      idle_threads.fetch_add(1);
-    } else {
-      const bool keep_top = top && std::min(nl, nr) < kSpawn;
-      l = build(first, nl, depth + 1, keep_top && nl >= nr);
-      r = build(mid, nr, depth + 1, keep_top && nr > nl);
+    mid = i;
+    if (mid == first || mid == first + count) { // cannot happen (both sides of the plane hold a bin)
+      lr[0] = lr[1] = clr[0] = clr[1] = Box();
+      mid = median_by_id(p, first, count, lr, clr);
     }
+    return true;
+  }
+
+  int build_serial(Prim* p, uint32_t first, uint32_t count, uint32_t depth, const Box& box, const Box& cbox,
+                   Local& L)
+  {
+    L.max_depth = std::max(L.max_depth, depth);
+    const int idx = (int)L.next_node++;
+    BinNode* nd = new (&nodes[idx]) BinNode();
+    nd->box = box;
+    nd->first = first;
+    nd->count = count;
+    if (count <= 1)
+      return idx;
+    Box lr[2], clr[2];
+    uint32_t mid;
+    if (!split_serial(p, first, count, box, cbox, mid, lr, clr))
+      return idx;
+    const int l = build_serial(p, first, mid - first, depth + 1, lr[0], clr[0], L);
+    const int r = build_serial(p, mid, first + count - mid, depth + 1, lr[1], clr[1], L);
     nodes[idx].left = l;
     nodes[idx].right = r;
     return idx;
+  }
+
+  // ---- phase 1 + driver -------------------------------------------------------------------
+  // `box`, `cbox`: bounds of all primitives / of their centroids (buf[0] is filled by the caller)
+  void build(const Box& box, const Box& cbox)
+  {
+    const unsigned T = pool.size();
+    // wide nodes: enough of them that the tasks below are many (8 per thread) and small
+    const uint32_t wide_min = T > 1 ? std::max<uint32_t>(8192u, n / (8u * T)) : 0xFFFFFFFFu;
+    std::vector<BinNode> top; // the wide nodes, in the order they are taken up
+    std::vector<Job> open;    // wide nodes still to split (LIFO)
+    Job first_job{ 0u, n, 0u, 0, box, cbox, -1, 0, 0u };
+    (n > wide_min ? open : tasks).push_back(first_job);
+    if (!open.empty())
+      buf[1].alloc(n);
+    std::vector<Bins> part(T);
+    std::vector<Box> cl(T), cr(T);
+    std::vector<uint32_t> n_left(T);
+    while (!open.empty()) {
+      const Job j = open.back();
+      open.pop_back();
+      const int idx = (int)top.size();
+      top.emplace_back();
+      top[idx].box = j.box;
+      top[idx].first = j.first;
+      top[idx].count = j.count;
+      if (j.parent >= 0)
+        (j.side ? top[j.parent].right : top[j.parent].left) = idx;
+      max_depth = std::max(max_depth, j.depth);
+
+      Split s;
+      prepare_split(s, j.cbox);
+      Prim* const src = buf[j.src].p;
+      Box lr[2], clr[2];
+      uint32_t mid;
+      int child_src = j.src;
+      if (!(s.on[0] || s.on[1] || s.on[2])) {
+        mid = median_by_id(src, j.first, j.count, lr, clr); // (a wide node is never a leaf)
+      } else {
+        for (unsigned k = 0; k < T; ++k)
+          part[k] = Bins();
+        pool.chunks(j.first, j.first + j.count, [&](uint32_t lo, uint32_t hi, unsigned k) { fill_bins(part[k], s, src, lo, hi); });
+        Bins B = part[0];
+        for (unsigned k = 1; k < T; ++k)
+          B.merge(part[k]);
+        choose(s, B);
+        child_boxes(s, B, lr[0], lr[1]);
+        // stable scatter into the other buffer: slice k writes its left primitives behind those of
+        // the slices before it, its right primitives likewise behind `mid`
+        uint32_t total_left = 0;
+        for (unsigned k = 0; k < T; ++k) {
+          n_left[k] = 0;
+          for (int b = 0; b <= s.bin; ++b)
+            n_left[k] += part[k].cnt[s.axis][b];
+          total_left += n_left[k];
+          cl[k] = cr[k] = Box();
+        }
+        mid = j.first + total_left;
+        Prim* const dst = buf[1 - j.src].p;
+        const int a = s.axis;
+        pool.chunks(j.first, j.first + j.count, [&](uint32_t lo, uint32_t hi, unsigned k) {
+          uint32_t wl = j.first, wr = mid + (lo - j.first);
+          for (unsigned q = 0; q < k; ++q)
+            wl += n_left[q];
+          wr -= wl - j.first; // right primitives before this slice = primitives before it - left ones
+          Box bl, br;
+          for (uint32_t i = lo; i < hi; ++i) {
+            if (s.bin_of(src[i], a) <= s.bin) {
+              bl.grow(src[i].c);
+              dst[wl++] = src[i];
+            } else {
+              br.grow(src[i].c);
+              dst[wr++] = src[i];
+            }
+          }
+          cl[k] = bl, cr[k] = br;
+        });
+        for (unsigned k = 0; k < T; ++k) {
+          clr[0].grow(cl[k]);
+          clr[1].grow(cr[k]);
+        }
+        child_src = 1 - j.src;
+      }
+      const Job kids[2] = { Job{ j.first, mid - j.first, j.depth + 1, child_src, lr[0], clr[0], idx, 0, 0u },
+                            Job{ mid, j.first + j.count - mid, j.depth + 1, child_src, lr[1], clr[1], idx, 1, 0u } };
+      for (int c = 1; c >= 0; --c) // (left child taken up first)
+        (kids[c].count > wide_min ? open : tasks).push_back(kids[c]);
+    }
+
+    // node slots: the wide nodes, then 2 * count - 1 per task
+    n_wide = (uint32_t)top.size();
+    size_t at = n_wide;
+    for (Job& t : tasks) {
+      t.node_base = (uint32_t)at;
+      at += 2 * (size_t)t.count - 1;
+    }
+    n_slots = at;
+    nodes.alloc(n_slots);
+    for (uint32_t i = 0; i < n_wide; ++i)
+      new (&nodes[i]) BinNode(top[i]);
+    for (const Job& t : tasks)
+      if (t.parent >= 0)
+        (t.side ? nodes[t.parent].right : nodes[t.parent].left) = (int)t.node_base;
+    root = 0; // the first wide node, or the root of the only task
+
+    // phase 2, largest subtree first
+    std::vector<uint32_t> order(tasks.size());
+    std::iota(order.begin(), order.end(), 0u);
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return tasks[x].count > tasks[y].count; });
+    std::vector<uint32_t> depth_of(tasks.size(), 0u);
+    pool.dynamic((uint32_t)tasks.size(), [&](uint32_t q) {
+      const Job& t = tasks[order[q]];
+      Local L;
+      L.next_node = t.node_base;
+      Prim* const p = buf[t.src].p;
+      build_serial(p, t.first, t.count, t.depth, t.box, t.cbox, L);
+      for (uint32_t i = t.first; i < t.first + t.count; ++i)
+        ids[i] = p[i].id;
+      depth_of[order[q]] = L.max_depth;
+    });
+    for (uint32_t d : depth_of)
+      max_depth = std::max(max_depth, d);
+    buf[0].release();
+    buf[1].release();
   }
 };
 
@@ -362,7 +660,7 @@ struct CollapseDp
 {
   static constexpr float kNodeCost = 1.0f;
   const float kPrimCost = getenv("PTC_PRIM_COST") ? (float)atof(getenv("PTC_PRIM_COST")) : 0.22f;
-  const std::vector<BinNode>& nodes;
+  const BinNode* const nodes;
   struct Entry
   {
     float c[8];        // c[i], i = 1..7
@@ -370,74 +668,73 @@ struct CollapseDp
     uint8_t use_dist[8]; // c[i] came from distribute(i) (else from c[i-1]), i = 2..7
     bool leaf1;        // c[1] is the leaf alternative
   };
-  std::unique_ptr<Entry[]> e; // one per binary node; every entry is written by solve()
-  std::atomic<int> idle_threads;
-  static constexpr uint32_t kSpawn = 1u << 15; // subtrees with more primitives may run as tasks
+  Raw<Entry> e; // one per node slot; the entries of used slots are written by solve()
+  double sah_sum = 0; // sum over the binary tree of (leaf ? count : 1) * half_area (diagnostic)
 
-  // An entry depends on its two children only, so the subtrees of a node are independent: big
-  // ones run concurrently (the serial index-order loop this replaces was 0.5 s at 10 M triangles).
-  explicit CollapseDp(const std::vector<BinNode>& n, int root)
-    : nodes(n), e(new Entry[n.size()]), idle_threads((int)build_threads() - 1)
+  // An entry depends on its two children only: the builder's task subtrees are solved
+  // concurrently (bottom-up inside each), then the few wide nodes above them, children first.
+  CollapseDp(const Builder& b, Pool& pool) : nodes(b.nodes.p)
   {
-    solve(root);
+    e.alloc(b.n_slots);
+    std::vector<uint32_t> order(b.tasks.size());
+    std::iota(order.begin(), order.end(), 0u);
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return b.tasks[x].count > b.tasks[y].count; });
+    std::vector<double> part(b.tasks.size(), 0.0);
+    pool.dynamic((uint32_t)b.tasks.size(), [&](uint32_t q) {
+      double s = 0;
+      solve((int)b.tasks[order[q]].node_base, s);
+      part[order[q]] = s;
+    });
+    for (double s : part) // task order, not completion order: the same sum every time
+      sah_sum += s;
+    for (uint32_t i = b.n_wide; i-- > 0;) // a wide node's children have larger indices
+      solve_node((int)i, sah_sum);
   }
 
-  void solve(int idx)
+  void solve(int idx, double& sah)
   {
-    {
-      const BinNode& n = nodes[idx];
-      if (!n.leaf()) {
-        bool spawned = false;
-        if (n.count >= kSpawn && nodes[n.left].count >= kSpawn / 2 && nodes[n.right].count >= kSpawn / 2) {
-          int idle = idle_threads.load();
-          while (idle > 0 && !idle_threads.compare_exchange_weak(idle, idle - 1)) {
-          }
-          spawned = idle > 0;
-        }
-        if (spawned) {
-          std::thread t([&] { solve(n.left); });
-          solve(n.right);
-          t.join();
-          idle_threads.fetch_add(1);
-        } else {
-          solve(n.left);
-          solve(n.right);
+    const BinNode& n = nodes[idx];
+    if (!n.leaf()) {
+      solve(n.left, sah);
+      solve(n.right, sah);
+    }
+    solve_node(idx, sah);
+  }
+
+  void solve_node(int idx, double& sah)
+  {
+    const BinNode& n = nodes[idx];
+    Entry& en = e[idx];
+    std::memset(&en, 0, sizeof(en));
+    const float area = n.box.half_area();
+    sah += (n.leaf() ? (double)n.count : 1.0) * area;
+    const float c_leaf = n.count <= kMaxLeaf ? area * (float)n.count * kPrimCost : FLT_MAX;
+    if (n.leaf()) {
+      for (int i = 1; i < 8; ++i)
+        en.c[i] = c_leaf;
+      en.leaf1 = true;
+      return;
+    }
+    const Entry &l = e[n.left], &r = e[n.right];
+    float dist[9];
+    for (int j = 2; j <= 8; ++j) {
+      dist[j] = FLT_MAX;
+      for (int k = 1; k < j; ++k) {
+        if (k > 7 || j - k > 7)
+          continue;
+        float c = l.c[k] + r.c[j - k];
+        if (c < dist[j]) {
+          dist[j] = c;
+          en.split[j] = (uint8_t)k;
         }
       }
     }
-    {
-      const BinNode& n = nodes[idx];
-      Entry& en = e[idx];
-      std::memset(&en, 0, sizeof(en));
-      const float area = n.box.half_area();
-      const float c_leaf = n.count <= kMaxLeaf ? area * (float)n.count * kPrimCost : FLT_MAX;
-      if (n.leaf()) {
-        for (int i = 1; i < 8; ++i)
-          en.c[i] = c_leaf;
-        en.leaf1 = true;
-        return;
-      }
-      const Entry &l = e[n.left], &r = e[n.right];
-      float dist[9];
-      for (int j = 2; j <= 8; ++j) {
-        dist[j] = FLT_MAX;
-        for (int k = 1; k < j; ++k) {
-          if (k > 7 || j - k > 7)
-            continue;
-          float c = l.c[k] + r.c[j - k];
-          if (c < dist[j]) {
-            dist[j] = c;
-            en.split[j] = (uint8_t)k;
-          }
-        }
-      }
-      const float c_internal = dist[8] + area * kNodeCost;
-      en.leaf1 = c_leaf <= c_internal;
-      en.c[1] = en.leaf1 ? c_leaf : c_internal;
-      for (int i = 2; i < 8; ++i) {
-        en.use_dist[i] = dist[i] < en.c[i - 1];
-        en.c[i] = en.use_dist[i] ? dist[i] : en.c[i - 1];
-      }
+    const float c_internal = dist[8] + area * kNodeCost;
+    en.leaf1 = c_leaf <= c_internal;
+    en.c[1] = en.leaf1 ? c_leaf : c_internal;
+    for (int i = 2; i < 8; ++i) {
+      en.use_dist[i] = dist[i] < en.c[i - 1];
+      en.c[i] = en.use_dist[i] ? dist[i] : en.c[i - 1];
     }
   }
 
@@ -560,9 +857,9 @@ reorder_treelets(HostBvh& out)
   std::vector<uint32_t> new_of(n);
   for (uint32_t i = 0; i < n; ++i)
     new_of[order[i]] = i;
-  std::vector<Node8> nodes(n);
-  std::vector<TriRecord> tris(out.tris.size());
-  std::vector<uint32_t> ids(out.face_ids.size());
+  decltype(out.nodes) nodes(n);
+  decltype(out.tris) tris(out.tris.size());
+  decltype(out.face_ids) ids(out.face_ids.size());
   uint32_t tri_top = 0;
   for (uint32_t i = 0; i < n; ++i) {
     Node8 nd = out.nodes[order[i]];
@@ -592,50 +889,76 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
   for (uint32_t m = 0; m < desc->n_meshes; ++m)
     n_faces += desc->mesh_face_counts[m];
 
-  // Triangle boxes, padded.  The pad absorbs (a) the rounding of the slab test
-  // against the exact box and (b) the fp32 error of Moeller-Trumbore near edges,
-  // so a ray the reference's test accepts is never culled by a box.
+  if (n_faces == 0) {
+    Node8 n;
+    std::memset(&n, 0, sizeof(n));
+    n.e[0] = n.e[1] = n.e[2] = 1;
+    out.nodes.push_back(n);
+    out.stats.wide_depth = 1;
+    return;
+  }
+
   const bool timing = getenv("PTC_BUILD_TIMING") != nullptr;
   auto now = [] { return std::chrono::steady_clock::now(); };
   auto secs = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
     return std::chrono::duration<double>(b - a).count();
   };
   const auto t_begin = now();
-  // (threaded like everything below: one pass over 1.12 GB of Face records at 10 M triangles; the
-  // scene box is a min/max reduction, so it does not depend on how the range is cut)
-  std::vector<Box> boxes(n_faces);
-  Box scene;
-  {
-    const unsigned t = build_threads();
-    std::vector<Box> part(t);
-    const uint32_t per = (n_faces + t - 1) / t;
-    parallel_for(n_faces, [&](uint32_t lo, uint32_t hi) {
-      Box sb;
-      for (uint32_t f = lo; f < hi; ++f) {
-        for (int v = 0; v < 3; ++v)
-          boxes[f].grow(desc->faces[f].vertices[v]);
-        sb.grow(boxes[f]);
-      }
-      part[per ? lo / per : 0] = sb; // parallel_for cuts [0, n) into chunks of `per`
-    });
-    for (const Box& pb : part)
-      if (pb.valid())
-        scene.grow(pb);
-  }
-  float extent = 0.f, maxabs = 0.f;
-  if (n_faces)
-    for (int a = 0; a < 3; ++a) {
-      extent = std::max(extent, scene.hi[a] - scene.lo[a]);
-      maxabs = std::max(maxabs, std::max(std::fabs(scene.lo[a]), std::fabs(scene.hi[a])));
+  // (a scene of a few thousand triangles builds in well under a millisecond on one thread; waking
+  // workers would only add to it)
+  Pool pool(n_faces >= 16384 ? build_threads() : 1u);
+  const unsigned T = pool.size();
+  Builder b(pool, n_faces);
+
+  // Triangle boxes, padded.  The pad absorbs (a) the rounding of the slab test
+  // against the exact box and (b) the fp32 error of Moeller-Trumbore near edges,
+  // so a ray the reference's test accepts is never culled by a box.
+  // (two threaded passes, the first over 1.12 GB of Face records at 10 M triangles; every
+  // reduction is a min / max, so nothing depends on how the range is cut)
+  Builder::Prim* const prims = b.buf[0].p;
+  std::vector<Box> part(T), cpart(T);
+  pool.chunks(0, n_faces, [&](uint32_t lo, uint32_t hi, unsigned k) {
+    Box sb;
+    for (uint32_t f = lo; f < hi; ++f) {
+      Box fb;
+      for (int v = 0; v < 3; ++v)
+        fb.grow(desc->faces[f].vertices[v]);
+      prims[f].box = fb;
+      sb.grow(fb);
     }
-  const float pad = std::ldexp(std::max(extent, maxabs), -15) + FLT_MIN;
-  parallel_for(n_faces, [&](uint32_t lo, uint32_t hi) {
-    for (uint32_t f = lo; f < hi; ++f)
-      for (int a = 0; a < 3; ++a) {
-        boxes[f].lo[a] -= pad;
-        boxes[f].hi[a] += pad;
-      }
+    part[k] = sb;
   });
+  Box scene;
+  for (const Box& pb : part)
+    if (pb.valid())
+      scene.grow(pb);
+  float extent = 0.f, maxabs = 0.f;
+  for (int a = 0; a < 3; ++a) {
+    extent = std::max(extent, scene.hi[a] - scene.lo[a]);
+    maxabs = std::max(maxabs, std::max(std::fabs(scene.lo[a]), std::fabs(scene.hi[a])));
+  }
+  const float pad = std::ldexp(std::max(extent, maxabs), -15) + FLT_MIN;
+  for (unsigned k = 0; k < T; ++k)
+    part[k] = cpart[k] = Box();
+  pool.chunks(0, n_faces, [&](uint32_t lo, uint32_t hi, unsigned k) {
+    Box sb, cb;
+    for (uint32_t f = lo; f < hi; ++f) {
+      Builder::Prim& p = prims[f];
+      for (int a = 0; a < 3; ++a) {
+        p.box.lo[a] -= pad;
+        p.box.hi[a] += pad;
+        p.c[a] = 0.5f * (p.box.lo[a] + p.box.hi[a]);
+      }
+      p.id = f;
+      sb.grow(p.box);
+      cb.grow(p.c);
+    }
+    part[k] = sb, cpart[k] = cb;
+  });
+  Box root_box, root_cbox;
+  for (unsigned k = 0; k < T; ++k)
+    if (part[k].valid())
+      root_box.grow(part[k]), root_cbox.grow(cpart[k]);
 
   auto emit_tri = [&](uint32_t at, uint32_t f) {
     const ptc_face& face = desc->faces[f];
@@ -651,36 +974,17 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
     out.face_ids[at] = f;
   };
 
-  if (n_faces == 0) {
-    Node8 n;
-    std::memset(&n, 0, sizeof(n));
-    n.e[0] = n.e[1] = n.e[2] = 1;
-    out.nodes.push_back(n);
-    out.stats.wide_depth = 1;
-    return;
-  }
-
   const auto t0 = now();
-  if (timing)
-    fprintf(stderr, "build_bvh: triangle boxes %.2f s\n", secs(t_begin, t0));
-  Builder b(boxes);
-  if (timing)
-    fprintf(stderr, "build_bvh: builder set-up %.2f s\n", secs(t0, now()));
-  int root = b.build(0, n_faces, 0);
-  b.finish();
-  out.stats.max_depth = b.max_depth.load();
+  b.build(root_box, root_cbox);
+  const int root = b.root;
+  out.stats.max_depth = b.max_depth;
   const auto t1 = now();
 
-  // SAH cost of the binary tree (diagnostic)
+  const CollapseDp dp(b, pool);
   {
-    float root_area = b.nodes[root].box.half_area();
-    double cost = 0;
-    for (const BinNode& n : b.nodes)
-      cost += (n.leaf() ? (double)n.count : 1.0) * n.box.half_area();
-    out.stats.sah_cost = root_area > 0 ? (float)(cost / root_area) : 0.f;
+    const float root_area = b.nodes[root].box.half_area();
+    out.stats.sah_cost = root_area > 0 ? (float)(dp.sah_sum / root_area) : 0.f; // diagnostic
   }
-
-  const CollapseDp dp(b.nodes, root);
   const auto t2 = now();
 
   // Emission, level by level (== the order a serial breadth-first queue would give, so node
@@ -697,16 +1001,18 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
     int kids[8];
     int kid_in_slot[8];
     int n_kids;
-    uint32_t n_internal, n_tris;
+    uint32_t n_internal, n_tris, n_leaf_kids;
     uint32_t child_base, tri_base;
   };
-  std::vector<Item> level{ Item{ root, 0u } }, next;
-  std::vector<Plan> plan;
-  out.tris.reserve(n_faces);     // every face is emitted exactly once: no regrowth copies
-  out.face_ids.reserve(n_faces);
+  RawVector<Item> level, next;
+  level.push_back(Item{ root, 0u });
+  RawVector<Plan> plan;
+  // (sized once, not value-initialised: the threads that write the records touch the pages)
+  out.tris.resize(n_faces);
+  out.face_ids.resize(n_faces);
   out.nodes.reserve(n_faces / 4 + 16);
   out.nodes.resize(1);
-  uint32_t depth = 0;
+  uint32_t depth = 0, tri_top = 0;
   while (!level.empty()) {
     ++depth;
     plan.resize(level.size());
@@ -714,7 +1020,7 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
     //    slot s is visited first by rays whose direction is negative exactly on the axes set
     //    in s, so it should hold the child that comes first along sign_s.  Greedy on
     //    cost = centroid . sign_s.
-    parallel_for((uint32_t)level.size(), [&](uint32_t lo, uint32_t hi) {
+    pool.chunks(0, (uint32_t)level.size(), [&](uint32_t lo, uint32_t hi, unsigned) {
       std::vector<int> kids;
       for (uint32_t q = lo; q < hi; ++q) {
         const int bin = level[q].bin;
@@ -745,6 +1051,8 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
             cost[k][sl] = c;
           }
         }
+        for (int k = P.n_kids; k < 8; ++k)
+          P.kids[k] = -1;
         for (int round = 0; round < P.n_kids; ++round) {
           float bc = FLT_MAX;
           int bk = -1, bs = -1;
@@ -761,33 +1069,33 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
           slot_of[bk] = bs;
           P.kid_in_slot[bs] = bk;
         }
-        P.n_internal = P.n_tris = 0;
+        P.n_internal = P.n_tris = P.n_leaf_kids = 0;
         for (int sl = 0; sl < 8; ++sl) {
           const int k = P.kid_in_slot[sl];
           if (k < 0)
             continue;
-          if (dp.is_leaf(P.kids[k]))
+          if (dp.is_leaf(P.kids[k])) {
             P.n_tris += b.nodes[P.kids[k]].count;
-          else
+            P.n_leaf_kids++;
+          } else
             P.n_internal++;
         }
       }
     });
     // 2. index hand-out in queue order
-    uint32_t node_top = (uint32_t)out.nodes.size(), tri_top = (uint32_t)out.tris.size();
+    uint32_t node_top = (uint32_t)out.nodes.size();
     for (Plan& P : plan) {
       P.child_base = node_top;
       P.tri_base = tri_top;
       node_top += P.n_internal;
       tri_top += P.n_tris;
+      out.stats.n_leaves += P.n_leaf_kids;
     }
     const uint32_t next_first = (uint32_t)out.nodes.size();
     out.nodes.resize(node_top);
-    out.tris.resize(tri_top);
-    out.face_ids.resize(tri_top);
     next.resize(node_top - next_first);
     // 3. emit
-    parallel_for((uint32_t)level.size(), [&](uint32_t lo, uint32_t hi) {
+    pool.chunks(0, (uint32_t)level.size(), [&](uint32_t lo, uint32_t hi, unsigned) {
       for (uint32_t q = lo; q < hi; ++q) {
         const Plan& P = plan[q];
         const Box& nb = b.nodes[level[q].bin].box;
@@ -827,7 +1135,7 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
             n.valid24 |= ((1u << c.count) - 1u) << (3 * sl); // 001, 011, 111
             uint32_t ids[kMaxLeaf];
             for (uint32_t t = 0; t < c.count; ++t)
-              ids[t] = b.prims[c.first + t].id;
+              ids[t] = b.ids[c.first + t];
             for (uint32_t t = 1; t < c.count; ++t) // ascending face id (<= 3 entries)
               for (uint32_t u = t; u > 0 && ids[u] < ids[u - 1]; --u)
                 std::swap(ids[u], ids[u - 1]);
@@ -842,17 +1150,15 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
         out.nodes[level[q].out] = n;
       }
     });
-    for (const Plan& P : plan)
-      for (int sl = 0; sl < 8; ++sl)
-        if (P.kid_in_slot[sl] >= 0 && dp.is_leaf(P.kids[P.kid_in_slot[sl]]))
-          out.stats.n_leaves++;
     level.swap(next);
   }
+  out.tris.resize(tri_top); // == n_faces: every face is emitted exactly once
+  out.face_ids.resize(tri_top);
   out.stats.wide_depth = depth;
   reorder_treelets(out);
   if (timing)
-    fprintf(stderr, "build_bvh: %u faces: binary SAH %.2f s, collapse DP %.2f s, emit %.2f s\n", n_faces,
-            secs(t0, t1), secs(t1, t2), secs(t2, now()));
+    fprintf(stderr, "build_bvh: %u faces, %u threads: boxes %.2f s, binary SAH %.2f s (%u wide nodes, %zu tasks), collapse DP %.2f s, emit %.2f s\n",
+            n_faces, T, secs(t_begin, t0), secs(t0, t1), b.n_wide, b.tasks.size(), secs(t1, t2), secs(t2, now()));
 }
 
 uint32_t

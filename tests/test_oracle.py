@@ -164,3 +164,22 @@ def test_bvh_traversal_synthetic_and_axis_aligned_rays(oracle):
     i2, t2, _, _ = oracle_bvh_intersect(oracle, sc, hb, o, d)
     assert (i1 == i2).all()
     assert (bits(t1) == bits(t2)).all()
+
+
+def test_bvh_traversal_with_coincident_triangles(oracle):
+    """Many copies of one triangle (one centroid, no separating plane): the positional split of the
+    builder must lose none of them, and the FIRST copy must win the tie as in the reference's loop
+    (intersection.cuh:183-184)."""
+    base = pkg().synth.terrain_room(grid=12, tex_size=8)
+    faces = np.concatenate([np.repeat(base.faces[5:7], 300, axis=0), base.faces])
+    mats = [(int(m[0]), int(m[1]), float(m[2])) for m in base.materials]
+    sc = pkg().synth.make_blob(faces, [faces.shape[0]], mats, base.textures, base.lights, base.camera)
+    hb = pkg().host_bvh(sc)
+    assert sorted(hb["face_ids"].tolist()) == list(range(sc.n_faces))
+    o, d = random_rays(sc, 20000, seed=3)
+    i1, t1 = oracle.intersect(sc, o, d)
+    i2, t2, _, _ = oracle_bvh_intersect(oracle, sc, hb, o, d)
+    assert (i1 == i2).all()
+    assert (bits(t1) == bits(t2)).all()
+    assert ((i1 >= 0) & (i1 < 600)).any()  # the copies are hit, and then only through their first copy
+    assert set(np.unique(i1[(i1 >= 0) & (i1 < 600)]).tolist()) <= {0, 300}
