@@ -24,6 +24,7 @@
 #include <mutex>
 #include <numeric>
 #include <thread>
+#include <sys/mman.h>
 
 #if defined(__SSE2__)
 #include <emmintrin.h>
@@ -220,6 +221,8 @@ private:
 
 // malloc'ed array that is NOT value-initialised: the thread that fills a range is the one that
 // first touches its pages (one thread zero-filling 0.4 - 1 GB arrays was a third of the old build).
+// Big arrays ask for transparent huge pages (where the kernel grants them on madvise): the collapse
+// and the emission walk them at random.
 template <typename T>
 struct Raw
 {
@@ -231,7 +234,15 @@ struct Raw
   void alloc(size_t count)
   {
     std::free(p);
-    p = static_cast<T*>(std::malloc(std::max<size_t>(1, count) * sizeof(T)));
+    const size_t bytes = std::max<size_t>(1, count) * sizeof(T);
+    if (bytes >= (64u << 20)) {
+      void* q = nullptr;
+      if (posix_memalign(&q, 2u << 20, (bytes + (2u << 20) - 1) & ~(size_t)((2u << 20) - 1)) != 0)
+        throw std::bad_alloc();
+      madvise(q, bytes, MADV_HUGEPAGE);
+      p = static_cast<T*>(q);
+    } else
+      p = static_cast<T*>(std::malloc(bytes));
     if (!p)
       throw std::bad_alloc();
   }
@@ -279,9 +290,11 @@ struct Builder
     Box box[3][kBins];
 #endif
     uint32_t cnt[3][kBins];
+    uint32_t occupied[3]; // bit b: bin b of the axis holds something
     Bins()
     {
       std::memset(cnt, 0, sizeof(cnt));
+      occupied[0] = occupied[1] = occupied[2] = 0u;
 #if PTC_BUILD_SSE
       const __m128 big = _mm_set1_ps(FLT_MAX), small = _mm_set1_ps(-FLT_MAX);
       for (int a = 0; a < 3; ++a)
@@ -300,10 +313,12 @@ struct Builder
       box[a][b].grow(p.box);
 #endif
       cnt[a][b]++;
+      occupied[a] |= 1u << b;
     }
     void merge(const Bins& o)
     {
-      for (int a = 0; a < 3; ++a)
+      for (int a = 0; a < 3; ++a) {
+        occupied[a] |= o.occupied[a];
         for (int b = 0; b < kBins; ++b) {
 #if PTC_BUILD_SSE
           lo[a][b] = _mm_min_ps(o.lo[a][b], lo[a][b]);
@@ -313,6 +328,7 @@ struct Builder
 #endif
           cnt[a][b] += o.cnt[a][b];
         }
+      }
     }
     Box get(int a, int b) const
     {
@@ -328,6 +344,60 @@ struct Builder
 #endif
       return r;
     }
+  };
+
+  // running union of bins for the plane sweep; area() is Box::half_area() operation for operation
+  // (the products summed left to right), so both forms give the same bits
+  struct Sweep
+  {
+#if PTC_BUILD_SSE
+    __m128 lo = _mm_set1_ps(FLT_MAX), hi = _mm_set1_ps(-FLT_MAX);
+    void grow(const Bins& B, int a, int b)
+    {
+      lo = _mm_min_ps(B.lo[a][b], lo);
+      hi = _mm_max_ps(B.hi[a][b], hi);
+    }
+    float area() const
+    {
+      const __m128 d = _mm_sub_ps(hi, lo);                               // dx dy dz ..
+      const __m128 m = _mm_mul_ps(d, _mm_shuffle_ps(d, d, _MM_SHUFFLE(3, 0, 2, 1))); // dx*dy dy*dz dz*dx ..
+      __m128 s = _mm_add_ss(m, _mm_shuffle_ps(m, m, _MM_SHUFFLE(1, 1, 1, 1)));
+      s = _mm_add_ss(s, _mm_shuffle_ps(m, m, _MM_SHUFFLE(2, 2, 2, 2)));
+      return _mm_cvtss_f32(s);
+    }
+#else
+    Box acc;
+    void grow(const Bins& B, int a, int b) { acc.grow(B.box[a][b]); }
+    float area() const { return acc.half_area(); }
+#endif
+  };
+
+  // box of the centroids of the primitives one side of a partition receives
+  struct CentroidBox
+  {
+#if PTC_BUILD_SSE
+    __m128 lo = _mm_set1_ps(FLT_MAX), hi = _mm_set1_ps(-FLT_MAX);
+    void grow(const Prim& q)
+    {
+      const __m128 c = _mm_loadu_ps(q.c); // c[0..2] and the id bits (lane 3, ignored)
+      lo = _mm_min_ps(c, lo);
+      hi = _mm_max_ps(c, hi);
+    }
+    Box get() const
+    {
+      alignas(16) float l[4], h[4];
+      _mm_store_ps(l, lo);
+      _mm_store_ps(h, hi);
+      Box r;
+      for (int k = 0; k < 3; ++k)
+        r.lo[k] = l[k], r.hi[k] = h[k];
+      return r;
+    }
+#else
+    Box acc;
+    void grow(const Prim& q) { acc.grow(q.c); }
+    Box get() const { return acc; }
+#endif
   };
 
   struct Split
@@ -379,6 +449,31 @@ struct Builder
 
   static void fill_bins(Bins& B, const Split& s, const Prim* p, uint32_t lo, uint32_t hi)
   {
+#if PTC_BUILD_SSE
+    if (s.on[0] && s.on[1] && s.on[2]) {
+      // the three bin indices at once: the same subtract, multiply and truncation per lane as
+      // bin_of() (lane 3 carries the id bits through and is ignored); indices are 0..16, so a
+      // 16-bit min clamps them
+      const __m128 slo = _mm_setr_ps(s.lo[0], s.lo[1], s.lo[2], 0.f);
+      const __m128 ssc = _mm_setr_ps(s.scale[0], s.scale[1], s.scale[2], 0.f);
+      const __m128i cap = _mm_set1_epi32(kBins - 1);
+      for (uint32_t i = lo; i < hi; ++i) {
+        const __m128 t = _mm_mul_ps(_mm_sub_ps(_mm_loadu_ps(p[i].c), slo), ssc);
+        const __m128i b = _mm_min_epi16(_mm_cvttps_epi32(t), cap);
+        const __m128 plo = _mm_loadu_ps(p[i].box.lo), phi = _mm_loadu_ps(p[i].box.hi);
+        const int b0 = _mm_cvtsi128_si32(b), b1 = _mm_extract_epi16(b, 2), b2 = _mm_extract_epi16(b, 4);
+        B.lo[0][b0] = _mm_min_ps(plo, B.lo[0][b0]);
+        B.hi[0][b0] = _mm_max_ps(phi, B.hi[0][b0]);
+        B.lo[1][b1] = _mm_min_ps(plo, B.lo[1][b1]);
+        B.hi[1][b1] = _mm_max_ps(phi, B.hi[1][b1]);
+        B.lo[2][b2] = _mm_min_ps(plo, B.lo[2][b2]);
+        B.hi[2][b2] = _mm_max_ps(phi, B.hi[2][b2]);
+        B.cnt[0][b0]++, B.cnt[1][b1]++, B.cnt[2][b2]++;
+        B.occupied[0] |= 1u << b0, B.occupied[1] |= 1u << b1, B.occupied[2] |= 1u << b2;
+      }
+      return;
+    }
+#endif
     for (uint32_t i = lo; i < hi; ++i)
       for (int a = 0; a < 3; ++a)
         if (s.on[a])
@@ -395,25 +490,24 @@ struct Builder
       if (!s.on[a])
         continue;
       int occ[kBins], m = 0;
-      for (int b = 0; b < kBins; ++b)
-        if (B.cnt[a][b])
-          occ[m++] = b;
+      for (uint32_t bits = B.occupied[a]; bits; bits &= bits - 1)
+        occ[m++] = __builtin_ctz(bits);
       float right_area[kBins];
       uint32_t right_cnt[kBins];
-      Box acc;
+      Sweep right;
       uint32_t cnt = 0;
       for (int i = m - 1; i > 0; --i) {
-        acc.grow(B.get(a, occ[i]));
+        right.grow(B, a, occ[i]);
         cnt += B.cnt[a][occ[i]];
-        right_area[i] = acc.half_area();
+        right_area[i] = right.area();
         right_cnt[i] = cnt;
       }
-      acc = Box();
+      Sweep left;
       cnt = 0;
       for (int i = 0; i + 1 < m; ++i) {
-        acc.grow(B.get(a, occ[i]));
+        left.grow(B, a, occ[i]);
         cnt += B.cnt[a][occ[i]];
-        const float cost = acc.half_area() * cnt + right_area[i + 1] * right_cnt[i + 1];
+        const float cost = left.area() * cnt + right_area[i + 1] * right_cnt[i + 1];
         if (cost < s.cost) {
           s.cost = cost;
           s.axis = a;
@@ -476,26 +570,31 @@ struct Builder
     // in-place partition (the exchange order of std::partition); every primitive is classified
     // exactly once, and its centroid joins the box of the side it lands on
     const int a = s.axis;
+    const float slo = s.lo[a], ssc = s.scale[a];
+    const int sbin = s.bin;
+    auto goes_left = [=](const Prim& q) { return std::min(kBins - 1, (int)((q.c[a] - slo) * ssc)) <= sbin; };
+    CentroidBox cl, cr;
     uint32_t i = first, j = first + count;
     for (;;) {
-      while (i < j && s.bin_of(p[i], a) <= s.bin) {
-        clr[0].grow(p[i].c);
+      while (i < j && goes_left(p[i])) {
+        cl.grow(p[i]);
         ++i;
       }
       if (i == j)
         break;
-      clr[1].grow(p[i].c);
+      cr.grow(p[i]);
       --j;
-      while (i < j && !(s.bin_of(p[j], a) <= s.bin)) {
-        clr[1].grow(p[j].c);
+      while (i < j && !goes_left(p[j])) {
+        cr.grow(p[j]);
         --j;
       }
       if (i == j)
         break;
-      clr[0].grow(p[j].c);
+      cl.grow(p[j]);
       std::swap(p[i], p[j]);
       ++i;
     }
+    clr[0] = cl.get(), clr[1] = cr.get();
     mid = i;
     if (mid == first || mid == first + count) { // cannot happen (both sides of the plane hold a bin)
       lr[0] = lr[1] = clr[0] = clr[1] = Box();
@@ -589,17 +688,17 @@ struct Builder
           for (unsigned q = 0; q < k; ++q)
             wl += n_left[q];
           wr -= wl - j.first; // right primitives before this slice = primitives before it - left ones
-          Box bl, br;
+          CentroidBox bl, br;
           for (uint32_t i = lo; i < hi; ++i) {
             if (s.bin_of(src[i], a) <= s.bin) {
-              bl.grow(src[i].c);
+              bl.grow(src[i]);
               dst[wl++] = src[i];
             } else {
-              br.grow(src[i].c);
+              br.grow(src[i]);
               dst[wr++] = src[i];
             }
           }
-          cl[k] = bl, cr[k] = br;
+          cl[k] = bl.get(), cr[k] = br.get();
         });
         for (unsigned k = 0; k < T; ++k) {
           clr[0].grow(cl[k]);
