@@ -130,6 +130,6 @@ void build_bvh(const ptc_scene_desc* desc, HostBvh& out);
 
 // Shading records in global face order.
 // returns the largest material id any face names (0 for an empty scene), found in the same pass
-uint32_t build_shade_records(const ptc_scene_desc* desc, std::vector<ShadeRecord>& out);
+uint32_t build_shade_records(const ptc_scene_desc* desc, RawVector<ShadeRecord>& out);
 
 } // namespace ptc

@@ -1261,7 +1261,7 @@ build_bvh(const ptc_scene_desc* desc, HostBvh& out)
 }
 
 uint32_t
-build_shade_records(const ptc_scene_desc* desc, std::vector<ShadeRecord>& out)
+build_shade_records(const ptc_scene_desc* desc, RawVector<ShadeRecord>& out)
 {
   std::atomic<uint32_t> max_material{ 0 };
   uint32_t n_faces = 0;

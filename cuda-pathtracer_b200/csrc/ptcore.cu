@@ -738,7 +738,7 @@ upload_prepared(ptc_context* ctx, const ptc_scene_desc* desc, const PreparedScen
 {
   DeviceGuard g(ctx->device);
   const HostBvh& bvh = ps.bvh;
-  const std::vector<ShadeRecord>& shade = ps.shade;
+  const RawVector<ShadeRecord>& shade = ps.shade;
   const uint32_t n_faces = ps.n_faces;
 
   // built into a local record and published only when everything succeeded: a failed upload

@@ -16,7 +16,7 @@ namespace ptc {
 struct PreparedScene
 {
   HostBvh bvh;
-  std::vector<ShadeRecord> shade;
+  RawVector<ShadeRecord> shade;
   uint32_t n_faces = 0;
 };
 
