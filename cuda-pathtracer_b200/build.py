@@ -11,7 +11,7 @@ REPO = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libptcore.so")
 CUDA = os.environ.get("CUDA_HOME", "/usr/local/cuda")
-SOURCES = ["ptcore.cu", "kernels.cu", "group.cu", "bvh_builder.cpp", "flatten.cpp", "texpack.cpp"]
+SOURCES = ["ptcore.cu", "kernels.cu", "group.cu", "bvh_builder.cpp", "flatten.cpp", "texpack.cpp", "png.cpp"]
 HEADERS = ["bvh.h", "device_types.cuh", "kernels.cuh", "vecmath.cuh", "traverse.cuh", "shade.cuh",
            "ptcore_internal.h", "../../include/ptcore.h"]
 

@@ -79,7 +79,7 @@ EXPORTS = ["ptc_abi_version", "ptc_render_static", "ptc_group_upload_scene_from_
            "ptc_profile_frame", "ptc_render_host_async", "ptc_wait",
            "ptc_upload_scene_from_device", "ptc_set_cubemap_from_array",
            "ptc_set_cubemap_from_cross", "ptc_cubemap_faces_from_cross",
-           "ptc_write_ppm", "ptc_accum_save", "ptc_accum_load", "ptc_debug_read_bandwidth",
+           "ptc_write_ppm", "ptc_write_png", "ptc_accum_save", "ptc_accum_load", "ptc_debug_read_bandwidth",
            "ptc_group_create", "ptc_group_destroy", "ptc_group_last_error", "ptc_group_size",
            "ptc_group_context", "ptc_group_upload_scene", "ptc_group_set_cubemap", "ptc_group_render",
            "ptc_group_sync", "ptc_group_image", "ptc_group_read_image", "ptc_group_gather_accum",
@@ -119,7 +119,7 @@ def load_library() -> C.CDLL:
                      "ptc_launch_count", "ptc_set_wavefront", "ptc_profile_frame",
                      "ptc_render_host_async", "ptc_wait", "ptc_set_cubemap_from_cross",
                      "ptc_cubemap_faces_from_cross", "ptc_upload_scene_from_device",
-                     "ptc_set_cubemap_from_array", "ptc_write_ppm", "ptc_accum_save", "ptc_accum_load",
+                     "ptc_set_cubemap_from_array", "ptc_write_ppm", "ptc_write_png", "ptc_accum_save", "ptc_accum_load",
                      "ptc_debug_read_bandwidth", "ptc_group_create", "ptc_group_upload_scene",
                      "ptc_group_set_cubemap", "ptc_group_render", "ptc_group_sync", "ptc_group_read_image",
                      "ptc_group_gather_accum", "ptc_group_reset_accumulation", "ptc_shared_alloc",
@@ -192,6 +192,14 @@ def write_ppm(path: str, rgba: np.ndarray) -> None:
     h, w = rgba.shape[:2]
     if load_library().ptc_write_ppm(path.encode(), _ptr(rgba), C.c_uint32(w), C.c_uint32(h)):
         raise PtcError(f"ptc_write_ppm({path}) failed")
+
+
+def write_png(path: str, rgba: np.ndarray, keep_alpha: bool = False) -> None:
+    """RGBA8 frame ((h, w) uint32 or (h, w, 4) uint8, row 0 = top) -> PNG (RGB, or RGBA)."""
+    rgba = np.ascontiguousarray(rgba)
+    h, w = rgba.shape[:2]
+    if load_library().ptc_write_png(path.encode(), _ptr(rgba), C.c_uint32(w), C.c_uint32(h), C.c_int(int(keep_alpha))):
+        raise PtcError(f"ptc_write_png({path}) failed")
 
 
 def accum_save(path: str, accum: np.ndarray, samples: int) -> None:

@@ -37,8 +37,9 @@ extern "C" {
  * 5: additions only -- ptc_render_static, ptc_flatten_faces / ptc_upload_scene_indexed,
  *    ptc_texpack_*, ptc_group_upload_scene_from_device / ptc_group_set_cubemap_from_array,
  *    ptc_host_image_* / ptc_memcpy_strips_to_host / ptc_memcpy_strips_to_device;
- *    ptc_scene_info.smem_resident now reports what it says. */
-#define PTC_ABI_VERSION 5
+ *    ptc_scene_info.smem_resident now reports what it says.
+ * 6: addition only -- ptc_write_png. */
+#define PTC_ABI_VERSION 6
 
 typedef enum ptc_status
 {
@@ -307,12 +308,15 @@ int ptc_cubemap_faces_from_cross(const float* cross, uint32_t w, uint32_t h, uin
  * surface that interop.cpp:67-72 blitted upside down) ------------------------------------
  * ptc_write_ppm : binary PPM (P6) of an RGBA8 HOST frame as ptc_render writes it (row 0 = top,
  *                 alpha dropped).
+ * ptc_write_png : the same frame as a PNG (8-bit RGB, or RGBA when keep_alpha != 0; Sub filter,
+ *                 one fixed-Huffman deflate block, written by the library itself: no libpng / zlib).
  * ptc_accum_save/load : the float3 temporal framebuffer of a band (HOST, rows bottom-up as the
  *                 core keeps them) with the sample count it holds, so that a long accumulation
  *                 can stop and resume: load, pass the buffer as `accum` with upload_accum = 1
  *                 and continue with frame_nb = samples + 1.
  *                 File: "PTAC" u32 version(1) u32 width u32 rows u32 samples, then w*rows*3 f32. */
 int ptc_write_ppm(const char* path, const void* rgba, uint32_t width, uint32_t height);
+int ptc_write_png(const char* path, const void* rgba, uint32_t width, uint32_t height, int keep_alpha);
 int ptc_accum_save(const char* path, const float* accum, uint32_t width, uint32_t rows, uint32_t samples);
 int ptc_accum_load(const char* path, float* accum, uint64_t capacity_floats, uint32_t* width,
                    uint32_t* rows, uint32_t* samples);

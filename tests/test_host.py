@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     for s in syms:
         assert hasattr(lib, s), f"{s} declared in include/ptcore.h but not exported"
     assert sorted(P.core.EXPORTS) == syms
-    assert lib.ptc_abi_version() == 5
+    assert lib.ptc_abi_version() == 6
 
 
 def test_record_layouts_match_reference_contract():
@@ -477,6 +477,38 @@ def test_ppm_and_accumulator_files(tmp_path):
     open(a, "wb").write(b"nope")
     with pytest.raises(P.core.PtcError):
         P.core.accum_load(a)
+
+
+def test_png_writer_round_trip(tmp_path):
+    """ptc_write_png: the file is a valid PNG (CRCs, zlib stream, Adler-32 all checked
+    by an independent decoder) holding exactly the frame's bytes -- noise (literals only), flat and
+    periodic content (LZ77 matches up to the 32 KB window and the 258-byte match limit), 1 x 1."""
+    from PIL import Image
+    rng = np.random.default_rng(5)
+    h, w = 97, 211
+    noise = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    flat = np.zeros((h, w, 4), np.uint8)
+    flat[..., 0], flat[..., 3] = 200, 255
+    flat[h // 2:, :, 1] = (np.arange(w) // 8 * 9 % 256).astype(np.uint8)
+    stripes = np.zeros((40, 5000, 4), np.uint8)  # a row is 15 001 bytes: matches reach far back
+    stripes[..., :3] = rng.integers(0, 256, (1, 5000, 3), dtype=np.uint8)
+    stripes[::7] = 255 - stripes[::7]
+    one = np.array([[[1, 2, 3, 4]]], np.uint8)
+    p = str(tmp_path / "f.png")
+    for img in (noise, flat, stripes, one):
+        for alpha in (False, True):
+            P.core.write_png(p, img, keep_alpha=alpha)
+            im = Image.open(p)
+            im.load()
+            assert im.mode == ("RGBA" if alpha else "RGB")
+            assert (np.asarray(im) == img[..., : 4 if alpha else 3]).all()
+    assert os.path.getsize(p) < 100
+    P.core.write_png(p, flat)
+    assert os.path.getsize(p) < flat.size // 20  # flat content does compress
+    P.core.write_png(p, noise.view(np.uint32).reshape(h, w))  # the (h, w) uint32 form ptc_render fills
+    assert (np.asarray(Image.open(p)) == noise[..., :3]).all()
+    with pytest.raises(P.core.PtcError):
+        P.core.write_png(str(tmp_path / "no_such_dir" / "f.png"), noise)
 
 
 def _run_bench(*argv, env=None):
