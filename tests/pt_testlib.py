@@ -285,6 +285,64 @@ def random_rays(sc, n, seed=1, pad=0.05):
     return o, d
 
 
+# triangle soups that stress the builder and the quantised boxes (CPU: O1 == O2; GPU: device walk ==
+# the reference's brute force)
+def soup_scene(v):
+    """Scene from bare triangles (F, 3, 3): flat normals, trivial uvs, one material, no lights."""
+    synth = pkg().synth
+    v = np.asarray(v, np.float32)
+    f = v.shape[0]
+    n = np.tile(np.array([0, 0, 1], np.float32), (f, 3, 1))
+    uv = np.tile(np.array([[0, 0], [1, 0], [0, 1]], np.float32), (f, 1, 1))
+    faces = synth.faces_from_arrays(v, n, uv, np.zeros(f, np.uint32))
+    return synth.make_blob(faces, [f], [(0, -1, 1.0)], [np.ones((1, 1, 4), np.float32)], np.zeros((0, 8)),
+                           synth.camera_array((0, 0, 3), (0, 0, -1)))
+
+
+def aimed_rays(sc, n, rng):
+    """Rays from random origins THROUGH vertices, edge midpoints and centroids of random faces: hits on
+    shared edges and vertices are where two faces tie and where a box that is one ulp short loses a hit."""
+    v = sc.faces_f32()[:, :9].reshape(-1, 3, 3).astype(np.float64)
+    f = rng.integers(0, v.shape[0], n)
+    w = rng.integers(0, 7, n)
+    bary = np.array([[1, 0, 0], [0, 1, 0], [0, 0, 1], [.5, .5, 0], [0, .5, .5], [.5, 0, .5], [1 / 3, 1 / 3, 1 / 3]])[w]
+    target = (v[f] * bary[:, :, None]).sum(1)
+    lo, hi = v.reshape(-1, 3).min(0), v.reshape(-1, 3).max(0)
+    o = lo - 0.3 * (hi - lo + 1e-3) + (1.6 * (hi - lo + 1e-3)) * rng.random((n, 3))
+    d = target - o
+    d /= np.maximum(np.linalg.norm(d, axis=1, keepdims=True), 1e-30)
+    return o.astype(np.float32), d.astype(np.float32)
+
+
+def triangle_soups():
+    rng = np.random.default_rng(20240611)
+    def tri(centres, size):
+        return centres[:, None, :] + size * rng.normal(size=(centres.shape[0], 3, 3))
+    yield "uniform small triangles", tri(rng.random((2000, 3)), 0.02)
+    yield "long thin triangles across the scene", tri(rng.random((400, 3)), np.array([1.0, 0.01, 0.01]))
+    flat = tri(rng.random((800, 3)), 0.05)
+    flat[..., 2] = 0.25
+    yield "all in one axis-aligned plane (zero extent on z)", flat
+    c = rng.random((12, 3)) * 1000.0
+    yield "tight clusters in a large scene", tri(np.repeat(c, 150, axis=0), 1e-3)
+    yield "far from the origin", tri(rng.random((1500, 3)) + 1.0e4, 0.03)
+    # (smaller still and the reference's own test rejects every face: det < 1e-7, intersection.cuh:110)
+    yield "small scene near the reference's determinant cut-off", tri(rng.random((1500, 3)) * 0.05, 1.5e-3)
+    mixed = tri(rng.random((1000, 3)), 0.03)
+    mixed[::5, 1] = mixed[::5, 0]          # zero-area (two equal vertices)
+    mixed[1::5, 2] = 0.5 * (mixed[1::5, 0] + mixed[1::5, 1])  # zero-area (collinear)
+    yield "zero-area triangles mixed in", mixed
+    g = 24  # a mesh with exactly shared vertices and edges, every cell twice (duplicates)
+    xs = np.linspace(0, 1, g + 1)
+    X, Y = np.meshgrid(xs, xs)
+    P = np.stack([X, Y, 0.1 * np.sin(5 * X) * np.cos(4 * Y)], -1)
+    a, b, c2, d = P[:-1, :-1], P[:-1, 1:], P[1:, 1:], P[1:, :-1]
+    cells = np.concatenate([np.stack([a, b, c2], 2).reshape(-1, 3, 3), np.stack([a, c2, d], 2).reshape(-1, 3, 3)])
+    yield "shared-edge mesh, every face twice", np.concatenate([cells, cells])
+    yield "one triangle", tri(rng.random((1, 3)), 0.3)
+    yield "four triangles", tri(rng.random((4, 3)), 0.3)
+
+
 def oracle_bvh_intersect(orc, sc, hb, origins, dirs):
     """O2: the oracle's scalar traversal of the PRODUCT's BVH arrays (host_bvh())."""
     desc = sc.to_desc()

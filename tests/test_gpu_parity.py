@@ -17,7 +17,8 @@ import os
 import numpy as np
 import pytest
 
-from pt_testlib import (GOLDEN, RefGpu, cube_of, load_scene, oracle_render_stats, pkg, random_rays)
+from pt_testlib import (GOLDEN, RefGpu, aimed_rays, cube_of, load_scene, oracle_render_stats, pkg, random_rays,
+                        soup_scene, triangle_soups)
 
 pytestmark = pytest.mark.gpu
 P = pkg()
@@ -1204,3 +1205,37 @@ def test_full_image_store_and_flags(core):
         torch.cuda.synchronize()
         other.close()
         shared.close()
+
+
+# -- geometry that stresses the builder and the quantised boxes ------------------------------------
+@pytest.mark.xfail(strict=False, reason="added after the round's GPU budget was spent: never yet run on hardware "
+                   "(XPASS = the device walk agrees with the reference's brute force on this geometry)")
+@pytest.mark.parametrize("name,verts", list(triangle_soups()), ids=[n for n, _ in triangle_soups()])
+def test_device_traversal_on_triangle_soups(core, oracle, name, verts):
+    """The CPU suite's soups (tests/test_oracle.py::test_bvh_traversal_on_triangle_soups: thin, coplanar,
+    clustered, far-from-origin, near the determinant cut-off, zero-area, duplicated shared-edge meshes)
+    through the DEVICE walk: ids and t bit for bit against the reference's own brute-force loop on the
+    GPU (G0), or, without oracle/_ref, against oracle O1 within the stated CPU tolerances."""
+    sc = soup_scene(verts)
+    sid = core.upload_scene(sc)
+    o1, d1 = random_rays(sc, 3000, seed=len(name))
+    o2, d2 = aimed_rays(sc, 5000, np.random.default_rng(len(name)))
+    o, d = np.concatenate([o1, o2]), np.concatenate([d1, d2])
+    ids, t = core.intersect_rays(sid, o, d)
+    try:
+        g0 = RefGpu(sc)
+    except FileNotFoundError:
+        g0 = None
+    if g0 is not None:
+        try:
+            gid, gt = g0.intersect(o, d)
+        finally:
+            g0.close()
+        assert (ids == gid).all(), f"{name}: {int((ids != gid).sum())} rays disagree"
+        assert (bits(t) == bits(gt)).all()
+    else:
+        oid, ot = oracle.intersect(sc, o, d)
+        mism = ids != oid
+        assert mism.mean() <= ID_MISMATCH_FRAC, int(mism.sum())
+        ok = ~mism & (oid >= 0)
+        assert np.allclose(t[ok], ot[ok], rtol=1e-4, atol=1e-5)

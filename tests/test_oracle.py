@@ -13,7 +13,8 @@ import os
 import numpy as np
 import pytest
 
-from pt_testlib import GOLDEN, load_scene, oracle_bvh_intersect, oracle_render_stats, pkg, random_rays
+from pt_testlib import (GOLDEN, aimed_rays, load_scene, oracle_bvh_intersect, oracle_render_stats, pkg, random_rays,
+                        soup_scene, triangle_soups)
 
 
 def bits(a):
@@ -183,3 +184,22 @@ def test_bvh_traversal_with_coincident_triangles(oracle):
     assert (bits(t1) == bits(t2)).all()
     assert ((i1 >= 0) & (i1 < 600)).any()  # the copies are hit, and then only through their first copy
     assert set(np.unique(i1[(i1 >= 0) & (i1 < 600)]).tolist()) <= {0, 300}
+
+
+@pytest.mark.parametrize("name,verts", list(triangle_soups()), ids=[n for n, _ in triangle_soups()])
+def test_bvh_traversal_on_triangle_soups(oracle, name, verts):
+    """O2 (the oracle walking the product's BVH) == O1 (the reference's loop over all faces,
+    intersection.cuh:179-196) on geometry that stresses the builder and the quantised boxes:
+    ids and t bit for bit, for random rays and for rays aimed at vertices / edges / centroids."""
+    sc = soup_scene(verts)
+    hb = pkg().host_bvh(sc)
+    assert sorted(hb["face_ids"].tolist()) == list(range(sc.n_faces))
+    rng = np.random.default_rng(len(name))
+    o1, d1 = random_rays(sc, 3000, seed=len(name))
+    o2, d2 = aimed_rays(sc, 5000, rng)
+    o, d = np.concatenate([o1, o2]), np.concatenate([d1, d2])
+    i1, t1 = oracle.intersect(sc, o, d)
+    i2, t2, _, _ = oracle_bvh_intersect(oracle, sc, hb, o, d)
+    assert (i1 == i2).all(), f"{name}: {int((i1 != i2).sum())} rays disagree"
+    assert (bits(t1) == bits(t2)).all()
+    assert (i1[3000:] >= 0).mean() > 0.1  # the aimed rays do hit (front faces only, intersection.cuh:110)
