@@ -1208,8 +1208,6 @@ def test_full_image_store_and_flags(core):
 
 
 # -- geometry that stresses the builder and the quantised boxes ------------------------------------
-@pytest.mark.xfail(strict=False, reason="added after the round's GPU budget was spent: never yet run on hardware "
-                   "(XPASS = the device walk agrees with the reference's brute force on this geometry)")
 @pytest.mark.parametrize("name,verts", list(triangle_soups()), ids=[n for n, _ in triangle_soups()])
 def test_device_traversal_on_triangle_soups(core, oracle, name, verts):
     """The CPU suite's soups (tests/test_oracle.py::test_bvh_traversal_on_triangle_soups: thin, coplanar,
