@@ -270,11 +270,21 @@ _TREE_PINS = {
     1: "abc6adad83ba6305", 2: "212adad81df75d78", 5: "ea36dd2675d896e5", 24: "fcad3c181e09a235",
     40: "30c8d89d33c08161", 150: "227bef752c04487c", 300: "655c4e9ad843f67f",
 }
+# the synthetic grids are made with numpy's float32 sin / cos, whose last bit may differ between CPUs
+# (SIMD code paths): a grid is compared only where its Face bytes are the ones the pin was taken on
+_GRID_INPUT = {1: "5da30c32c5698d67", 2: "7bfca86891a0eee5", 5: "3984df7ce9ec003c", 24: "fd8ede562e1191ad",
+               40: "3e3f1d443181c20e", 150: "b6ac1357fb038cf9", 300: "dec15e98aabed7a8"}
 
 
 @pytest.mark.parametrize("key", list(_TREE_PINS))
 def test_bvh_tree_is_the_pinned_tree(key):
-    sc = load_scene(key) if isinstance(key, str) else P.synth.terrain_room(key, tex_size=8)
+    import hashlib
+    if isinstance(key, str):
+        sc = load_scene(key)
+    else:
+        sc = P.synth.terrain_room(key, tex_size=8)
+        if hashlib.sha1(sc.faces.tobytes()).hexdigest()[:16] != _GRID_INPUT[key]:
+            pytest.skip("numpy's float32 sin / cos give other bits on this CPU: not the pinned input")
     assert _tree_hash(P.host_bvh(sc)) == _TREE_PINS[key]
 
 
