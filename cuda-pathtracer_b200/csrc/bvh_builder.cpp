@@ -26,7 +26,7 @@
 #include <thread>
 #include <sys/mman.h>
 
-#if defined(__SSE2__)
+#if defined(__SSE2__) && !defined(PTC_BUILD_SCALAR) // (aarch64 hosts and -DPTC_BUILD_SCALAR take the plain C++ forms: same bits)
 #include <emmintrin.h>
 #define PTC_BUILD_SSE 1
 #else

@@ -288,6 +288,26 @@ def test_bvh_tree_is_the_pinned_tree(key):
     assert _tree_hash(P.host_bvh(sc)) == _TREE_PINS[key]
 
 
+def test_bvh_builder_scalar_build_gives_the_same_tree(tmp_path):
+    """The builder's SSE forms (bin fill, plane sweep, centroid boxes) against its plain C++ forms
+    (-DPTC_BUILD_SCALAR, what a non-x86 host compiles): same nodes, records and ids."""
+    so = str(tmp_path / "libbvh_scalar.so")
+    csrc = os.path.join(REPO, "cuda-pathtracer_b200", "csrc")
+    subprocess.run(["g++", "-std=c++17", "-O2", "-DPTC_BUILD_SCALAR", "-fPIC", "-pthread", "-ffp-contract=off", "-shared",
+                    "-I", os.path.join(REPO, "include"), "-I", csrc, os.path.join(csrc, "bvh_builder.cpp"), "-o", so],
+                   check=True)
+    lib = C.CDLL(so)
+    lib.ptc_host_bvh_free.restype = None
+    for sc in (load_scene("indoor_plain"), P.synth.terrain_room(150, tex_size=8), _with_duplicates(12, 2, 1000)):
+        desc, hb = sc.to_desc(), P.core.PtcHostBvh()
+        assert lib.ptc_host_bvh_build(C.byref(desc), C.byref(hb)) == 0
+        got = (C.string_at(hb.nodes, hb.n_nodes * hb.node_bytes), C.string_at(hb.tris, hb.n_tris * hb.tri_bytes),
+               C.string_at(hb.tri_face_ids, hb.n_tris * 4))
+        lib.ptc_host_bvh_free(C.byref(hb))
+        want = P.host_bvh(sc)
+        assert got == (want["nodes"].tobytes(), want["tris"].tobytes(), want["face_ids"].tobytes())
+
+
 def test_bvh_coincident_centroids_do_not_depend_on_threads(monkeypatch):
     """Primitives whose centroids coincide are cut by position after ordering them by face id
     (bvh_builder.cpp median_by_id), in a subtree task (2 x 1000 copies) and in a node wide enough
